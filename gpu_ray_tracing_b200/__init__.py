@@ -1,0 +1,11 @@
+"""B200-native drop-in for the per-pixel ray-trace pass of Sur091/GPU-Ray-Tracing.
+
+The product is the CUDA shared library behind include/rt_abi.h; this package is the thin host
+layer that mirrors the reference's names for tests, benchmarks and headless use.
+"""
+from .api import (  # noqa: F401
+    CameraSettings, ComputeShaderNode, ComputeShaderState, GpuSphere, MultiRenderer, Renderer, RtError, RtVec3,
+    SceneCamera, SphereCollection, SPHERE_DTYPE, create_default_spheres, create_grid_spheres,
+    create_random_spheres, device_count, lib, orbit_camera, render, render_frames,
+)
+from ._lib import LIB_PATH, build  # noqa: F401

@@ -1,0 +1,428 @@
+"""ctypes bindings for include/rt_abi.h plus a thin host layer that mirrors the reference's names.
+
+Reference counterparts (paths relative to the reference repo):
+  CameraSettings / SceneCamera ............ src/camera.rs:9-46, 256-351
+  GpuSphere / SphereCollection ............ src/scene/sphere.rs:14-42
+  create_default_spheres .................. src/scene/sphere.rs:45-153 (seeded here)
+  ComputeShaderNode (Loading/Init/Update) . src/lib.rs:326-422
+  render(scene, camera, w, h) ............. new headless entry (rt_render)
+
+Everything that computes goes through the C ABI; numpy is used only to hold bytes.
+"""
+import ctypes as C
+import enum
+
+import numpy as np
+
+from . import _lib
+
+# ------------------------------------------------------------------------------------------------
+# layouts
+# ------------------------------------------------------------------------------------------------
+
+
+class RtVec3(C.Structure):
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("z", C.c_float)]
+
+    def __init__(self, x=0.0, y=0.0, z=0.0):
+        super().__init__(x, y, z)
+
+    def tuple(self):
+        return (self.x, self.y, self.z)
+
+
+class SceneCamera(C.Structure):
+    """176-byte uniform, src/camera.rs:256-291."""
+    _fields_ = [
+        ("center", RtVec3), ("viewport_height", C.c_float),
+        ("viewport_upper_left", RtVec3), ("viewport_width", C.c_float),
+        ("pixel_delta_u", RtVec3), ("defocus_angle", C.c_float),
+        ("pixel_delta_v", RtVec3), ("aspect_ratio", C.c_float),
+        ("defocus_disk_u", RtVec3), ("_padding0", C.c_float),
+        ("viewport_u", RtVec3), ("_padding1", C.c_float),
+        ("defocus_disk_v", RtVec3), ("max_depth", C.c_float),
+        ("look_from", RtVec3), ("samples_per_pixel", C.c_float),
+        ("look_at", RtVec3), ("camera_has_moved", C.c_float),
+        ("vup", RtVec3), ("random_seed", C.c_float),
+        ("viewport_v", RtVec3), ("defocus_radius", C.c_float),
+    ]
+
+    def copy(self):
+        out = SceneCamera()
+        C.memmove(C.byref(out), C.byref(self), C.sizeof(SceneCamera))
+        return out
+
+    def to_bytes(self) -> bytes:
+        return bytes(memoryview(self))
+
+    @classmethod
+    def from_bytes(cls, b: bytes) -> "SceneCamera":
+        assert len(b) == 176
+        return cls.from_buffer_copy(b)
+
+    @classmethod
+    def from_settings(cls, settings: "CameraSettings", width: int, height: int, random_seed: float) -> "SceneCamera":
+        """SceneCamera::from(&CameraSettings), src/camera.rs:293-351, for a width x height image."""
+        out = cls()
+        _check(lib().rt_camera_from_settings(C.byref(settings), width, height, C.c_float(random_seed), C.byref(out)))
+        return out
+
+
+class GpuSphere(C.Structure):
+    """32-byte storage element, src/scene/sphere.rs:20-26."""
+    _fields_ = [("position", RtVec3), ("radius", C.c_float), ("color", C.c_float * 4)]
+
+
+class CameraSettings(C.Structure):
+    """src/camera.rs:9-28; defaults from camera.rs:30-46."""
+    _fields_ = [
+        ("field_of_view", C.c_float), ("samples_per_pixel", C.c_uint32), ("camera_has_moved", C.c_uint32),
+        ("max_depth", C.c_uint32), ("vup", RtVec3), ("look_from", RtVec3), ("look_at", RtVec3),
+        ("defocus_angle", C.c_float), ("focus_distance", C.c_float),
+    ]
+
+    @classmethod
+    def default(cls) -> "CameraSettings":
+        s = cls()
+        lib().rt_camera_settings_default(C.byref(s))
+        return s
+
+
+SPHERE_DTYPE = np.dtype([("position", "<f4", 3), ("radius", "<f4"), ("color", "<f4", 4)])
+assert SPHERE_DTYPE.itemsize == 32 and C.sizeof(GpuSphere) == 32 and C.sizeof(SceneCamera) == 176
+
+RT_OK = 0
+RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_NO_SCENE, RT_ERR_OUT_OF_MEMORY, RT_ERR_STATE = -1, -2, -3, -4, -5, -6
+
+
+class RtError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"rt error {code}: {message}")
+        self.code = code
+
+
+_LIB = None
+
+# name -> (restype, argtypes); every symbol include/rt_abi.h declares
+_P = C.c_void_p
+_SIGNATURES = {
+    "rt_last_error": (C.c_char_p, []),
+    "rt_version": (C.c_char_p, []),
+    "rt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "rt_create": (C.c_int, [C.c_int, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_create_window": (C.c_int, [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_destroy": (C.c_int, [_P]),
+    "rt_set_scene": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32]),
+    "rt_init": (C.c_int, [_P]),
+    "rt_update": (C.c_int, [_P, C.POINTER(SceneCamera)]),
+    "rt_update_n": (C.c_int, [_P, C.POINTER(SceneCamera), C.c_uint32]),
+    "rt_synchronize": (C.c_int, [_P]),
+    "rt_read_accum": (C.c_int, [_P, _P]),
+    "rt_write_accum": (C.c_int, [_P, _P]),
+    "rt_read_rgba8": (C.c_int, [_P, _P]),
+    "rt_rays_traced": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "rt_exact_tests": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "rt_reset_counters": (C.c_int, [_P]),
+    "rt_timer_begin": (C.c_int, [_P]),
+    "rt_timer_end": (C.c_int, [_P, C.POINTER(C.c_float)]),
+    "rt_kernel_launches": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "rt_accum_device_ptr": (C.c_int, [_P, C.POINTER(_P)]),
+    "rt_rgba8_device_ptr": (C.c_int, [_P, C.POINTER(_P)]),
+    "rt_quantize": (C.c_int, [_P]),
+    "rt_stream": (C.c_int, [_P, C.POINTER(_P)]),
+    "rt_window": (C.c_int, [_P] + [C.POINTER(C.c_uint32)] * 4),
+    "rt_set_kernel_variant": (C.c_int, [_P, C.c_int]),
+    "rt_render": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
+    "rt_render_frames": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
+    "rt_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_multi_destroy": (C.c_int, [_P]),
+    "rt_multi_set_scene": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32]),
+    "rt_multi_init": (C.c_int, [_P]),
+    "rt_multi_update": (C.c_int, [_P, C.POINTER(SceneCamera)]),
+    "rt_multi_gather_rgba8": (C.c_int, [_P, _P]),
+    "rt_multi_gather_accum": (C.c_int, [_P, _P]),
+    "rt_multi_rays_traced": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
+    "rt_multi_shard": (C.c_int, [_P, C.c_uint32, C.POINTER(_P)]),
+    "rt_camera_settings_default": (None, [C.POINTER(CameraSettings)]),
+    "rt_camera_from_settings": (C.c_int, [C.POINTER(CameraSettings), C.c_uint32, C.c_uint32, C.c_float, C.POINTER(SceneCamera)]),
+    "rt_create_default_spheres": (C.c_int, [C.c_uint64, _P, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "rt_create_random_spheres": (C.c_int, [C.c_uint64, C.c_uint32, _P]),
+    "rt_create_grid_spheres": (C.c_int, [C.c_uint64, C.c_uint32, _P]),
+    "rt_orbit_camera": (C.c_int, [C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.POINTER(SceneCamera)]),
+}
+
+
+def lib() -> C.CDLL:
+    global _LIB
+    if _LIB is None:
+        handle = _lib.load()
+        for name, (restype, argtypes) in _SIGNATURES.items():
+            fn = getattr(handle, name)   # AttributeError here == the library does not export the ABI
+            fn.restype = restype
+            fn.argtypes = argtypes
+        _LIB = handle
+    return _LIB
+
+
+def _check(code: int) -> None:
+    if code != RT_OK:
+        raise RtError(code, lib().rt_last_error().decode("utf-8", "replace"))
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    code = lib().rt_device_count(C.byref(n))
+    return n.value if code == RT_OK else 0
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+# ------------------------------------------------------------------------------------------------
+# scenes (src/scene/sphere.rs)
+# ------------------------------------------------------------------------------------------------
+class SphereCollection:
+    """`SphereCollection { spheres, count }` (sphere.rs:29-33): a padded buffer and the live count."""
+
+    def __init__(self, spheres: np.ndarray, count: int):
+        spheres = np.ascontiguousarray(spheres, dtype=SPHERE_DTYPE)
+        if count > len(spheres):
+            raise ValueError("count exceeds buffer length")
+        self.spheres = spheres
+        self.count = int(count)
+
+    def to_bytes(self) -> bytes:
+        return self.spheres.tobytes()
+
+    @classmethod
+    def from_bytes(cls, b: bytes, count: int) -> "SphereCollection":
+        return cls(np.frombuffer(b, dtype=SPHERE_DTYPE).copy(), count)
+
+
+def create_default_spheres(seed: int = 0) -> SphereCollection:
+    """sphere.rs:45-153 with a seeded generator in place of rand::random."""
+    buf = np.zeros(256, dtype=SPHERE_DTYPE)
+    count, length = C.c_uint32(0), C.c_uint32(0)
+    _check(lib().rt_create_default_spheres(seed, _ptr(buf), len(buf), C.byref(count), C.byref(length)))
+    return SphereCollection(buf[: length.value].copy(), count.value)
+
+
+def create_random_spheres(n: int, seed: int = 1234) -> SphereCollection:
+    buf = np.zeros(n, dtype=SPHERE_DTYPE)
+    _check(lib().rt_create_random_spheres(seed, n, _ptr(buf)))
+    return SphereCollection(buf, n)
+
+
+def create_grid_spheres(n: int, seed: int = 4321) -> SphereCollection:
+    buf = np.zeros(n, dtype=SPHERE_DTYPE)
+    _check(lib().rt_create_grid_spheres(seed, n, _ptr(buf)))
+    return SphereCollection(buf, n)
+
+
+def orbit_camera(k: int, n: int, width: int, height: int, radius: float = 60.0, cam_height: float = 9.0,
+                 fov_deg: float = 40.0) -> SceneCamera:
+    out = SceneCamera()
+    _check(lib().rt_orbit_camera(k, n, radius, cam_height, fov_deg, width, height, C.byref(out)))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# renderer
+# ------------------------------------------------------------------------------------------------
+class Renderer:
+    """One device, one accumulation image (or a row window of it)."""
+
+    def __init__(self, width: int, height: int, device: int = 0, row_begin: int = 0, row_count: int = None):
+        self._h = C.c_void_p()
+        if row_count is None:
+            row_count = height - row_begin
+        _check(lib().rt_create_window(device, width, height, row_begin, row_count, C.byref(self._h)))
+        self.width, self.height, self.row_begin, self.row_count, self.device = width, height, row_begin, row_count, device
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().rt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def set_scene(self, scene: SphereCollection):
+        _check(lib().rt_set_scene(self._h, _ptr(scene.spheres), len(scene.spheres), scene.count))
+
+    def init(self):
+        _check(lib().rt_init(self._h))
+
+    def update(self, camera: SceneCamera):
+        _check(lib().rt_update(self._h, C.byref(camera)))
+
+    def update_n(self, cameras):
+        arr = (SceneCamera * len(cameras))(*cameras)
+        _check(lib().rt_update_n(self._h, arr, len(cameras)))
+
+    def synchronize(self):
+        _check(lib().rt_synchronize(self._h))
+
+    def read_accum(self, out: np.ndarray = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.row_count, self.width, 4), dtype=np.float32)
+        _check(lib().rt_read_accum(self._h, _ptr(out)))
+        return out
+
+    def write_accum(self, accum: np.ndarray):
+        accum = np.ascontiguousarray(accum, dtype=np.float32)
+        assert accum.size == self.row_count * self.width * 4
+        _check(lib().rt_write_accum(self._h, _ptr(accum)))
+
+    def read_rgba8(self, out: np.ndarray = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.row_count, self.width, 4), dtype=np.uint8)
+        _check(lib().rt_read_rgba8(self._h, _ptr(out)))
+        return out
+
+    def read_rgba8_into(self, host_ptr: int):
+        _check(lib().rt_read_rgba8(self._h, C.c_void_p(host_ptr)))
+
+    def quantize(self):
+        _check(lib().rt_quantize(self._h))
+
+    def rays_traced(self) -> int:
+        v = C.c_uint64(0)
+        _check(lib().rt_rays_traced(self._h, C.byref(v)))
+        return v.value
+
+    def exact_tests(self) -> int:
+        v = C.c_uint64(0)
+        _check(lib().rt_exact_tests(self._h, C.byref(v)))
+        return v.value
+
+    def reset_counters(self):
+        _check(lib().rt_reset_counters(self._h))
+
+    def timer_begin(self):
+        _check(lib().rt_timer_begin(self._h))
+
+    def timer_end(self) -> float:
+        ms = C.c_float(0)
+        _check(lib().rt_timer_end(self._h, C.byref(ms)))
+        return ms.value
+
+    def kernel_launches(self) -> int:
+        v = C.c_uint64(0)
+        _check(lib().rt_kernel_launches(self._h, C.byref(v)))
+        return v.value
+
+    def set_kernel_variant(self, variant: int):
+        _check(lib().rt_set_kernel_variant(self._h, variant))
+
+    def accum_device_ptr(self) -> int:
+        p = C.c_void_p()
+        _check(lib().rt_accum_device_ptr(self._h, C.byref(p)))
+        return p.value
+
+    def rgba8_device_ptr(self) -> int:
+        p = C.c_void_p()
+        _check(lib().rt_rgba8_device_ptr(self._h, C.byref(p)))
+        return p.value
+
+    def stream(self) -> int:
+        p = C.c_void_p()
+        _check(lib().rt_stream(self._h, C.byref(p)))
+        return p.value or 0
+
+
+class MultiRenderer:
+    """One image sharded by row blocks over several devices of this host (rt_multi_*)."""
+
+    def __init__(self, devices, width: int, height: int):
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib().rt_multi_create(arr, len(devices), width, height, C.byref(self._h)))
+        self.width, self.height, self.devices = width, height, list(devices)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            lib().rt_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def set_scene(self, scene: SphereCollection):
+        _check(lib().rt_multi_set_scene(self._h, _ptr(scene.spheres), len(scene.spheres), scene.count))
+
+    def init(self):
+        _check(lib().rt_multi_init(self._h))
+
+    def update(self, camera: SceneCamera):
+        _check(lib().rt_multi_update(self._h, C.byref(camera)))
+
+    def gather_rgba8(self, to_host: bool = True):
+        out = np.empty((self.height, self.width, 4), dtype=np.uint8) if to_host else None
+        _check(lib().rt_multi_gather_rgba8(self._h, _ptr(out) if to_host else None))
+        return out
+
+    def gather_accum(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        _check(lib().rt_multi_gather_accum(self._h, _ptr(out)))
+        return out
+
+    def rays_traced(self) -> int:
+        v = C.c_uint64(0)
+        _check(lib().rt_multi_rays_traced(self._h, C.byref(v)))
+        return v.value
+
+
+# ------------------------------------------------------------------------------------------------
+# the render-graph node (src/lib.rs:326-422)
+# ------------------------------------------------------------------------------------------------
+class ComputeShaderState(enum.Enum):
+    Loading = 0
+    Init = 1
+    Update = 2
+
+
+class ComputeShaderNode:
+    """Mirror of `ComputeShaderNode` (src/lib.rs:332-422): `update()` advances the state machine
+    Loading -> Init -> Update(1) <-> Update(0) (lib.rs:345-377) and `run()` issues the dispatch of
+    the current state (lib.rs:379-421): nothing while Loading, `init` in Init, `update` in Update.
+    Pipelines are compiled ahead of time here, so Loading lasts exactly one `update()` call."""
+
+    def __init__(self, renderer: Renderer):
+        self.renderer = renderer
+        self.state = ComputeShaderState.Loading
+        self.index = 0   # the ping-pong index the reference carries; kept for API parity only
+
+    def update(self):
+        if self.state is ComputeShaderState.Loading:
+            self.state = ComputeShaderState.Init
+        elif self.state is ComputeShaderState.Init:
+            self.state, self.index = ComputeShaderState.Update, 1
+        else:
+            self.index = 1 - self.index
+
+    def run(self, camera: SceneCamera):
+        if self.state is ComputeShaderState.Init:
+            self.renderer.init()
+        elif self.state is ComputeShaderState.Update:
+            self.renderer.update(camera)
+
+
+def render(scene: SphereCollection, camera: SceneCamera, width: int, height: int, samples: int = 1,
+           device: int = 0) -> np.ndarray:
+    """Headless render(scene, camera, w, h): rgba32f (h, w, 4) = (mean rgb, sample count)."""
+    out = np.empty((height, width, 4), dtype=np.float32)
+    _check(lib().rt_render(device, _ptr(scene.spheres), scene.count, C.byref(camera), width, height, samples, _ptr(out)))
+    return out
+
+
+def render_frames(scene: SphereCollection, cameras, width: int, height: int, device: int = 0) -> np.ndarray:
+    out = np.empty((len(cameras), height, width, 4), dtype=np.uint8)
+    arr = (SceneCamera * len(cameras))(*cameras)
+    _check(lib().rt_render_frames(device, _ptr(scene.spheres), scene.count, arr, len(cameras), width, height, _ptr(out)))
+    return out

@@ -1,0 +1,348 @@
+// rt_api.cu — the extern "C" boundary declared in include/rt_abi.h (single-device part).
+//
+// Mirrors the render-world side of the reference plugin (src/lib.rs:138-229, 326-422): the
+// renderer owns what the Bevy node owned — accumulation image, sphere storage buffer + count,
+// camera uniform — and `rt_init` / `rt_update` are the two dispatches of ComputeShaderNode::run.
+// There is no CPU fallback: without a usable CUDA device every entry returns RT_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/rt_abi.h"
+#include "rt_kernels.cuh"
+#include "rt_internal.h"
+
+namespace rti {
+
+static thread_local char g_error[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return code;
+}
+int fail_cuda(cudaError_t e, const char* what) {
+    int code = (e == cudaErrorMemoryAllocation) ? RT_ERR_OUT_OF_MEMORY
+             : (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? RT_ERR_NO_DEVICE
+             : RT_ERR_CUDA;
+    return fail(code, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+const char* last_error() { return g_error; }
+
+}  // namespace rti
+
+using rti::fail;
+using rti::fail_cuda;
+
+#define RT_CUDA(call)                                   \
+    do {                                                \
+        cudaError_t e_ = (call);                        \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call); \
+    } while (0)
+
+#define RT_CHECK_HANDLE(r)                                           \
+    do {                                                             \
+        if (!(r)) return fail(RT_ERR_INVALID_ARG, "null renderer");  \
+        RT_CUDA(cudaSetDevice((r)->device));                         \
+    } while (0)
+
+extern "C" {
+
+const char* rt_last_error(void) { return rti::last_error(); }
+const char* rt_version(void) { return "gpu-ray-tracing_b200 0.1 (sm_100a)"; }
+
+int rt_device_count(int* count) {
+    if (!count) return fail(RT_ERR_INVALID_ARG, "count is null");
+    *count = 0;
+    cudaError_t e = cudaGetDeviceCount(count);
+    if (e != cudaSuccess) {
+        *count = 0;
+        return fail_cuda(e, "cudaGetDeviceCount");
+    }
+    if (*count == 0) return fail(RT_ERR_NO_DEVICE, "no CUDA device");
+    return RT_OK;
+}
+
+int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_begin, uint32_t row_count,
+                     RtRenderer** out) {
+    if (!out) return fail(RT_ERR_INVALID_ARG, "out is null");
+    *out = nullptr;
+    if (width == 0 || height == 0 || row_count == 0) return fail(RT_ERR_INVALID_ARG, "empty image %ux%u rows %u", width, height, row_count);
+    if ((uint64_t)row_begin + row_count > height) return fail(RT_ERR_INVALID_ARG, "row window [%u,+%u) outside height %u", row_begin, row_count, height);
+    if (width > (1u << 20) || height > (1u << 20)) return fail(RT_ERR_INVALID_ARG, "image too large");
+    int n = 0;
+    int rc = rt_device_count(&n);
+    if (rc != RT_OK) return rc;
+    if (device < 0 || device >= n) return fail(RT_ERR_INVALID_ARG, "device %d out of range (have %d)", device, n);
+    RT_CUDA(cudaSetDevice(device));
+    RT_CUDA(rtk::configure_kernels());
+
+    RtRenderer* r = new (std::nothrow) RtRenderer();
+    if (!r) return fail(RT_ERR_OUT_OF_MEMORY, "host allocation failed");
+    r->device = device;
+    r->width = width; r->height = height; r->row_begin = row_begin; r->row_count = row_count;
+    r->n_texels = (uint64_t)width * row_count;
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking);
+    r->sm_count = prop.multiProcessorCount;
+    if (e == cudaSuccess) e = cudaMalloc(&r->accum, r->n_texels * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc(&r->rgba8, r->n_texels * sizeof(uchar4));
+    if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&r->counters, 2 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
+    if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->accum, 0, r->n_texels * sizeof(float4), r->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->counters, 0, 2 * sizeof(unsigned long long), r->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
+    if (e != cudaSuccess) {
+        int code = fail_cuda(e, "rt_create");
+        rt_destroy(r);
+        return code;
+    }
+    *out = r;
+    return RT_OK;
+}
+
+int rt_create(int device, uint32_t width, uint32_t height, RtRenderer** out) {
+    return rt_create_window(device, width, height, 0, height, out);
+}
+
+int rt_destroy(RtRenderer* r) {
+    if (!r) return RT_OK;
+    cudaSetDevice(r->device);
+    if (r->stream) cudaStreamSynchronize(r->stream);
+    cudaFree(r->accum);
+    cudaFree(r->rgba8);
+    cudaFree(r->spheres);
+    cudaFree(r->geom);
+    cudaFree(r->tile_counter);
+    cudaFree(r->counters);
+    if (r->ev_begin) cudaEventDestroy(r->ev_begin);
+    if (r->ev_end) cudaEventDestroy(r->ev_end);
+    if (r->stream) cudaStreamDestroy(r->stream);
+    delete r;
+    return RT_OK;
+}
+
+int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, uint32_t count) {
+    RT_CHECK_HANDLE(r);
+    if (count > buffer_len) return fail(RT_ERR_INVALID_ARG, "count %u exceeds buffer_len %u", count, buffer_len);
+    if (buffer_len > 0 && !spheres) return fail(RT_ERR_INVALID_ARG, "spheres is null");
+    if (count > (1u << 26)) return fail(RT_ERR_INVALID_ARG, "too many spheres");
+    // storage buffers cannot be empty in wgpu either; keep one slot so pointers stay valid
+    const uint32_t cap_needed = buffer_len > 0 ? buffer_len : 1;
+    const uint32_t pad_needed = (count + 7) / 8 * 8 + 8;
+    if (cap_needed > r->sphere_capacity || pad_needed > r->geom_capacity) {
+        RT_CUDA(cudaStreamSynchronize(r->stream));
+        cudaFree(r->spheres); r->spheres = nullptr; r->sphere_capacity = 0;
+        cudaFree(r->geom); r->geom = nullptr; r->geom_capacity = 0;
+        RT_CUDA(cudaMalloc(&r->spheres, (size_t)cap_needed * sizeof(GpuSphere)));
+        r->sphere_capacity = cap_needed;
+        RT_CUDA(cudaMalloc(&r->geom, (size_t)pad_needed * sizeof(float4)));
+        r->geom_capacity = pad_needed;
+    }
+    if (buffer_len > 0)
+        RT_CUDA(cudaMemcpyAsync(r->spheres, spheres, (size_t)buffer_len * sizeof(GpuSphere), cudaMemcpyHostToDevice, r->stream));
+    r->n_spheres = count;
+    RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
+    r->launches += count ? 1 : 0;
+    // the source is borrowed for the call only (pageable memory: the copy above has been staged,
+    // but make the contract unconditional)
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    r->has_scene = true;
+    return RT_OK;
+}
+
+int rt_init(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(cudaMemsetAsync(r->accum, 0, r->n_texels * sizeof(float4), r->stream));
+    return RT_OK;
+}
+
+static int update_one(RtRenderer* r, const SceneCamera* camera) {
+    rtk::UpdateParams p;
+    memcpy(&p.cam, camera, sizeof(SceneCamera));
+    p.accum = r->accum;
+    p.geom = r->geom;
+    p.spheres = r->spheres;
+    p.n_spheres = r->n_spheres;
+    p.width = r->width; p.height = r->height;
+    p.row_begin = r->row_begin; p.row_count = r->row_count;
+    p.tiles_x = (r->width + rtk::kWarpTileW - 1) / rtk::kWarpTileW;
+    p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
+    p.tile_counter = r->tile_counter;
+    p.counters = r->counters;
+    RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
+int rt_update(RtRenderer* r, const SceneCamera* camera) {
+    RT_CHECK_HANDLE(r);
+    if (!camera) return fail(RT_ERR_INVALID_ARG, "camera is null");
+    if (!r->has_scene) return fail(RT_ERR_NO_SCENE, "rt_update before rt_set_scene");
+    return update_one(r, camera);
+}
+
+int rt_update_n(RtRenderer* r, const SceneCamera* cameras, uint32_t n) {
+    RT_CHECK_HANDLE(r);
+    if (n > 0 && !cameras) return fail(RT_ERR_INVALID_ARG, "cameras is null");
+    if (!r->has_scene) return fail(RT_ERR_NO_SCENE, "rt_update_n before rt_set_scene");
+    for (uint32_t i = 0; i < n; ++i) {
+        int rc = update_one(r, cameras + i);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+int rt_synchronize(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    return RT_OK;
+}
+
+int rt_read_accum(RtRenderer* r, float* host) {
+    RT_CHECK_HANDLE(r);
+    if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
+    RT_CUDA(cudaMemcpyAsync(host, r->accum, r->n_texels * sizeof(float4), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    return RT_OK;
+}
+
+int rt_write_accum(RtRenderer* r, const float* host) {
+    RT_CHECK_HANDLE(r);
+    if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
+    RT_CUDA(cudaMemcpyAsync(r->accum, host, r->n_texels * sizeof(float4), cudaMemcpyHostToDevice, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    return RT_OK;
+}
+
+int rt_quantize(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(rtk::launch_quantize(r->accum, r->rgba8, r->n_texels, r->stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
+int rt_read_rgba8(RtRenderer* r, uint8_t* host) {
+    RT_CHECK_HANDLE(r);
+    if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
+    int rc = rt_quantize(r);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaMemcpyAsync(host, r->rgba8, r->n_texels * sizeof(uchar4), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    return RT_OK;
+}
+
+static int read_counter(RtRenderer* r, int which, uint64_t* out) {
+    RT_CHECK_HANDLE(r);
+    if (!out) return fail(RT_ERR_INVALID_ARG, "out is null");
+    unsigned long long v = 0;
+    RT_CUDA(cudaMemcpyAsync(&v, r->counters + which, sizeof(v), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    *out = v;
+    return RT_OK;
+}
+int rt_rays_traced(RtRenderer* r, uint64_t* rays) { return read_counter(r, 0, rays); }
+int rt_exact_tests(RtRenderer* r, uint64_t* tests) { return read_counter(r, 1, tests); }
+int rt_reset_counters(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(cudaMemsetAsync(r->counters, 0, 2 * sizeof(unsigned long long), r->stream));
+    return RT_OK;
+}
+
+int rt_timer_begin(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(cudaEventRecord(r->ev_begin, r->stream));
+    return RT_OK;
+}
+int rt_timer_end(RtRenderer* r, float* elapsed_ms) {
+    RT_CHECK_HANDLE(r);
+    if (!elapsed_ms) return fail(RT_ERR_INVALID_ARG, "elapsed_ms is null");
+    RT_CUDA(cudaEventRecord(r->ev_end, r->stream));
+    RT_CUDA(cudaEventSynchronize(r->ev_end));
+    RT_CUDA(cudaEventElapsedTime(elapsed_ms, r->ev_begin, r->ev_end));
+    return RT_OK;
+}
+int rt_kernel_launches(RtRenderer* r, uint64_t* launches) {
+    if (!r || !launches) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *launches = r->launches;
+    return RT_OK;
+}
+
+int rt_accum_device_ptr(RtRenderer* r, void** ptr) {
+    if (!r || !ptr) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *ptr = r->accum;
+    return RT_OK;
+}
+int rt_rgba8_device_ptr(RtRenderer* r, void** ptr) {
+    if (!r || !ptr) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *ptr = r->rgba8;
+    return RT_OK;
+}
+int rt_stream(RtRenderer* r, void** s) {
+    if (!r || !s) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *s = (void*)r->stream;
+    return RT_OK;
+}
+int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height, uint32_t* row_begin, uint32_t* row_count) {
+    if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    if (width) *width = r->width;
+    if (height) *height = r->height;
+    if (row_begin) *row_begin = r->row_begin;
+    if (row_count) *row_count = r->row_count;
+    return RT_OK;
+}
+int rt_set_kernel_variant(RtRenderer* r, int variant) {
+    if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    if (variant < 0 || variant > 3) return fail(RT_ERR_INVALID_ARG, "variant %d not in 0..3", variant);
+    r->variant = variant;
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Headless one-shot entries
+// ---------------------------------------------------------------------------------------------
+int rt_render(int device, const GpuSphere* spheres, uint32_t count, const SceneCamera* camera, uint32_t width,
+              uint32_t height, uint32_t samples, float* out_rgba32f) {
+    if (!camera || !out_rgba32f) return fail(RT_ERR_INVALID_ARG, "null argument");
+    RtRenderer* r = nullptr;
+    int rc = rt_create(device, width, height, &r);
+    if (rc != RT_OK) return rc;
+    rc = rt_set_scene(r, spheres, count, count);
+    if (rc == RT_OK) rc = rt_init(r);
+    for (uint32_t i = 0; rc == RT_OK && i < samples; ++i) {
+        SceneCamera cam = *camera;
+        if (i > 0) cam.camera_has_moved = 0.0f;   // the reset flag holds for the first frame only (camera.rs:245-252)
+        rc = rt_update(r, &cam);
+    }
+    if (rc == RT_OK) rc = rt_read_accum(r, out_rgba32f);
+    rt_destroy(r);
+    return rc;
+}
+
+int rt_render_frames(int device, const GpuSphere* spheres, uint32_t count, const SceneCamera* cameras,
+                     uint32_t n_frames, uint32_t width, uint32_t height, uint8_t* out_rgba8) {
+    if ((n_frames && !cameras) || !out_rgba8) return fail(RT_ERR_INVALID_ARG, "null argument");
+    RtRenderer* r = nullptr;
+    int rc = rt_create(device, width, height, &r);
+    if (rc != RT_OK) return rc;
+    rc = rt_set_scene(r, spheres, count, count);
+    const size_t frame_bytes = (size_t)width * height * 4;
+    for (uint32_t f = 0; rc == RT_OK && f < n_frames; ++f) {
+        rc = rt_init(r);
+        if (rc == RT_OK) rc = rt_update(r, cameras + f);
+        if (rc == RT_OK) rc = rt_read_rgba8(r, out_rgba8 + f * frame_bytes);
+    }
+    rt_destroy(r);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,237 @@
+// rt_core.cuh — per-ray arithmetic of the ray-trace pass, shared by every kernel variant.
+//
+// Follows /root/reference/assets/compute_shader.wgsl (cited per function).  All arithmetic is
+// IEEE-754 binary32 with ONE rounding per WGSL operator: this translation unit must be built
+// with -fmad=false (nvcc) so that a*b+c is never contracted; the only fused operations in the
+// product are the explicit fmaf() calls of the broad phase (rt_kernels.cu), which never decide
+// a result on their own.  Transcendentals come from include/rt_pinned_math.h.
+//
+// The functions are __host__ __device__ so that tests can run the very same code on the CPU
+// (tests/emu) when no GPU is present; the product never executes them on the host.
+#pragma once
+
+#include <stdint.h>
+#include <math.h>
+
+#include "../../include/rt_abi.h"
+#include "../../include/rt_pinned_math.h"
+
+#if defined(__CUDACC__)
+#define RT_DEV __host__ __device__ __forceinline__
+#else
+#define RT_DEV static inline
+#endif
+
+namespace rtc {
+
+struct f3 {
+    float x, y, z;
+};
+RT_DEV f3 mk(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+RT_DEV f3 mk(const RtVec3& v) { return mk(v.x, v.y, v.z); }
+RT_DEV f3 add(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+RT_DEV f3 sub(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+RT_DEV f3 mul(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+RT_DEV f3 scale(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+RT_DEV f3 divs(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+RT_DEV f3 neg(f3 a) { return mk(-a.x, -a.y, -a.z); }
+RT_DEV float dot(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+RT_DEV f3 normalize(f3 a) { return divs(a, sqrtf(dot(a, a))); }
+
+// WGSL u32(f32): truncate, saturate, NaN -> 0
+RT_DEV uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float2uint_rz(f);
+#else
+    if (!(f > 0.0f)) return 0u;
+    if (f >= 4294967296.0f) return 0xFFFFFFFFu;
+    return (uint32_t)f;
+#endif
+}
+
+// compute_shader.wgsl:50-59 (naga precedence: shift before xor)
+RT_DEV uint32_t hash(uint32_t s) {
+    s ^= 2747636419u;
+    s *= 2654435769u;
+    s ^= s >> 16;
+    s *= 2654435769u;
+    s ^= s >> 16;
+    s *= 2654435769u;
+    return s;
+}
+// compute_shader.wgsl:61-63 — the f32 literal 4294967295.0 is 2^32
+RT_DEV float random_float(uint32_t v) { return (float)hash(v) * 2.3283064365386963e-10f; }
+
+// compute_shader.wgsl:234-243
+RT_DEV f3 random_unit_vector(uint32_t seed) {
+    float z = 2.0f * random_float(seed) - 1.0f;
+    float a = random_float(seed + 1u) * 6.283185307f;
+    float r = sqrtf(1.0f - z * z);
+    float sn, cs;
+    rt_sincos(a, &sn, &cs);
+    return mk(r * cs, r * sn, z);
+}
+
+struct Ray {
+    f3 o, d;
+};
+
+// compute_shader.wgsl:305-331 (get_ray, sample_square, defocus_disk_sample)
+RT_DEV Ray get_ray(const SceneCamera& cam, int x, int y, uint32_t sample_index, uint32_t seed_bits) {
+    uint32_t seed = hash(hash((uint32_t)x * 73u) ^ hash((uint32_t)y * 51u) ^ (sample_index * 25u + seed_bits));
+    float ox = random_float(seed) - 0.5f;
+    float oy = random_float(seed * seed) - 0.5f;
+    float sx = ((float)x + 0.5f) + ox;
+    float sy = ((float)y + 0.5f) + oy;
+    f3 pc = add(add(mk(cam.viewport_upper_left), mk(cam.pixel_delta_u.x * sx, cam.pixel_delta_u.y * sx, cam.pixel_delta_u.z * sx)),
+                mk(cam.pixel_delta_v.x * sy, cam.pixel_delta_v.y * sy, cam.pixel_delta_v.z * sy));
+    Ray r;
+    if (cam.defocus_angle > 0.0f) {
+        float angle = (2.0f * 3.1415926f) * random_float(seed + 1u);
+        float sn, cs;
+        rt_sincos(angle, &sn, &cs);
+        float len = sqrtf(cs * cs + sn * sn);
+        float px = cs / len, py = sn / len;
+        r.o = add(add(mk(cam.center), scale(px, mk(cam.defocus_disk_u))), scale(py, mk(cam.defocus_disk_v)));
+    } else {
+        r.o = mk(cam.center);
+    }
+    r.d = sub(pc, r.o);
+    return r;
+}
+
+// The quadratic of sphere_hit (compute_shader.wgsl:183-201) up to the accepted root.
+// `a` = dot(d, d) is loop invariant and passed in.  Returns true and the root when the sphere is
+// hit inside (tmin, tmax) with the reference's <= / <= rejection.
+RT_DEV bool sphere_root(f3 o, f3 d, float a, f3 center, float radius, float tmin, float tmax, float* root_out) {
+    f3 oc = sub(center, o);
+    float h = dot(oc, d);
+    float c = dot(oc, oc) - radius * radius;
+    float disc = h * h - a * c;
+    if (disc < 0.0f) return false;
+    float sq = sqrtf(disc);
+    float root = (h - sq) / a;
+    if (root <= tmin || tmax <= root) {
+        root = (h + sq) / a;
+        if (root <= tmin || tmax <= root) return false;
+    }
+    *root_out = root;
+    return true;
+}
+
+// Sky gradient of ray_color (compute_shader.wgsl:293-296) times the accumulated factor.
+RT_DEV f3 sky_times(f3 factor, f3 dir) {
+    f3 u = normalize(dir);
+    float a = 0.5f * (u.y + 1.0f);
+    float ia = 1.0f - a;
+    f3 sky = mk(ia * 1.0f + a * 0.5f, ia * 1.0f + a * 0.7f, ia * 1.0f + a * 1.0f);
+    return mul(factor, sky);
+}
+
+// Hit record construction (compute_shader.wgsl:204-218, 158-162) followed by the material
+// dispatch of ray_color (compute_shader.wgsl:268-286).  On return *ray is the scattered ray and
+// *factor has been multiplied by the attenuation.  Returns false when the sample is absorbed
+// (ray_color returns black, compute_shader.wgsl:274,278,282).
+RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
+    f3 o = ray->o, d = ray->d;
+    f3 center = mk(sp.position);
+    f3 p = add(o, scale(t, d));
+    f3 outward = divs(sub(p, center), sp.radius);
+    bool front = dot(d, outward) < 0.0f;
+    f3 n = front ? outward : neg(outward);
+    float w = sp.color[3];
+    f3 albedo = mk(sp.color[0], sp.color[1], sp.color[2]);
+    Ray out;
+    out.o = p;
+    if (w < -1.0f) {
+        // lambertian_scatter, compute_shader.wgsl:84-93
+        f3 dir = add(n, random_unit_vector(bounce_seed));
+        if (dot(dir, dir) < 1e-6f) dir = n;
+        out.d = dir;
+        *factor = mul(*factor, albedo);
+        *ray = out;
+        return true;
+    } else if (w <= 1.0f) {
+        // metal_scatter, compute_shader.wgsl:95-100; reflect(e1,e2) = e1 - 2 dot(e2,e1) e2
+        f3 refl = sub(d, scale(2.0f * dot(n, d), n));
+        f3 reflected = add(normalize(refl), scale(w, random_unit_vector(bounce_seed)));
+        out.d = normalize(reflected);
+        *factor = mul(*factor, albedo);
+        *ray = out;
+        return dot(reflected, n) > 0.0f;
+    } else {
+        // dielectric_scatter + reflectance, compute_shader.wgsl:102-141
+        float ior = sp.color[0];
+        float ratio = front ? (1.0f / ior) : ior;
+        f3 ud = normalize(d);
+        float cos_theta = fminf(dot(neg(ud), n), 1.0f);
+        float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        bool cannot_refract = ratio * sin_theta > 1.0f;
+        float r0 = (1.0f - ratio) / (1.0f + ratio);
+        r0 = r0 * r0;
+        float refl_prob = r0 + (1.0f - r0) * rt_pow5(1.0f - cos_theta);
+        bool should_reflect = cannot_refract || refl_prob > random_float(bounce_seed);
+        f3 dir;
+        if (should_reflect) {
+            dir = sub(ud, scale(2.0f * dot(n, ud), n));
+        } else {
+            // WGSL refract(e1, e2, e3)
+            float dn = dot(n, ud);
+            float k = 1.0f - (ratio * ratio) * (1.0f - dn * dn);
+            if (k < 0.0f) {
+                dir = mk(0.0f, 0.0f, 0.0f);
+            } else {
+                dir = sub(scale(ratio, ud), scale(ratio * dn + sqrtf(k), n));
+            }
+        }
+        out.d = normalize(dir);
+        // attenuation = vec3(1.0): color_factor *= 1.0 is exact, skipped
+        *ray = out;
+        return true;
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Broad phase.  Conservative sign test of the discriminant with fused
+// arithmetic: 7 FFMA per (ray, sphere).  Shared by the kernels and the CPU emulation in tests/emu.
+// ---------------------------------------------------------------------------------------------
+#define RT_KAPPA 1.52587890625e-05 /* 2^-16 */
+
+struct BroadRay {
+    float ux, uy, uz;     // d / |d|
+    float h0;             // -dot(O, u)
+    float mox, moy, moz;  // -2 O
+    float thr;            // |O|^2 (1 - kappa)
+};
+
+RT_DEV BroadRay broad_arm(f3 o, f3 d, float a) {
+    BroadRay b;
+    float inv = 1.0f / sqrtf(a);
+    b.ux = d.x * inv; b.uy = d.y * inv; b.uz = d.z * inv;
+    b.h0 = -((o.x * b.ux + o.y * b.uy) + o.z * b.uz);
+    b.mox = -2.0f * o.x; b.moy = -2.0f * o.y; b.moz = -2.0f * o.z;
+    float oo = dot(o, o);
+    b.thr = fmaf(-(float)RT_KAPPA, oo, oo);
+    return b;
+}
+
+// g >= thr  <=>  candidate.  (sx, sy, sz, sk) is the per-sphere record of broad_record().
+RT_DEV float broad_g(float sx, float sy, float sz, float sk, float ux, float uy, float uz, float h0, float mox,
+                     float moy, float moz) {
+    float h = fmaf(sx, ux, fmaf(sy, uy, fmaf(sz, uz, h0)));
+    float c = fmaf(sx, mox, fmaf(sy, moy, fmaf(sz, moz, sk)));
+    return fmaf(h, h, -c);
+}
+
+// k = |C|^2 - r^2 - kappa (|C|^2 + r^2), evaluated in binary64 and rounded toward -infinity.
+RT_DEV float broad_record_k(const GpuSphere& s) {
+    const double cx = s.position.x, cy = s.position.y, cz = s.position.z, r = s.radius;
+    const double cc = cx * cx + cy * cy + cz * cz, rr = r * r;
+    const double k = cc - rr - RT_KAPPA * (cc + rr);
+    float f = (float)k;
+    if ((double)f > k) f = nextafterf(f, -INFINITY);
+    return f;
+}
+
+}  // namespace rtc

@@ -1,0 +1,34 @@
+// rt_internal.h — state behind the opaque handles of include/rt_abi.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rt_abi.h"
+
+struct RtRenderer {
+    int device = 0;
+    int sm_count = 0;
+    uint32_t width = 0, height = 0, row_begin = 0, row_count = 0;
+    uint64_t n_texels = 0;
+    cudaStream_t stream = nullptr;
+    float4* accum = nullptr;              // (mean.rgb, n) per texel of the window
+    uchar4* rgba8 = nullptr;
+    GpuSphere* spheres = nullptr;         // the caller's storage buffer, as uploaded
+    uint32_t sphere_capacity = 0;
+    float4* geom = nullptr;               // broad-phase records
+    uint32_t geom_capacity = 0;
+    uint32_t n_spheres = 0;
+    bool has_scene = false;
+    unsigned int* tile_counter = nullptr;
+    unsigned long long* counters = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    uint64_t launches = 0;
+    int variant = 0;
+};
+
+namespace rti {
+int fail(int code, const char* fmt, ...);
+int fail_cuda(cudaError_t e, const char* what);
+const char* last_error();
+}  // namespace rti

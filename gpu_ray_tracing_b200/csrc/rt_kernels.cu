@@ -1,0 +1,510 @@
+// rt_kernels.cu — CUDA kernels (sm_100a) for the `update` pass of compute_shader.wgsl:333-364.
+//
+// Build with -fmad=false: every a*b+c below is two roundings, exactly as the oracle evaluates it.
+// Fused multiply-adds appear only as explicit fmaf() in the BROAD PHASE, whose result is never
+// used for anything but "does this (ray, sphere) pair need the exact quadratic".
+//
+// Kernel structure:
+//   broad phase  — per (ray, sphere): 7 FFMA + 1 FSETP.  With unit direction u = d/|d|,
+//                  disc/|d|^2 = (C.u - O.u)^2 - (C.(-2O) + (|C|^2 - r^2)) - |O|^2, so with the
+//                  per-sphere float4 (C, k = |C|^2 - r^2 - slack) broadcast from shared memory and
+//                  8 per-ray registers (u, -O.u, -2O, |O|^2 - slack) the sign test is two 3-FFMA
+//                  dot chains, one FFMA and one compare.  The slack makes it conservative: it can
+//                  pass a sphere the exact test rejects, never the reverse.
+//   narrow phase — for the rare candidates only, the reference's quadratic verbatim
+//                  (rtc::sphere_root), in sphere-index order with the shrinking t_max of
+//                  sphere_list_hit (compute_shader.wgsl:164-180).  Results are therefore
+//                  bit-identical to evaluating every sphere exactly.
+#include "rt_kernels.cuh"
+#include "rt_core.cuh"
+
+namespace rtk {
+
+using rtc::f3;
+
+namespace {
+
+constexpr float kTMin = 0.001f;    // compute_shader.wgsl:266
+constexpr float kTMax = 3.4e35f;
+constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kUnroll = 4;         // spheres per broad-phase iteration
+constexpr int kGeomPad = 8;        // geometry arrays are padded to a multiple of this
+
+// Per-thread state of kPix rays.  Every index is a compile-time constant after unrolling, so the
+// arrays live in registers.
+struct Lanes {
+    float dx[kPix], dy[kPix], dz[kPix];     // ray direction, as the reference holds it
+    float mox[kPix], moy[kPix], moz[kPix];  // -2 * ray origin (exact; origin = -0.5 * this)
+    float a[kPix];                          // dot(d, d) with the reference's rounding
+    float ux[kPix], uy[kPix], uz[kPix];     // broad phase: unit direction
+    float h0[kPix];                         // broad phase: -dot(O, u)
+    float thr[kPix];                        // broad phase: |O|^2 (1 - kappa); +inf for idle rays
+    float best_t[kPix];
+    int best_i[kPix];
+    bool alive[kPix];
+};
+
+__device__ __forceinline__ float broad_g(const float4 sp, const Lanes& L, int p) {
+    return rtc::broad_g(sp.x, sp.y, sp.z, sp.w, L.ux[p], L.uy[p], L.uz[p], L.h0[p], L.mox[p], L.moy[p], L.moz[p]);
+}
+
+__device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
+    L.dx[p] = d.x; L.dy[p] = d.y; L.dz[p] = d.z;
+    const float a = rtc::dot(d, d);
+    L.a[p] = a;
+    const rtc::BroadRay b = rtc::broad_arm(o, d, a);
+    L.mox[p] = b.mox; L.moy[p] = b.moy; L.moz[p] = b.moz;
+    L.ux[p] = b.ux; L.uy[p] = b.uy; L.uz[p] = b.uz;
+    L.h0[p] = b.h0;
+    L.thr[p] = b.thr;
+    L.best_t[p] = kTMax;
+    L.best_i[p] = -1;
+    L.alive[p] = true;
+}
+
+__device__ __forceinline__ void idle_ray(Lanes& L, int p) {
+    L.dx[p] = L.dy[p] = L.dz[p] = 0.0f;
+    L.mox[p] = L.moy[p] = L.moz[p] = 0.0f;
+    L.a[p] = 1.0f;
+    L.ux[p] = L.uy[p] = L.uz[p] = 0.0f;
+    L.h0[p] = 0.0f;
+    L.thr[p] = __int_as_float(0x7f800000);
+    L.best_t[p] = kTMax;
+    L.best_i[p] = -1;
+    L.alive[p] = false;
+}
+
+__device__ __forceinline__ f3 origin_of(const Lanes& L, int p) {
+    return rtc::mk(-0.5f * L.mox[p], -0.5f * L.moy[p], -0.5f * L.moz[p]);
+}
+
+// Narrow phase over `count` consecutive spheres starting at shared-memory slot `slot`
+// (global index `index0`): the reference's sphere_hit root for every candidate ray.
+__device__ __forceinline__ void narrow_phase(const float4* __restrict__ s_geom, int slot, int count, int index0,
+                                          const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
+                                          uint32_t& exact_tests) {
+#pragma unroll 1
+    for (int u = 0; u < count; ++u) {
+        const int idx = index0 + u;
+        if ((uint32_t)idx >= n_spheres) break;   // padding
+        const float4 sp = s_geom[slot + u];
+        const float radius = __ldg(&spheres[idx].radius);
+        const f3 center = rtc::mk(sp.x, sp.y, sp.z);
+#pragma unroll
+        for (int p = 0; p < kPix; ++p) {
+            if (L.alive[p] && !(broad_g(sp, L, p) < L.thr[p])) {
+                ++exact_tests;
+                float root;
+                if (rtc::sphere_root(origin_of(L, p), rtc::mk(L.dx[p], L.dy[p], L.dz[p]), L.a[p], center, radius,
+                                     kTMin, L.best_t[p], &root)) {
+                    L.best_t[p] = root;
+                    L.best_i[p] = idx;
+                }
+            }
+        }
+    }
+}
+
+// Broad phase over `count` (multiple of kUnroll) spheres resident at s_geom[0..count).
+__device__ __forceinline__ void scan_spheres(const float4* __restrict__ s_geom, int count, int index0,
+                                             const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
+                                             uint32_t& exact_tests) {
+#pragma unroll 1
+    for (int s = 0; s < count; s += kUnroll) {
+        float4 sp[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) sp[u] = s_geom[s + u];
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+#pragma unroll
+            for (int p = 0; p < kPix; ++p) any |= !(broad_g(sp[u], L, p) < L.thr[p]);
+        }
+        if (any) narrow_phase(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
+    }
+}
+
+__device__ __forceinline__ GpuSphere load_sphere(const GpuSphere* __restrict__ spheres, int idx) {
+    const float4* q = reinterpret_cast<const float4*>(spheres + idx);
+    float4 g = __ldg(q), m = __ldg(q + 1);
+    GpuSphere s;
+    s.position.x = g.x; s.position.y = g.y; s.position.z = g.z; s.radius = g.w;
+    s.color[0] = m.x; s.color[1] = m.y; s.color[2] = m.z; s.color[3] = m.w;
+    return s;
+}
+
+// Per-pixel bookkeeping of `update` around the traversal.
+struct PixelJob {
+    f3 factor[kPix];
+    uint32_t bseed[kPix];   // ray_color's `seed` argument (compute_shader.wgsl:355)
+    uint32_t n[kPix];       // samples_until_now after the reset rule
+    bool sampling[kPix];    // n < samples_per_pixel and inside the image
+    bool black[kPix];       // sample absorbed
+    bool inb[kPix];
+};
+
+}  // namespace
+
+namespace {
+
+// Load the texels of one warp tile, apply the reset / sample-count rule of `update`
+// (compute_shader.wgsl:339-353) and arm the primary rays (get_ray, :305-325).
+__device__ __forceinline__ void begin_tile(const UpdateParams& P, uint32_t tile, int lane, uint32_t seed_bits,
+                                           uint32_t spp, bool reset, Lanes& L, PixelJob& J, int& row, int (&px)[kPix]) {
+    const uint32_t tx = tile % P.tiles_x, ty = tile / P.tiles_x;
+    row = (int)(ty * kWarpTileH) + (lane >> 3);
+    const int y_abs = (int)P.row_begin + row;
+#pragma unroll
+    for (int p = 0; p < kPix; ++p) {
+        px[p] = (int)(tx * kWarpTileW) + (lane & 7) + 8 * p;
+        J.inb[p] = (uint32_t)px[p] < P.width && (uint32_t)row < P.row_count;
+        J.black[p] = false;
+        J.factor[p] = rtc::mk(1.0f, 1.0f, 1.0f);
+        uint32_t n = 0;
+        if (J.inb[p] && !reset) n = rtc::f2u(P.accum[(size_t)row * P.width + px[p]].w);
+        J.n[p] = n;
+        J.sampling[p] = J.inb[p] && n < spp;
+        if (J.sampling[p]) {
+            const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
+            rtc::Ray r = rtc::get_ray(P.cam, px[p], y_abs, seed, seed_bits);
+            J.bseed[p] = seed + 1u;
+            arm_ray(L, p, r.o, r.d);
+        } else {
+            J.bseed[p] = 0u;
+            idle_ray(L, p);
+        }
+    }
+}
+
+// After a traversal: miss -> the ray leaves for the sky; hit -> scatter (compute_shader.wgsl:267-290).
+__device__ __forceinline__ void after_traversal(const UpdateParams& P, uint32_t bounce, Lanes& L, PixelJob& J) {
+#pragma unroll
+    for (int p = 0; p < kPix; ++p) {
+        if (!L.alive[p]) continue;
+        if (L.best_i[p] < 0) {
+            // keep direction for the sky colour, stop tracing
+            L.alive[p] = false;
+            L.thr[p] = __int_as_float(0x7f800000);
+            continue;
+        }
+        const GpuSphere sp = load_sphere(P.spheres, L.best_i[p]);
+        rtc::Ray r;
+        r.o = origin_of(L, p);
+        r.d = rtc::mk(L.dx[p], L.dy[p], L.dz[p]);
+        const uint32_t s = rtc::hash(J.bseed[p] + bounce * 1000u);   // compute_shader.wgsl:268
+        const bool ok = rtc::scatter(&r, &J.factor[p], L.best_t[p], sp, s);
+        if (!ok) {
+            J.black[p] = true;
+            L.alive[p] = false;
+            L.thr[p] = __int_as_float(0x7f800000);
+            L.dx[p] = r.d.x; L.dy[p] = r.d.y; L.dz[p] = r.d.z;
+        } else {
+            arm_ray(L, p, r.o, r.d);
+        }
+    }
+}
+
+// Running mean and texel store (compute_shader.wgsl:356-363).
+__device__ __forceinline__ void end_tile(const UpdateParams& P, const Lanes& L, const PixelJob& J, int row,
+                                         const int (&px)[kPix], bool reset) {
+#pragma unroll
+    for (int p = 0; p < kPix; ++p) {
+        if (!J.inb[p]) continue;
+        float4* texel = &P.accum[(size_t)row * P.width + px[p]];
+        f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
+        if (!reset) {
+            float4 t = *texel;
+            mean = rtc::mk(t.x, t.y, t.z);
+        }
+        uint32_t n = J.n[p];
+        if (J.sampling[p]) {
+            f3 color = J.black[p] ? rtc::mk(0.0f, 0.0f, 0.0f)
+                                  : rtc::sky_times(J.factor[p], rtc::mk(L.dx[p], L.dy[p], L.dz[p]));
+            float denom = (float)(n + 1u);
+            mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), denom));
+            n += 1u;
+        }
+        *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
+    }
+}
+
+__device__ __forceinline__ void flush_counters(const UpdateParams& P, uint32_t rays, uint32_t exact_tests, int lane) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        rays += __shfl_xor_sync(kFull, rays, o);
+        exact_tests += __shfl_xor_sync(kFull, exact_tests, o);
+    }
+    if (lane == 0) {
+        atomicAdd(&P.counters[0], (unsigned long long)rays);
+        atomicAdd(&P.counters[1], (unsigned long long)exact_tests);
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// Variant 2: scene resident in shared memory, persistent warps pulling 32x4 tiles.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_geom[];
+    const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
+    for (int i = threadIdx.x; i < n_pad; i += kBlockThreads) s_geom[i] = __ldg(&P.geom[i]);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    uint32_t rays = 0, exact_tests = 0;
+
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+        tile = __shfl_sync(kFull, tile, 0);
+        if (tile >= P.n_tiles) break;
+
+        Lanes L;
+        PixelJob J;
+        int row, px[kPix];
+        begin_tile(P, tile, lane, seed_bits, spp, reset, L, J, row, px);
+
+        for (uint32_t bounce = 0; bounce < max_depth; ++bounce) {
+            bool mine = false;
+#pragma unroll
+            for (int p = 0; p < kPix; ++p) {
+                mine |= L.alive[p];
+                rays += L.alive[p] ? 1u : 0u;
+            }
+            if (!__any_sync(kFull, mine)) break;
+            scan_spheres(s_geom, n_pad, 0, P.spheres, P.n_spheres, L, exact_tests);
+            after_traversal(P, bounce, L, J);
+        }
+        end_tile(P, L, J, row, px, reset);
+    }
+    flush_counters(P, rays, exact_tests, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Variant 1: baseline.  The shader as written: 8x8 workgroups, one invocation per pixel, every
+// sphere read from the storage buffer and put through the full quadratic (src/lib.rs:416,
+// compute_shader.wgsl:164-221).  Kept as the A/B arm and as an independent second GPU path.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) update_baseline_kernel(const __grid_constant__ UpdateParams P) {
+    const int x = blockIdx.x * 8 + (threadIdx.x & 7);
+    const int row = blockIdx.y * 8 + (threadIdx.x >> 3);
+    uint32_t rays = 0;
+    if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+        const int y_abs = (int)P.row_begin + row;
+        const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+        const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+        const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+        float4* texel = &P.accum[(size_t)row * P.width + x];
+        float4 t = *texel;
+        f3 mean = rtc::mk(t.x, t.y, t.z);
+        uint32_t n = rtc::f2u(t.w);
+        if (P.cam.camera_has_moved > 0.5f) {
+            mean = rtc::mk(0.0f, 0.0f, 0.0f);
+            n = 0u;
+        }
+        if (n < spp) {
+            const uint32_t seed = 1u + n + seed_bits;
+            rtc::Ray r = rtc::get_ray(P.cam, x, y_abs, seed, seed_bits);
+            f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
+            bool black = false;
+            for (uint32_t i = 0; i < max_depth; ++i) {
+                ++rays;
+                const float a = rtc::dot(r.d, r.d);
+                float closest = kTMax;
+                int best = -1;
+                for (uint32_t s = 0; s < P.n_spheres; ++s) {
+                    const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + s));
+                    float root;
+                    if (rtc::sphere_root(r.o, r.d, a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, closest, &root)) {
+                        closest = root;
+                        best = (int)s;
+                    }
+                }
+                if (best < 0) break;
+                const GpuSphere sp = load_sphere(P.spheres, best);
+                if (!rtc::scatter(&r, &factor, closest, sp, rtc::hash(seed + 1u + i * 1000u))) {
+                    black = true;
+                    break;
+                }
+            }
+            f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times(factor, r.d);
+            mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+            n += 1u;
+        }
+        *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
+    }
+    // one atomic per warp
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(kFull, rays, o);
+    if (lane == 0 && rays) atomicAdd(&P.counters[0], (unsigned long long)rays);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Scene preparation: per-sphere broad-phase record (C, |C|^2 - r^2 - kappa (|C|^2 + r^2)),
+// evaluated in binary64 and rounded toward -inf so the slack can only grow.  Entries past n up
+// to the padded length can never be candidates.
+// ---------------------------------------------------------------------------------------------
+__global__ void prep_geometry_kernel(const GpuSphere* __restrict__ spheres, float4* __restrict__ geom, uint32_t n,
+                                     uint32_t n_pad) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    if (i >= n) {
+        geom[i] = make_float4(0.0f, 0.0f, 0.0f, 3.0e38f);
+        return;
+    }
+    const GpuSphere s = spheres[i];
+    geom[i] = make_float4(s.position.x, s.position.y, s.position.z, rtc::broad_record_k(s));
+}
+
+// Linear RGBA8 of the running mean: q(x) = floor(clamp(x, 0, 1) * 255 + 0.5), alpha 255.
+__device__ __forceinline__ unsigned quant1(float v) {
+    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+    float q = floorf(v * 255.0f + 0.5f);
+    return (q == q) ? (unsigned)q : 0u;
+}
+__device__ __forceinline__ unsigned quant_texel(float4 t) {
+    return quant1(t.x) | (quant1(t.y) << 8) | (quant1(t.z) << 16) | 0xFF000000u;
+}
+__global__ void quantize_kernel(const float4* __restrict__ accum, uint32_t* __restrict__ rgba8, uint64_t n_texels) {
+    // four texels per thread: 64 B in, one 16 B store out
+    const uint64_t i4 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i4 + 3 < n_texels) {
+        uint4 o;
+        o.x = quant_texel(accum[i4 + 0]);
+        o.y = quant_texel(accum[i4 + 1]);
+        o.z = quant_texel(accum[i4 + 2]);
+        o.w = quant_texel(accum[i4 + 3]);
+        *reinterpret_cast<uint4*>(rgba8 + i4) = o;
+    } else {
+        for (uint64_t i = i4; i < n_texels; ++i) rgba8[i] = quant_texel(accum[i]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Variant 3: scenes larger than shared memory.  A CTA owns 8 consecutive warp tiles (1024 pixels);
+// the broad-phase records stream through a double-buffered 2 x 32 KB stage, one barrier per chunk.
+// Per-ray nearest-hit state stays in registers across chunks, so index order (and with it the
+// reference's tie rule) is preserved.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_stage[];   // [2][kChunkSpheres]
+    __shared__ uint32_t s_block_tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
+    const int n_chunks = (n_pad + kChunkSpheres - 1) / kChunkSpheres;
+    const uint32_t n_block_tiles = (P.n_tiles + 7u) / 8u;
+    uint32_t rays = 0, exact_tests = 0;
+
+    for (;;) {
+        __syncthreads();   // everyone is done with s_block_tile and the stages of the previous tile
+        if (threadIdx.x == 0) s_block_tile = atomicAdd(P.tile_counter, 1u);
+        __syncthreads();
+        const uint32_t bt = s_block_tile;
+        if (bt >= n_block_tiles) break;
+
+        Lanes L;
+        PixelJob J;
+        int row, px[kPix];
+        begin_tile(P, bt * 8u + (uint32_t)warp, lane, seed_bits, spp, reset, L, J, row, px);
+
+        for (uint32_t bounce = 0; bounce < max_depth; ++bounce) {
+            bool mine = false;
+#pragma unroll
+            for (int p = 0; p < kPix; ++p) {
+                mine |= L.alive[p];
+                rays += L.alive[p] ? 1u : 0u;
+            }
+            const bool warp_alive = __any_sync(kFull, mine);
+            if (!__syncthreads_or(mine ? 1 : 0)) break;   // also fences the stages against the previous bounce
+
+            // prologue: chunk 0 -> stage 0
+            {
+                const int cnt = min(kChunkSpheres, n_pad);
+                for (int i = threadIdx.x; i < cnt; i += kBlockThreads) s_stage[i] = __ldg(&P.geom[i]);
+            }
+            __syncthreads();
+            for (int c = 0; c < n_chunks; ++c) {
+                const int base = c * kChunkSpheres;
+                const int cnt = min(kChunkSpheres, n_pad - base);
+                if (c + 1 < n_chunks) {
+                    const int nbase = base + kChunkSpheres;
+                    const int ncnt = min(kChunkSpheres, n_pad - nbase);
+                    float4* dst = s_stage + ((c + 1) & 1) * kChunkSpheres;
+                    for (int i = threadIdx.x; i < ncnt; i += kBlockThreads) dst[i] = __ldg(&P.geom[nbase + i]);
+                }
+                if (warp_alive)
+                    scan_spheres(s_stage + (c & 1) * kChunkSpheres, cnt, base, P.spheres, P.n_spheres, L, exact_tests);
+                __syncthreads();
+            }
+            after_traversal(P, bounce, L, J);
+        }
+        end_tile(P, L, J, row, px, reset);
+    }
+    flush_counters(P, rays, exact_tests, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Launchers
+// ---------------------------------------------------------------------------------------------
+cudaError_t configure_kernels() {
+    cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(kResidentMaxSpheres * sizeof(float4)));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(2 * kChunkSpheres * sizeof(float4)));
+}
+
+cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream) {
+    if (variant == 0) variant = (p.n_spheres <= kResidentMaxSpheres) ? 2 : 3;
+    if (variant == 2 && p.n_spheres > kResidentMaxSpheres) variant = 3;
+    if (variant == 1) {
+        dim3 grid((p.width + 7) / 8, (p.row_count + 7) / 8);
+        update_baseline_kernel<<<grid, 64, 0, stream>>>(p);
+        return cudaGetLastError();
+    }
+    cudaError_t e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
+    if (variant == 2) {
+        const uint32_t warps_needed = p.n_tiles;
+        uint32_t blocks = (warps_needed + 7) / 8;
+        const uint32_t resident = (uint32_t)sm_count * 2u;
+        if (blocks > resident) blocks = resident;
+        if (blocks == 0) blocks = 1;
+        update_resident_kernel<<<blocks, kBlockThreads, n_pad * sizeof(float4), stream>>>(p);
+    } else {
+        uint32_t blocks = (p.n_tiles + 7) / 8;
+        const uint32_t resident = (uint32_t)sm_count * 2u;
+        if (blocks > resident) blocks = resident;
+        if (blocks == 0) blocks = 1;
+        update_streamed_kernel<<<blocks, kBlockThreads, 2 * kChunkSpheres * sizeof(float4), stream>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream) {
+    const uint32_t n_pad = (n + kGeomPad - 1) / kGeomPad * kGeomPad;
+    if (n_pad == 0) return cudaSuccess;
+    prep_geometry_kernel<<<(n_pad + 255) / 256, 256, 0, stream>>>(spheres, geom, n, n_pad);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream) {
+    if (n_texels == 0) return cudaSuccess;
+    const uint64_t threads = (n_texels + 3) / 4;
+    quantize_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(accum, reinterpret_cast<uint32_t*>(rgba8),
+                                                                         n_texels);
+    return cudaGetLastError();
+}
+
+}  // namespace rtk

@@ -1,0 +1,39 @@
+// rt_kernels.cuh — launch interface between the C-ABI host code (rt_api.cu) and the kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rt_abi.h"
+
+namespace rtk {
+
+constexpr int kPix = 4;             // pixels per thread
+constexpr int kWarpTileW = 32;      // a warp owns a 32 x 4 pixel tile: lane -> (lane & 7) + 8 p, lane >> 3
+constexpr int kWarpTileH = 4;
+constexpr int kBlockThreads = 256;  // 8 warps
+constexpr int kChunkSpheres = 2048; // streamed kernel: spheres per shared-memory stage (32 KB)
+constexpr uint32_t kResidentMaxSpheres = 4096;  // 64 KB of shared memory per CTA at most
+
+struct UpdateParams {
+    SceneCamera cam;            // 176 B, lands in the kernel parameter constant bank
+    float4* accum;              // window base: row_count * width texels (mean.rgb, n)
+    const float4* geom;         // n_spheres x (cx, cy, cz, |C|^2 - r^2 - slack)
+    const GpuSphere* spheres;   // the caller's buffer as uploaded (32 B stride)
+    uint32_t n_spheres;
+    uint32_t width, height;     // full image
+    uint32_t row_begin, row_count;  // window
+    uint32_t tiles_x, n_tiles;  // warp tiles over the window
+    unsigned int* tile_counter; // dynamic tile scheduler, zeroed before the launch
+    unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
+};
+
+// variant: 1 = baseline (thread per pixel, exact test per sphere from global memory),
+//          2 = tiled broad phase with the scene resident in shared memory,
+//          3 = tiled broad phase streaming sphere chunks through shared memory.
+cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream);
+cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream);
+cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream);
+cudaError_t configure_kernels();   // one-off cudaFuncSetAttribute calls
+
+}  // namespace rtk

@@ -1,0 +1,179 @@
+// rt_multi.cu — one image sharded by contiguous row blocks over several devices of one host,
+// scene replicated, result gathered into devices[0] by peer copies over NVLink
+// (cudaMemcpyPeerAsync on each shard's own stream, so every shard's copy starts the moment its
+// kernel retires and overlaps the other shards' compute).  No collective is needed: the shader has
+// no inter-pixel dependency (compute_shader.wgsl:333-364 touches only its own texel).
+#include <cuda_runtime.h>
+
+#include <new>
+#include <vector>
+
+#include "../../include/rt_abi.h"
+#include "rt_internal.h"
+
+using rti::fail;
+using rti::fail_cuda;
+
+struct RtMultiRenderer {
+    std::vector<RtRenderer*> shards;
+    uint32_t width = 0, height = 0;
+    uchar4* full_rgba8 = nullptr;    // on devices[0]
+    float4* full_accum = nullptr;    // on devices[0], allocated on first use
+};
+
+#define RTM_CUDA(call)                                      \
+    do {                                                    \
+        cudaError_t e_ = (call);                            \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call); \
+    } while (0)
+
+extern "C" {
+
+int rt_multi_destroy(RtMultiRenderer* m) {
+    if (!m) return RT_OK;
+    if (!m->shards.empty()) {
+        cudaSetDevice(m->shards[0]->device);
+        cudaFree(m->full_rgba8);
+        cudaFree(m->full_accum);
+    }
+    for (RtRenderer* s : m->shards) rt_destroy(s);
+    delete m;
+    return RT_OK;
+}
+
+int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height, RtMultiRenderer** out) {
+    if (!out) return fail(RT_ERR_INVALID_ARG, "out is null");
+    *out = nullptr;
+    if (!devices || n_devices == 0) return fail(RT_ERR_INVALID_ARG, "no devices");
+    if (height < n_devices) return fail(RT_ERR_INVALID_ARG, "fewer rows (%u) than devices (%u)", height, n_devices);
+    RtMultiRenderer* m = new (std::nothrow) RtMultiRenderer();
+    if (!m) return fail(RT_ERR_OUT_OF_MEMORY, "host allocation failed");
+    m->width = width; m->height = height;
+    // contiguous row blocks, sized in multiples of the 4-row warp tile where possible
+    const uint32_t tiles = (height + 3) / 4;
+    uint32_t row = 0;
+    for (uint32_t i = 0; i < n_devices; ++i) {
+        uint32_t t0 = (uint32_t)((uint64_t)tiles * i / n_devices), t1 = (uint32_t)((uint64_t)tiles * (i + 1) / n_devices);
+        uint32_t r0 = t0 * 4, r1 = (i + 1 == n_devices) ? height : t1 * 4;
+        if (r1 > height) r1 = height;
+        if (r1 <= r0) { rt_multi_destroy(m); return fail(RT_ERR_INVALID_ARG, "image too small to shard %u ways", n_devices); }
+        RtRenderer* s = nullptr;
+        int rc = rt_create_window(devices[i], width, height, r0, r1 - r0, &s);
+        if (rc != RT_OK) { rt_multi_destroy(m); return rc; }
+        m->shards.push_back(s);
+        row = r1;
+    }
+    (void)row;
+    // peer access devices[0] <-> devices[i]; cudaMemcpyPeerAsync falls back to staging when absent
+    for (uint32_t i = 1; i < n_devices; ++i) {
+        if (devices[i] == devices[0]) continue;
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, devices[0], devices[i]) == cudaSuccess && can) {
+            cudaSetDevice(devices[0]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(devices[i], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { rt_multi_destroy(m); return fail_cuda(e, "cudaDeviceEnablePeerAccess"); }
+            cudaSetDevice(devices[i]);
+            e = cudaDeviceEnablePeerAccess(devices[0], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { rt_multi_destroy(m); return fail_cuda(e, "cudaDeviceEnablePeerAccess"); }
+            cudaGetLastError();
+        }
+    }
+    cudaError_t e = cudaSetDevice(devices[0]);
+    if (e == cudaSuccess) e = cudaMalloc(&m->full_rgba8, (size_t)width * height * sizeof(uchar4));
+    if (e != cudaSuccess) { rt_multi_destroy(m); return fail_cuda(e, "rt_multi_create"); }
+    *out = m;
+    return RT_OK;
+}
+
+int rt_multi_set_scene(RtMultiRenderer* m, const GpuSphere* spheres, uint32_t buffer_len, uint32_t count) {
+    if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    for (RtRenderer* s : m->shards) {
+        int rc = rt_set_scene(s, spheres, buffer_len, count);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+int rt_multi_init(RtMultiRenderer* m) {
+    if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    for (RtRenderer* s : m->shards) {
+        int rc = rt_init(s);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+int rt_multi_update(RtMultiRenderer* m, const SceneCamera* camera) {
+    if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    for (RtRenderer* s : m->shards) {   // asynchronous: all devices run concurrently
+        int rc = rt_update(s, camera);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
+}
+
+int rt_multi_gather_rgba8(RtMultiRenderer* m, uint8_t* host) {
+    if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    const int dev0 = m->shards[0]->device;
+    for (RtRenderer* s : m->shards) {
+        int rc = rt_quantize(s);
+        if (rc != RT_OK) return rc;
+        RTM_CUDA(cudaSetDevice(s->device));
+        RTM_CUDA(cudaMemcpyPeerAsync(m->full_rgba8 + (size_t)s->row_begin * m->width, dev0, s->rgba8, s->device,
+                                     s->n_texels * sizeof(uchar4), s->stream));
+    }
+    for (RtRenderer* s : m->shards) {
+        RTM_CUDA(cudaSetDevice(s->device));
+        RTM_CUDA(cudaStreamSynchronize(s->stream));
+    }
+    if (host) {
+        RTM_CUDA(cudaSetDevice(dev0));
+        RTM_CUDA(cudaMemcpy(host, m->full_rgba8, (size_t)m->width * m->height * sizeof(uchar4), cudaMemcpyDeviceToHost));
+    }
+    return RT_OK;
+}
+
+int rt_multi_gather_accum(RtMultiRenderer* m, float* host) {
+    if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    const int dev0 = m->shards[0]->device;
+    if (!m->full_accum) {
+        RTM_CUDA(cudaSetDevice(dev0));
+        RTM_CUDA(cudaMalloc(&m->full_accum, (size_t)m->width * m->height * sizeof(float4)));
+    }
+    for (RtRenderer* s : m->shards) {
+        RTM_CUDA(cudaSetDevice(s->device));
+        RTM_CUDA(cudaMemcpyPeerAsync(m->full_accum + (size_t)s->row_begin * m->width, dev0, s->accum, s->device,
+                                     s->n_texels * sizeof(float4), s->stream));
+    }
+    for (RtRenderer* s : m->shards) {
+        RTM_CUDA(cudaSetDevice(s->device));
+        RTM_CUDA(cudaStreamSynchronize(s->stream));
+    }
+    if (host) {
+        RTM_CUDA(cudaSetDevice(dev0));
+        RTM_CUDA(cudaMemcpy(host, m->full_accum, (size_t)m->width * m->height * sizeof(float4), cudaMemcpyDeviceToHost));
+    }
+    return RT_OK;
+}
+
+int rt_multi_rays_traced(RtMultiRenderer* m, uint64_t* rays) {
+    if (!m || !rays) return fail(RT_ERR_INVALID_ARG, "null argument");
+    uint64_t total = 0;
+    for (RtRenderer* s : m->shards) {
+        uint64_t v = 0;
+        int rc = rt_rays_traced(s, &v);
+        if (rc != RT_OK) return rc;
+        total += v;
+    }
+    *rays = total;
+    return RT_OK;
+}
+
+int rt_multi_shard(RtMultiRenderer* m, uint32_t index, RtRenderer** shard) {
+    if (!m || !shard) return fail(RT_ERR_INVALID_ARG, "null argument");
+    if (index >= m->shards.size()) return fail(RT_ERR_INVALID_ARG, "shard %u of %zu", index, m->shards.size());
+    *shard = m->shards[index];
+    return RT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,239 @@
+/*
+ * rt_abi.h — C ABI of the B200-native per-pixel ray-trace pass.
+ *
+ * This header is the drop-in boundary for the ONE hot path of Sur091/GPU-Ray-Tracing:
+ * the `init` / `update` compute entry points of assets/compute_shader.wgsl, together with
+ * the two byte layouts that feed them.  Everything is plain C: fixed-size structs, raw
+ * pointers and sizes, `int` status codes.  No C++ or torch types cross this boundary.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   SceneCamera  176-byte uniform ........ src/camera.rs:256-291 == compute_shader.wgsl:7-40
+ *   GpuSphere    32-byte storage stride .. src/scene/sphere.rs:14-26 == compute_shader.wgsl:80-82,151-155
+ *   accumulation texel rgba32float ....... src/lib.rs:63-77 == compute_shader.wgsl:4-5,339-341,362-363
+ *   `init` dispatch ...................... src/lib.rs:398-407 -> compute_shader.wgsl:65-70
+ *   `update` dispatch .................... src/lib.rs:408-417 -> compute_shader.wgsl:333-364
+ *   per-frame buffer upload .............. src/lib.rs:151-207 (camera, spheres, count)
+ */
+#ifndef RT_ABI_H_
+#define RT_ABI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define RT_API __declspec(dllexport)
+#else
+#define RT_API __attribute__((visibility("default")))
+#endif
+
+/* ---------------------------------------------------------------------------------------
+ * Binary layouts (bit-identical to the reference's #[repr(C)] Pod structs)
+ * ------------------------------------------------------------------------------------- */
+
+typedef struct RtVec3 {
+    float x, y, z;
+} RtVec3;
+
+/* src/camera.rs:256-291.  11 rows of (vec3, f32).  Fields the shader reads are marked *. */
+typedef struct SceneCamera {
+    RtVec3 center;              float viewport_height;   /* off   0* / 12  */
+    RtVec3 viewport_upper_left; float viewport_width;    /* off  16* / 28  */
+    RtVec3 pixel_delta_u;       float defocus_angle;     /* off  32* / 44* */
+    RtVec3 pixel_delta_v;       float aspect_ratio;      /* off  48* / 60  */
+    RtVec3 defocus_disk_u;      float _padding0;         /* off  64* / 76  */
+    RtVec3 viewport_u;          float _padding1;         /* off  80  / 92  */
+    RtVec3 defocus_disk_v;      float max_depth;         /* off  96* / 108* */
+    RtVec3 look_from;           float samples_per_pixel; /* off 112  / 124* */
+    RtVec3 look_at;             float camera_has_moved;  /* off 128  / 140* */
+    RtVec3 vup;                 float random_seed;       /* off 144  / 156* */
+    RtVec3 viewport_v;          float defocus_radius;    /* off 160  / 172  */
+} SceneCamera;
+
+/* src/scene/sphere.rs:14-26.  color.w is the material selector (compute_shader.wgsl:272,276):
+ *   w < -1  lambertian (albedo = color.xyz)
+ *  -1..1    metal      (albedo = color.xyz, fuzz = w)
+ *   w >  1  dielectric (index of refraction = color.x) */
+typedef struct GpuSphere {
+    RtVec3 position;
+    float  radius;
+    float  color[4];
+} GpuSphere;
+
+/* src/camera.rs:9-28 (CameraSettings) — the host-side camera model SceneCamera derives from. */
+typedef struct CameraSettings {
+    float    field_of_view;      /* vertical, degrees */
+    uint32_t samples_per_pixel;
+    uint32_t camera_has_moved;   /* bool in the reference */
+    uint32_t max_depth;
+    RtVec3   vup;
+    RtVec3   look_from;
+    RtVec3   look_at;
+    float    defocus_angle;      /* degrees */
+    float    focus_distance;
+} CameraSettings;
+
+#if defined(__cplusplus)
+static_assert(sizeof(RtVec3) == 12, "Vec3 is 3 x f32, align 4 (glam 0.29)");
+static_assert(sizeof(SceneCamera) == 176, "SceneCamera uniform is 176 bytes");
+static_assert(offsetof(SceneCamera, viewport_upper_left) == 16, "layout");
+static_assert(offsetof(SceneCamera, defocus_angle) == 44, "layout");
+static_assert(offsetof(SceneCamera, pixel_delta_v) == 48, "layout");
+static_assert(offsetof(SceneCamera, defocus_disk_u) == 64, "layout");
+static_assert(offsetof(SceneCamera, defocus_disk_v) == 96, "layout");
+static_assert(offsetof(SceneCamera, max_depth) == 108, "layout");
+static_assert(offsetof(SceneCamera, samples_per_pixel) == 124, "layout");
+static_assert(offsetof(SceneCamera, camera_has_moved) == 140, "layout");
+static_assert(offsetof(SceneCamera, random_seed) == 156, "layout");
+static_assert(offsetof(SceneCamera, defocus_radius) == 172, "layout");
+static_assert(sizeof(GpuSphere) == 32, "GpuSphere stride is 32 bytes");
+static_assert(offsetof(GpuSphere, radius) == 12, "layout");
+static_assert(offsetof(GpuSphere, color) == 16, "layout");
+#endif
+
+/* Status codes.  Nothing aborts or throws across this boundary; the reference's panic!/unwrap
+ * sites (src/lib.rs:216-217,356-358,399-401) map to a negative status + rt_last_error(). */
+enum {
+    RT_OK                 = 0,
+    RT_ERR_INVALID_ARG    = -1,
+    RT_ERR_CUDA           = -2,
+    RT_ERR_NO_DEVICE      = -3,
+    RT_ERR_NO_SCENE       = -4,
+    RT_ERR_OUT_OF_MEMORY  = -5,
+    RT_ERR_STATE          = -6
+};
+
+typedef struct RtRenderer RtRenderer;          /* opaque: one device, one image (or row window) */
+typedef struct RtMultiRenderer RtMultiRenderer; /* opaque: one image sharded over several devices */
+
+/* ---------------------------------------------------------------------------------------
+ * Library / device
+ * ------------------------------------------------------------------------------------- */
+RT_API const char* rt_last_error(void);              /* thread-local, never NULL */
+RT_API const char* rt_version(void);
+RT_API int rt_device_count(int* count);              /* RT_ERR_NO_DEVICE when CUDA is unusable */
+
+/* ---------------------------------------------------------------------------------------
+ * Renderer handle == the render-world state the Bevy node owns (src/lib.rs:138-229):
+ * the accumulation image, the sphere storage buffer + count and the camera uniform.
+ * The reference ping-pongs two textures (src/lib.rs:218-228) only because a WebGPU storage
+ * texture cannot be read and written in one pass; each pixel touches its own texel only
+ * (compute_shader.wgsl:339,363), so here the accumulation is one in-place float4 image.
+ *
+ * A renderer may own a ROW WINDOW [row_begin, row_begin+row_count) of a width x height image:
+ * that is the multi-GPU shard.  Pixel seeds use absolute (x, y) (compute_shader.wgsl:309-310)
+ * so a window renders exactly the texels the full image would hold.
+ * ------------------------------------------------------------------------------------- */
+RT_API int rt_create(int device, uint32_t width, uint32_t height, RtRenderer** out);
+RT_API int rt_create_window(int device, uint32_t width, uint32_t height,
+                            uint32_t row_begin, uint32_t row_count, RtRenderer** out);
+RT_API int rt_destroy(RtRenderer* r);
+
+/* prepare_sphere_buffer (src/lib.rs:177-207): `spheres` points at `buffer_len` structs of which
+ * the first `count` are traced (the reference pads the Vec to MAX_SPHERES, sphere.rs:142-150).
+ * Borrowed for the call only. */
+RT_API int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, uint32_t count);
+
+/* WGSL `init` (compute_shader.wgsl:65-70): zero every accumulation texel. */
+RT_API int rt_init(RtRenderer* r);
+
+/* WGSL `update` (compute_shader.wgsl:333-364): one dispatch over every pixel of the window with
+ * this 176-byte uniform (prepare_camera_bind_group, src/lib.rs:151-175).  Asynchronous on the
+ * renderer's stream; any read-back call synchronises. */
+RT_API int rt_update(RtRenderer* r, const SceneCamera* camera);
+
+/* `n` consecutive `update` dispatches, cameras[i] used for dispatch i — the per-frame loop of
+ * ComputeShaderNode (src/lib.rs:369-374) with the per-frame random_seed re-roll of
+ * src/camera.rs:346 supplied by the caller.  Identical to calling rt_update n times. */
+RT_API int rt_update_n(RtRenderer* r, const SceneCamera* cameras, uint32_t n);
+
+RT_API int rt_synchronize(RtRenderer* r);
+
+/* Read / restore the accumulation window: row_count*width texels of (mean_r, mean_g, mean_b, n). */
+RT_API int rt_read_accum(RtRenderer* r, float* host_rgba32f);
+RT_API int rt_write_accum(RtRenderer* r, const float* host_rgba32f);
+/* Linear RGBA8 of the running mean: q(x) = floor(clamp(x,0,1)*255 + 0.5), alpha = 255. */
+RT_API int rt_read_rgba8(RtRenderer* r, uint8_t* host_rgba8);
+
+/* Number of sphere_list_hit traversals (compute_shader.wgsl:266) executed since the last
+ * rt_reset_counters: the "rays" of the Mrays/s metric. */
+RT_API int rt_rays_traced(RtRenderer* r, uint64_t* rays);
+/* Number of (ray, sphere) pairs that went through the exact quadratic after the broad phase. */
+RT_API int rt_exact_tests(RtRenderer* r, uint64_t* tests);
+RT_API int rt_reset_counters(RtRenderer* r);
+
+/* Device-side timing of the update kernels on the renderer's own stream (CUDA events). */
+RT_API int rt_timer_begin(RtRenderer* r);
+RT_API int rt_timer_end(RtRenderer* r, float* elapsed_ms);   /* synchronises */
+RT_API int rt_kernel_launches(RtRenderer* r, uint64_t* launches);
+
+/* Interop for a host that already lives on the GPU (torch, another CUDA library). */
+RT_API int rt_accum_device_ptr(RtRenderer* r, void** ptr);   /* float4[row_count*width] */
+RT_API int rt_rgba8_device_ptr(RtRenderer* r, void** ptr);   /* uchar4[row_count*width], filled by rt_quantize */
+RT_API int rt_quantize(RtRenderer* r);                       /* accum -> rgba8, on the stream */
+RT_API int rt_stream(RtRenderer* r, void** cuda_stream);
+RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
+                     uint32_t* row_begin, uint32_t* row_count);
+
+/* Kernel selection for experiments/tests: 0 = auto, 1 = baseline (one thread per pixel, exact
+ * quadratic per sphere), 2 = tiled broad-phase + exact narrow phase. */
+RT_API int rt_set_kernel_variant(RtRenderer* r, int variant);
+
+/* ---------------------------------------------------------------------------------------
+ * Headless one-shot entries (new surface asked for by the port target; the reference has
+ * only the windowed app, src/lib.rs:28-58)
+ * ------------------------------------------------------------------------------------- */
+/* render(scene, camera, w, h): zeroed accumulators, `samples` update dispatches with this
+ * camera (random_seed as given), result as rgba32f (w*h*4 floats). */
+RT_API int rt_render(int device, const GpuSphere* spheres, uint32_t count,
+                     const SceneCamera* camera, uint32_t width, uint32_t height,
+                     uint32_t samples, float* out_rgba32f);
+/* One frame per camera (fly-through); out_rgba8 holds n_frames*w*h*4 bytes. */
+RT_API int rt_render_frames(int device, const GpuSphere* spheres, uint32_t count,
+                            const SceneCamera* cameras, uint32_t n_frames,
+                            uint32_t width, uint32_t height, uint8_t* out_rgba8);
+
+/* ---------------------------------------------------------------------------------------
+ * One image sharded by row tiles over several devices of one host, scene replicated,
+ * result gathered to devices[0] by peer copy over NVLink.
+ * ------------------------------------------------------------------------------------- */
+RT_API int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height,
+                           RtMultiRenderer** out);
+RT_API int rt_multi_destroy(RtMultiRenderer* m);
+RT_API int rt_multi_set_scene(RtMultiRenderer* m, const GpuSphere* spheres, uint32_t buffer_len, uint32_t count);
+RT_API int rt_multi_init(RtMultiRenderer* m);
+RT_API int rt_multi_update(RtMultiRenderer* m, const SceneCamera* camera);
+RT_API int rt_multi_gather_rgba8(RtMultiRenderer* m, uint8_t* host_rgba8);   /* may be NULL: gather on device only */
+RT_API int rt_multi_gather_accum(RtMultiRenderer* m, float* host_rgba32f);
+RT_API int rt_multi_rays_traced(RtMultiRenderer* m, uint64_t* rays);
+RT_API int rt_multi_shard(RtMultiRenderer* m, uint32_t index, RtRenderer** shard);
+
+/* ---------------------------------------------------------------------------------------
+ * Host helpers: the CPU code on either side of the path
+ * ------------------------------------------------------------------------------------- */
+/* CameraSettings::default() (src/camera.rs:30-46). */
+RT_API void rt_camera_settings_default(CameraSettings* out);
+/* SceneCamera::from(&CameraSettings) (src/camera.rs:293-351) generalised from crate::SIZE to
+ * (width, height); random_seed is supplied (the reference rolls rand::random::<f32>() there). */
+RT_API int rt_camera_from_settings(const CameraSettings* settings, uint32_t width, uint32_t height,
+                                   float random_seed, SceneCamera* out);
+/* create_default_spheres (src/scene/sphere.rs:45-153) with a seeded generator instead of the
+ * thread RNG.  Writes at most `capacity` spheres, returns the number in *count and the padded
+ * buffer length (>= MAX_SPHERES = 100) in *buffer_len. */
+RT_API int rt_create_default_spheres(uint64_t seed, GpuSphere* out, uint32_t capacity,
+                                     uint32_t* count, uint32_t* buffer_len);
+/* Benchmark scenes: ground sphere + (n-1) random spheres. */
+RT_API int rt_create_random_spheres(uint64_t seed, uint32_t n, GpuSphere* out);
+/* Ground sphere + (n-1) small spheres on a square grid, the reference recipe scaled up. */
+RT_API int rt_create_grid_spheres(uint64_t seed, uint32_t n, GpuSphere* out);
+/* Orbit fly-through: pose k of n around look_at (camera.rs:125-253 yaw controls, scripted). */
+RT_API int rt_orbit_camera(uint32_t k, uint32_t n, float radius, float height, float fov_deg,
+                           uint32_t width, uint32_t height_px, SceneCamera* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_ABI_H_ */

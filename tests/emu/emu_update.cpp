@@ -1,0 +1,81 @@
+// emu_update.cpp — CPU emulation of the CUDA `update` kernels for machines without a GPU.
+// TEST INFRASTRUCTURE: compiles the product's own per-ray code (gpu_ray_tracing_b200/csrc/rt_core.cuh)
+// for the host and drives it with the same broad-phase / narrow-phase control flow as
+// rt_kernels.cu, so that `-m "not gpu"` tests can (a) compare the kernels' arithmetic bit-for-bit
+// with the oracle and (b) audit the broad phase: every (ray, sphere) pair the broad phase rejects
+// is also put through the exact quadratic, and a pair it wrongly rejected counts as a violation.
+// Built with -ffp-contract=off; fmaf() is the IEEE fused operation, as FFMA is on the GPU.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "../../gpu_ray_tracing_b200/csrc/rt_core.cuh"
+
+using rtc::f3;
+
+extern "C" __attribute__((visibility("default")))
+void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t count, uint32_t width, uint32_t height,
+                uint32_t row_begin, uint32_t row_count, float* accum, uint64_t* stats /* rays, exact, violations */) {
+    (void)height;
+    const SceneCamera& cam = *cam_p;
+    std::vector<float> gk(count);
+    for (uint32_t i = 0; i < count; ++i) gk[i] = rtc::broad_record_k(spheres[i]);
+    const uint32_t seed_bits = rtc::f2u(cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(cam.samples_per_pixel);
+    const uint32_t max_depth = rtc::f2u(cam.max_depth);
+    const bool reset = cam.camera_has_moved > 0.5f;
+    uint64_t rays = 0, exact = 0, violations = 0;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations)
+#endif
+    for (int64_t row = 0; row < (int64_t)row_count; ++row) {
+        const int y_abs = (int)(row_begin + row);
+        for (uint32_t x = 0; x < width; ++x) {
+            float* texel = accum + ((size_t)row * width + x) * 4;
+            f3 mean = rtc::mk(texel[0], texel[1], texel[2]);
+            uint32_t n = rtc::f2u(texel[3]);
+            if (reset) { mean = rtc::mk(0, 0, 0); n = 0; }
+            if (n < spp) {
+                const uint32_t seed = 1u + n + seed_bits;
+                rtc::Ray r = rtc::get_ray(cam, (int)x, y_abs, seed, seed_bits);
+                f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
+                bool black = false;
+                for (uint32_t i = 0; i < max_depth; ++i) {
+                    ++rays;
+                    const float a = rtc::dot(r.d, r.d);
+                    const rtc::BroadRay b = rtc::broad_arm(r.o, r.d, a);
+                    float best_t = 3.4e35f;
+                    int best_i = -1;
+                    for (uint32_t s = 0; s < count; ++s) {
+                        const GpuSphere& sp = spheres[s];
+                        const float g = rtc::broad_g(sp.position.x, sp.position.y, sp.position.z, gk[s], b.ux, b.uy, b.uz,
+                                                     b.h0, b.mox, b.moy, b.moz);
+                        float root;
+                        if (!(g < b.thr)) {
+                            ++exact;
+                            if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, best_t, &root)) {
+                                best_t = root;
+                                best_i = (int)s;
+                            }
+                        } else if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, -INFINITY, INFINITY, &root)) {
+                            ++violations;   // broad phase rejected a pair whose exact discriminant is >= 0 (or NaN)
+                        }
+                    }
+                    if (best_i < 0) break;
+                    if (!rtc::scatter(&r, &factor, best_t, spheres[best_i], rtc::hash(seed + 1u + i * 1000u))) {
+                        black = true;
+                        break;
+                    }
+                }
+                f3 color = black ? rtc::mk(0, 0, 0) : rtc::sky_times(factor, r.d);
+                mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+                n += 1u;
+            }
+            texel[0] = mean.x; texel[1] = mean.y; texel[2] = mean.z; texel[3] = (float)n;
+        }
+    }
+    if (stats) { stats[0] = rays; stats[1] = exact; stats[2] = violations; }
+}
