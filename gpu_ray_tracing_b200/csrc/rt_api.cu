@@ -138,7 +138,7 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
     if (count > (1u << 26)) return fail(RT_ERR_INVALID_ARG, "too many spheres");
     // storage buffers cannot be empty in wgpu either; keep one slot so pointers stay valid
     const uint32_t cap_needed = buffer_len > 0 ? buffer_len : 1;
-    const uint32_t pad_needed = (count + 7) / 8 * 8 + 8;
+    const uint32_t pad_needed = (count + 7) / 8 * 8 + 8;   // rtk: kGeomPad rounding + kGeomTail
     if (cap_needed > r->sphere_capacity || pad_needed > r->geom_capacity) {
         RT_CUDA(cudaStreamSynchronize(r->stream));
         cudaFree(r->spheres); r->spheres = nullptr; r->sphere_capacity = 0;
@@ -152,7 +152,7 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
         RT_CUDA(cudaMemcpyAsync(r->spheres, spheres, (size_t)buffer_len * sizeof(GpuSphere), cudaMemcpyHostToDevice, r->stream));
     r->n_spheres = count;
     RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
-    r->launches += count ? 1 : 0;
+    r->launches += 1;
     // the source is borrowed for the call only (pageable memory: the copy above has been staged,
     // but make the contract unconditional)
     RT_CUDA(cudaStreamSynchronize(r->stream));

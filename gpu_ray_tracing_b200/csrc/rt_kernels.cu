@@ -28,34 +28,57 @@ constexpr float kTMin = 0.001f;    // compute_shader.wgsl:266
 constexpr float kTMax = 3.4e35f;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kUnroll = 4;         // spheres per broad-phase iteration
-constexpr int kGeomPad = 8;        // geometry arrays are padded to a multiple of this
+constexpr int kGeomPad = 8;        // geometry arrays are padded to a multiple of this ...
+constexpr int kGeomTail = 8;       // ... plus a tail the software prefetch may read (never computed)
 
 // Per-thread state of kPix rays.  Every index is a compile-time constant after unrolling, so the
 // arrays live in registers.
+constexpr int kPairs = kPix / 2;
+static_assert(kPix % 2 == 0, "the broad phase works on pixel pairs (FFMA2)");
+
 struct Lanes {
     float dx[kPix], dy[kPix], dz[kPix];     // ray direction, as the reference holds it
-    float mox[kPix], moy[kPix], moz[kPix];  // -2 * ray origin (exact; origin = -0.5 * this)
+    float ox[kPix], oy[kPix], oz[kPix];     // ray origin
     float a[kPix];                          // dot(d, d) with the reference's rounding
-    float ux[kPix], uy[kPix], uz[kPix];     // broad phase: unit direction
-    float h0[kPix];                         // broad phase: -dot(O, u)
-    float thr[kPix];                        // broad phase: |O|^2 (1 - kappa); +inf for idle rays
+    // broad phase, two rays per 64-bit register pair (.x = ray 2q, .y = ray 2q+1)
+    float2 ux[kPairs], uy[kPairs], uz[kPairs];     // unit direction
+    float2 h0[kPairs];                             // -dot(O, u)
+    float2 mox[kPairs], moy[kPairs], moz[kPairs];  // -2 O
+    float thr[kPix];                        // |O|^2 (1 - kappa); +inf for idle rays
     float best_t[kPix];
     int best_i[kPix];
     bool alive[kPix];
 };
 
+__device__ __forceinline__ float& half(float2& v, int p) { return (p & 1) ? v.y : v.x; }
+__device__ __forceinline__ float half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
+
+// Broad phase for the ray pair q against one sphere record: 7 FFMA2 (fma.rn.f32x2, sm_100).
+// The sphere scalars enter as broadcast operands; each half is the IEEE fused operation, so the
+// values equal rtc::broad_g() per ray.
+__device__ __forceinline__ float2 broad_g2(const float4 sp, const Lanes& L, int q) {
+    const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z);
+    float2 h = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], L.h0[q])));
+    float2 c = __ffma2_rn(sx, L.mox[q], __ffma2_rn(sy, L.moy[q], __ffma2_rn(sz, L.moz[q], make_float2(sp.w, sp.w))));
+    return __ffma2_rn(h, h, make_float2(-c.x, -c.y));
+}
+
 __device__ __forceinline__ float broad_g(const float4 sp, const Lanes& L, int p) {
-    return rtc::broad_g(sp.x, sp.y, sp.z, sp.w, L.ux[p], L.uy[p], L.uz[p], L.h0[p], L.mox[p], L.moy[p], L.moz[p]);
+    const int q = p >> 1;
+    return rtc::broad_g(sp.x, sp.y, sp.z, sp.w, half(L.ux[q], p), half(L.uy[q], p), half(L.uz[q], p), half(L.h0[q], p),
+                        half(L.mox[q], p), half(L.moy[q], p), half(L.moz[q], p));
 }
 
 __device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
+    const int q = p >> 1;
     L.dx[p] = d.x; L.dy[p] = d.y; L.dz[p] = d.z;
+    L.ox[p] = o.x; L.oy[p] = o.y; L.oz[p] = o.z;
     const float a = rtc::dot(d, d);
     L.a[p] = a;
     const rtc::BroadRay b = rtc::broad_arm(o, d, a);
-    L.mox[p] = b.mox; L.moy[p] = b.moy; L.moz[p] = b.moz;
-    L.ux[p] = b.ux; L.uy[p] = b.uy; L.uz[p] = b.uz;
-    L.h0[p] = b.h0;
+    half(L.mox[q], p) = b.mox; half(L.moy[q], p) = b.moy; half(L.moz[q], p) = b.moz;
+    half(L.ux[q], p) = b.ux; half(L.uy[q], p) = b.uy; half(L.uz[q], p) = b.uz;
+    half(L.h0[q], p) = b.h0;
     L.thr[p] = b.thr;
     L.best_t[p] = kTMax;
     L.best_i[p] = -1;
@@ -63,20 +86,20 @@ __device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
 }
 
 __device__ __forceinline__ void idle_ray(Lanes& L, int p) {
+    const int q = p >> 1;
     L.dx[p] = L.dy[p] = L.dz[p] = 0.0f;
-    L.mox[p] = L.moy[p] = L.moz[p] = 0.0f;
+    L.ox[p] = L.oy[p] = L.oz[p] = 0.0f;
     L.a[p] = 1.0f;
-    L.ux[p] = L.uy[p] = L.uz[p] = 0.0f;
-    L.h0[p] = 0.0f;
+    half(L.mox[q], p) = 0.0f; half(L.moy[q], p) = 0.0f; half(L.moz[q], p) = 0.0f;
+    half(L.ux[q], p) = 0.0f; half(L.uy[q], p) = 0.0f; half(L.uz[q], p) = 0.0f;
+    half(L.h0[q], p) = 0.0f;
     L.thr[p] = __int_as_float(0x7f800000);
     L.best_t[p] = kTMax;
     L.best_i[p] = -1;
     L.alive[p] = false;
 }
 
-__device__ __forceinline__ f3 origin_of(const Lanes& L, int p) {
-    return rtc::mk(-0.5f * L.mox[p], -0.5f * L.moy[p], -0.5f * L.moz[p]);
-}
+__device__ __forceinline__ f3 origin_of(const Lanes& L, int p) { return rtc::mk(L.ox[p], L.oy[p], L.oz[p]); }
 
 // Narrow phase over `count` consecutive spheres starting at shared-memory slot `slot`
 // (global index `index0`): the reference's sphere_hit root for every candidate ray.
@@ -105,22 +128,41 @@ __device__ __forceinline__ void narrow_phase(const float4* __restrict__ s_geom, 
     }
 }
 
-// Broad phase over `count` (multiple of kUnroll) spheres resident at s_geom[0..count).
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+// Broad phase over `count` (multiple of kUnroll) spheres resident at s_geom[0..count); the
+// kUnroll records after the end must be readable (prefetch).  The next group's records are
+// loaded before the current group's arithmetic so the LDS latency is off the critical path.
 __device__ __forceinline__ void scan_spheres(const float4* __restrict__ s_geom, int count, int index0,
                                              const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
                                              uint32_t& exact_tests) {
-#pragma unroll 1
-    for (int s = 0; s < count; s += kUnroll) {
-        float4 sp[kUnroll];
+    uint32_t addr = (uint32_t)__cvta_generic_to_shared(s_geom);
+    float4 cur[kUnroll];
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) sp[u] = s_geom[s + u];
+    for (int u = 0; u < kUnroll; ++u) cur[u] = lds128(addr + 16u * u);
+#pragma unroll 2
+    for (int s = 0; s < count; s += kUnroll) {
+        addr += 16u * kUnroll;
+        float4 nxt[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
         bool any = false;
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
 #pragma unroll
-            for (int p = 0; p < kPix; ++p) any |= !(broad_g(sp[u], L, p) < L.thr[p]);
+            for (int q = 0; q < kPairs; ++q) {
+                const float2 g = broad_g2(cur[u], L, q);
+                any |= !(g.x < L.thr[2 * q]);
+                any |= !(g.y < L.thr[2 * q + 1]);
+            }
         }
         if (any) narrow_phase(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) cur[u] = nxt[u];
     }
 }
 
@@ -248,7 +290,7 @@ __device__ __forceinline__ void flush_counters(const UpdateParams& P, uint32_t r
 __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_geom[];
     const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
-    for (int i = threadIdx.x; i < n_pad; i += kBlockThreads) s_geom[i] = __ldg(&P.geom[i]);
+    for (int i = threadIdx.x; i < n_pad + kGeomTail; i += kBlockThreads) s_geom[i] = __ldg(&P.geom[i]);
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
@@ -393,7 +435,8 @@ __global__ void quantize_kernel(const float4* __restrict__ accum, uint32_t* __re
 // reference's tie rule) is preserved.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const __grid_constant__ UpdateParams P) {
-    extern __shared__ float4 s_stage[];   // [2][kChunkSpheres]
+    extern __shared__ float4 s_stage[];   // [2][kChunkSpheres + kGeomTail]
+    constexpr int kStage = kChunkSpheres + kGeomTail;
     __shared__ uint32_t s_block_tile;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
@@ -430,7 +473,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
             // prologue: chunk 0 -> stage 0
             {
                 const int cnt = min(kChunkSpheres, n_pad);
-                for (int i = threadIdx.x; i < cnt; i += kBlockThreads) s_stage[i] = __ldg(&P.geom[i]);
+                for (int i = threadIdx.x; i < cnt + kGeomTail; i += kBlockThreads) s_stage[i] = __ldg(&P.geom[i]);
             }
             __syncthreads();
             for (int c = 0; c < n_chunks; ++c) {
@@ -439,11 +482,11 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
                 if (c + 1 < n_chunks) {
                     const int nbase = base + kChunkSpheres;
                     const int ncnt = min(kChunkSpheres, n_pad - nbase);
-                    float4* dst = s_stage + ((c + 1) & 1) * kChunkSpheres;
-                    for (int i = threadIdx.x; i < ncnt; i += kBlockThreads) dst[i] = __ldg(&P.geom[nbase + i]);
+                    float4* dst = s_stage + ((c + 1) & 1) * kStage;
+                    for (int i = threadIdx.x; i < ncnt + kGeomTail; i += kBlockThreads) dst[i] = __ldg(&P.geom[nbase + i]);
                 }
                 if (warp_alive)
-                    scan_spheres(s_stage + (c & 1) * kChunkSpheres, cnt, base, P.spheres, P.n_spheres, L, exact_tests);
+                    scan_spheres(s_stage + (c & 1) * kStage, cnt, base, P.spheres, P.n_spheres, L, exact_tests);
                 __syncthreads();
             }
             after_traversal(P, bounce, L, J);
@@ -458,10 +501,10 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 cudaError_t configure_kernels() {
     cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(kResidentMaxSpheres * sizeof(float4)));
+                                         (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(2 * kChunkSpheres * sizeof(float4)));
+                                (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
 }
 
 cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream) {
@@ -481,20 +524,19 @@ cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cuda
         const uint32_t resident = (uint32_t)sm_count * 2u;
         if (blocks > resident) blocks = resident;
         if (blocks == 0) blocks = 1;
-        update_resident_kernel<<<blocks, kBlockThreads, n_pad * sizeof(float4), stream>>>(p);
+        update_resident_kernel<<<blocks, kBlockThreads, (n_pad + kGeomTail) * sizeof(float4), stream>>>(p);
     } else {
         uint32_t blocks = (p.n_tiles + 7) / 8;
         const uint32_t resident = (uint32_t)sm_count * 2u;
         if (blocks > resident) blocks = resident;
         if (blocks == 0) blocks = 1;
-        update_streamed_kernel<<<blocks, kBlockThreads, 2 * kChunkSpheres * sizeof(float4), stream>>>(p);
+        update_streamed_kernel<<<blocks, kBlockThreads, 2 * (kChunkSpheres + kGeomTail) * sizeof(float4), stream>>>(p);
     }
     return cudaGetLastError();
 }
 
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream) {
-    const uint32_t n_pad = (n + kGeomPad - 1) / kGeomPad * kGeomPad;
-    if (n_pad == 0) return cudaSuccess;
+    const uint32_t n_pad = (n + kGeomPad - 1) / kGeomPad * kGeomPad + kGeomTail;
     prep_geometry_kernel<<<(n_pad + 255) / 256, 256, 0, stream>>>(spheres, geom, n, n_pad);
     return cudaGetLastError();
 }

@@ -1,0 +1,164 @@
+"""GPU parity: the CUDA kernels, called through the C ABI, against the CPU oracle on the same
+bytes.  The bar is bit-identical rgba32f accumulators (stronger than the <= 1/255 after RGBA8
+quantisation the port target states); the RGBA8 mismatch count is reported either way."""
+import numpy as np
+import pytest
+
+import gpu_ray_tracing_b200 as rt
+import oracle_lib as ol
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_update(scene, cams, width, height, variant=0, accum=None, row_begin=0, row_count=None):
+    with rt.Renderer(width, height, row_begin=row_begin, row_count=row_count) as r:
+        r.set_kernel_variant(variant)
+        r.set_scene(scene)
+        if accum is None:
+            r.init()
+        else:
+            r.write_accum(accum)
+        for cam in cams:
+            r.update(cam)
+        return r.read_accum(), r.rays_traced(), r.exact_tests()
+
+
+def assert_parity(gpu, cpu, what):
+    rep = ol.compare_images(cpu, gpu)
+    print(what, rep)
+    assert rep["pixels_over_1_255"] == 0, (what, rep)
+    assert rep["bit_identical"], (what, rep)
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("depth", [1, 30])
+def test_default_scene_720p(variant, depth):
+    """BASELINE config 1: repo default scene at 1280x720, first frame."""
+    W, H = 1280, 720
+    scene, cam = scenes.default_scene(), scenes.camera(W, H, max_depth=depth, spp=500)
+    cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+    gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H, variant)
+    assert rays_gpu == rays_cpu
+    assert_parity(gpu, cpu, f"default 720p depth {depth} variant {variant}")
+
+
+@pytest.mark.parametrize("variant", [2, 3])
+def test_default_scene_4k_depth1(variant):
+    """BASELINE config 2: default scene at 3840x2160 (layout + tolerance check)."""
+    W, H = 3840, 2160
+    scene, cam = scenes.default_scene(), scenes.camera(W, H, max_depth=1, spp=1)
+    cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+    gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H, variant)
+    assert rays_gpu == rays_cpu == W * H
+    assert_parity(gpu, cpu, f"default 4K variant {variant}")
+
+
+@pytest.mark.parametrize("variant", [1, 2, 3])
+def test_random_1024_spheres(variant):
+    """BASELINE config 3 scene at a size the oracle finishes in seconds."""
+    W, H = 960, 540
+    scene, cam = scenes.random_scene(1024), scenes.camera(W, H, max_depth=1, spp=1)
+    cpu, _ = ol.oracle_update(cam, scene, W, H)
+    gpu, rays, exact = gpu_update(scene, [cam], W, H, variant)
+    assert rays == W * H
+    assert_parity(gpu, cpu, f"random1024 variant {variant}")
+
+
+def test_random_1024_depth8_progressive():
+    """Three progressive frames with a re-rolled random_seed and the reset flag cleared."""
+    W, H = 640, 360
+    scene = scenes.random_scene(1024)
+    cams = [scenes.camera(W, H, max_depth=8, spp=500, random_seed=s, moved=m)
+            for s, m in ((0.25, 1), (0.625, 0), (0.8125, 0))]
+    cpu = np.zeros((H, W, 4), dtype=np.float32)
+    rays_cpu = 0
+    for cam in cams:
+        cpu, r = ol.oracle_update(cam, scene, W, H, accum=cpu)
+        rays_cpu += r
+    gpu, rays_gpu, _ = gpu_update(scene, cams, W, H)
+    assert rays_gpu == rays_cpu
+    assert (gpu[..., 3] == 3.0).all()
+    assert_parity(gpu, cpu, "random1024 depth8 x3 frames")
+
+
+def test_ragged_sizes_and_windows():
+    """Sizes that are not multiples of the 8x8 workgroup / 32x4 warp tile, and a row window."""
+    scene = scenes.default_scene()
+    for (W, H) in ((33, 7), (1, 1), (250, 131)):
+        cam = scenes.camera(W, H, max_depth=4, spp=2)
+        cpu, _ = ol.oracle_update(cam, scene, W, H)
+        for variant in (1, 2, 3):
+            gpu, _, _ = gpu_update(scene, [cam], W, H, variant)
+            assert_parity(gpu, cpu, f"{W}x{H} variant {variant}")
+    W, H = 250, 131
+    cam = scenes.camera(W, H, max_depth=4, spp=2)
+    cpu, _ = ol.oracle_update(cam, scene, W, H)
+    gpu, _, _ = gpu_update(scene, [cam], W, H, row_begin=37, row_count=50)
+    assert_parity(gpu, cpu[37:87], "row window 37..87")
+
+
+def test_sample_cap_and_empty_scene():
+    """n >= samples_per_pixel leaves the texel alone; zero spheres renders pure sky; max_depth 0 too."""
+    W, H = 64, 32
+    scene = scenes.default_scene()
+    cam = scenes.camera(W, H, max_depth=5, spp=2, moved=0)
+    start = np.zeros((H, W, 4), dtype=np.float32)
+    start[..., :3] = 0.25
+    start[..., 3] = 2.0
+    gpu, rays, _ = gpu_update(scene, [cam], W, H, accum=start.copy())
+    assert rays == 0 and np.array_equal(gpu, start)
+    empty = rt.SphereCollection(np.zeros(4, dtype=rt.SPHERE_DTYPE), 0)
+    cam = scenes.camera(W, H, max_depth=5, spp=1)
+    cpu, _ = ol.oracle_update(cam, empty, W, H)
+    gpu, _, _ = gpu_update(empty, [cam], W, H)
+    assert_parity(gpu, cpu, "empty scene")
+    cam0 = scenes.camera(W, H, max_depth=0, spp=1)
+    cpu, rays_cpu = ol.oracle_update(cam0, scene, W, H)
+    gpu, rays_gpu, _ = gpu_update(scene, [cam0], W, H)
+    assert rays_cpu == rays_gpu == 0
+    assert_parity(gpu, cpu, "max_depth 0")
+
+
+def test_large_scene_streamed():
+    """16,384 spheres (four shared-memory chunks per traversal) — the config-5 path at small size."""
+    W, H = 256, 144
+    scene = scenes.grid_scene(16384)
+    cam = rt.orbit_camera(3, 256, W, H)
+    cpu, _ = ol.oracle_update(cam, scene, W, H)
+    gpu, rays, _ = gpu_update(scene, [cam], W, H)
+    assert rays == W * H
+    assert_parity(gpu, cpu, "grid 16384")
+    cam.max_depth = 6.0
+    cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+    gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
+    assert rays_cpu == rays_gpu
+    assert_parity(gpu, cpu, "grid 16384 depth 6")
+
+
+def test_rgba8_and_headless_render():
+    W, H = 320, 180
+    scene, cam = scenes.default_scene(), scenes.camera(W, H, max_depth=10, spp=4)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        r.update(cam)
+        accum, rgba = r.read_accum(), r.read_rgba8()
+    assert np.array_equal(rgba, ol.quantize(accum))
+    out = rt.render(scene, cam, W, H, samples=1)
+    assert np.array_equal(out, accum)
+
+
+def test_node_state_machine_on_device():
+    """Loading -> Init -> Update(1) <-> Update(0): the Init dispatch zeroes, every later one samples."""
+    W, H = 64, 64
+    scene, cam = scenes.default_scene(), scenes.camera(W, H, max_depth=3, spp=10, moved=0)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        node = rt.ComputeShaderNode(r)
+        counts = []
+        for _ in range(5):
+            node.update()
+            node.run(cam)
+            counts.append(float(r.read_accum()[0, 0, 3]))
+    assert counts == [0.0, 1.0, 2.0, 3.0, 4.0]
