@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the per-pixel ray-trace pass on B200 (BASELINE.json metric).
+
+Workload (config["workload"]): 1024 random spheres, 3840x2160, max_depth 1, 1 sample — one
+`update` dispatch per frame, rays == pixels.  A step renders one frame per GPU (frames of a camera
+batch are sharded over the ranks, scene replicated; weak scaling); with N > 1 every frame's RGBA8
+image is gathered to rank 0 over NCCL, overlapped with the next step's kernel.
+
+  python bench.py [--gpus N --steps K --warmup W]          our arm (CUDA kernels through the C ABI)
+  python bench.py --impl reference [...]                   the CPU restatement of the shader (oracle)
+                                                           on the box's host cores, same metric/config
+
+One JSON line on stdout (rank 0).  Keys beyond the base contract: roofline (FP32-FMA bound; the
+denominator is measured in the same run by tools/ffma_peak.cu because MEASURED_PEAKS.json carries no
+FP32 figure), hbm (the accumulation-image traffic against the measured copy bandwidth),
+cpu_baseline, e2e, clocks, gpu_launches, parity.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+W, H, N_SPHERES = 3840, 2160, 1024
+FLOP_PER_TEST = 18   # oc 3 + h 5 + c 7 + disc 3, a = d.d hoisted
+METRIC = "Mrays/s at 4K/1024 spheres"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def workload_config(n_gpus):
+    return {
+        "workload": f"{N_SPHERES} random spheres (seed 1234) at {W}x{H}, max_depth 1, 1 sample/pixel, one frame per GPU per step",
+        "spheres": N_SPHERES, "width": W, "height": H, "max_depth": 1, "frames_per_step": n_gpus,
+        "parallelism": f"frames sharded over {n_gpus} GPU(s), scene replicated" + (", RGBA8 gathered to rank 0 (NCCL)" if n_gpus > 1 else ""),
+        "l2": "accumulation image (132.7 MB float4, stored once per step) exceeds the 126 MB L2; the 32 KB sphere buffer is shared-memory resident by design",
+    }
+
+
+class ClockSampler:
+    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.samples, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append((time.perf_counter(), line.strip()))
+
+    def stop(self, since=None):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        mhz, mx, reasons, power = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        timed = [x for t, x in self.samples if since is None or t >= since]
+        if len(timed) < 3:   # a very short timed region: fall back to everything sampled under load (warm-up included)
+            timed = [x for _, x in self.samples]
+        for s in timed:
+            f = [x.strip() for x in s.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                mhz.append(float(f[0]))
+                mx = float(f[1])
+                power.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(mhz) if mhz else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "power_w_max": max(power) if power else None, "samples": len(mhz)}
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {}
+
+
+def ffma_peak_tflops(device):
+    """FP32 FMA peak measured now, on this GPU (tools/ffma_peak.cu)."""
+    lib = C.CDLL(os.path.join(ROOT, "tools", "libffma_peak.so"))
+    tf, sms = C.c_double(0), C.c_int(0)
+    rc = lib.ffma_peak(device, 8, C.byref(tf), None, C.byref(sms))
+    if rc != 0:
+        raise RuntimeError(f"ffma_peak failed: {rc}")
+    return tf.value, sms.value
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arms (the only places the oracle is executed outside tests/)
+# ------------------------------------------------------------------------------------------------
+def cpu_sample(rows, row_begin, threads=0):
+    """Time one oracle `update` over a row window of the 4K workload.  Returns (Mrays/s, seconds, rays, threads)."""
+    import numpy as np
+    import oracle_lib as ol
+    import scenes
+    scene, cam = scenes.random_scene(N_SPHERES), scenes.camera(W, H, 1, 1)
+    accum = np.zeros((rows, W, 4), dtype=np.float32)
+    nthreads = threads or ol.oracle().oracle_max_threads()
+    t0 = time.perf_counter()
+    _, rays = ol.oracle_update(cam, scene, W, H, accum=accum, row_begin=row_begin, row_count=rows, threads=nthreads)
+    dt = time.perf_counter() - t0
+    return rays / dt / 1e6, dt, rays, nthreads
+
+
+def run_reference(args):
+    """--impl reference: the reference's shader math on the host cores.  The WGSL itself cannot run
+    here (no wgpu / graphics stack / Rust: 'unavailable on this box'), so this is the C++ port."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    rows = 216   # bounded sample: a tenth of the frame, centred (horizon + spheres in view)
+    row_begin = (H - rows) // 2
+    for _ in range(max(args.warmup, 1)):
+        cpu_sample(48, row_begin)
+    t0 = time.perf_counter()
+    rays_total, threads = 0, 1
+    for _ in range(args.steps):
+        _, _, rays, threads = cpu_sample(rows, row_begin)
+        rays_total += rays
+    dt = time.perf_counter() - t0
+    value = rays_total / dt / 1e6
+    sample = f"rows {row_begin}..{row_begin + rows} of the {W}x{H} frame per step ({rows * W} rays x {N_SPHERES} spheres)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU restatement of compute_shader.wgsl (oracle/rt_oracle.cpp, g++ -O2 -ffp-contract=off, OpenMP); "
+                "the reference shader via wgpu/lavapipe is unavailable on this box",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import gpu_ray_tracing_b200 as rt
+    import scenes
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log(f"note: WORLD_SIZE={world} but --gpus {args.gpus}; using WORLD_SIZE")
+    if rt.device_count() < 1:
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback): " + rt.lib().rt_last_error().decode())
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    K, Wm = args.steps, max(args.warmup, 3)
+    scene = scenes.random_scene(N_SPHERES)
+    # one camera per (step, rank): the same pose with a re-rolled random_seed (camera.rs:346) — depth-1
+    # cost is pose independent (every ray tests every sphere), so steps are comparable
+    def cam_for(step):
+        seed = ((step * world + rank) * 2654435761 % (1 << 24)) / float(1 << 24)
+        return scenes.camera(W, H, 1, 1, random_seed=seed)
+
+    r = rt.Renderer(W, H, device=local_rank)
+    r.set_scene(scene)
+    r.init()
+    ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", local_rank))
+
+    # ---- parity spot check against the oracle (rank 0, 16 rows of the real workload) ----------
+    parity = None
+    if rank == 0:
+        import oracle_lib as ol
+        cam = cam_for(0)
+        r.update(cam)
+        gpu_rows = r.read_accum()[1072:1088]
+        cpu_rows, _ = ol.oracle_update(cam, scene, W, H, row_begin=1072, row_count=16)
+        parity = ol.compare_images(cpu_rows, gpu_rows)
+        parity["checked"] = "rows 1072..1088 of the benchmark frame vs oracle"
+        r.init()
+
+    send = [torch.empty((H, W, 4), dtype=torch.uint8, device="cuda") for _ in range(2)] if world > 1 else None
+    recv = [[torch.empty((H, W, 4), dtype=torch.uint8, device="cuda") for _ in range(world)] for _ in range(2)] \
+        if (world > 1 and rank == 0) else None
+    works = [None, None]
+
+    def step(i):
+        r.update(cam_for(i))
+        if world > 1:
+            b = i & 1
+            with torch.cuda.stream(ext):
+                if works[b] is not None:
+                    works[b].wait()            # the send buffer of step i-2 is free again
+                r.quantize_into(send[b].data_ptr())
+                works[b] = dist.gather(send[b], recv[b] if rank == 0 else None, dst=0, async_op=True)
+
+    def drain():
+        with torch.cuda.stream(ext):
+            for b in (0, 1):
+                if works[b] is not None:
+                    works[b].wait()
+                    works[b] = None
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for i in range(Wm):
+        step(i)
+    drain()
+    r.synchronize()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    r.reset_counters()
+    launches0 = r.kernel_launches()
+    t_region = time.perf_counter()
+    r.timer_begin()
+    for i in range(K):
+        step(Wm + i)
+    drain()                                    # the end event is ordered after the last gather
+    ms = r.timer_end()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    wall_ms = (time.perf_counter() - t_region) * 1e3
+    clocks = sampler.stop(since=t_region) if rank == 0 else None
+    rays = r.rays_traced()
+    launches = r.kernel_launches() - launches0
+    stats = torch.tensor([ms, float(rays), float(launches), wall_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        mx = stats.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = stats.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms, rays, launches, wall_ms = mx[0].item(), int(sm[1].item()), int(sm[2].item()), mx[3].item()
+    value = rays / (ms * 1e-3) / 1e6
+
+    # ---- dominant kernel alone (roofline): CUDA events on the launching stream ------------------
+    n_k = 20
+    cam = cam_for(0)
+    r.update(cam)
+    r.synchronize()
+    r.timer_begin()
+    for _ in range(n_k):
+        r.update(cam)
+    kernel_ms = r.timer_end() / n_k
+    flops_per_launch = float(W) * H * N_SPHERES * FLOP_PER_TEST
+    achieved_tf = flops_per_launch / (kernel_ms * 1e-3) / 1e12
+
+    # ---- end to end through the C ABI with HOST buffers ----------------------------------------
+    # per step: sphere buffer uploaded from pinned host memory (the reference re-creates its buffers
+    # from host memory every frame, src/lib.rs:151-207), the 176-byte camera uniform rides in the
+    # kernel parameters, and the frame comes back as RGBA8 into pinned host memory.
+    host_spheres = torch.from_numpy(scene.spheres.view(np.uint8).copy()).pin_memory()
+    host_image = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+    K_e2e = max(3, min(K, 50))
+    for i in range(2):
+        r.set_scene_from(host_spheres.data_ptr(), len(scene.spheres), scene.count)
+        r.update(cam_for(i))
+        r.read_rgba8_into(host_image.data_ptr())
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(K_e2e):
+        r.set_scene_from(host_spheres.data_ptr(), len(scene.spheres), scene.count)
+        r.update(cam_for(i))
+        r.read_rgba8_into(host_image.data_ptr())      # synchronous: the image is on the host when it returns
+    e2e_s = time.perf_counter() - t0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = K_e2e * world * W * H / e2e_t.item() / 1e6
+    checksum = int(host_image.view(-1)[::4099].to(torch.int64).sum().item())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: denominators, CPU baseline, the JSON line ---------------------------------------
+    peak_tf, sms = ffma_peak_tflops(local_rank)
+    peaks = measured_peaks()
+    theo_tf = sms * 128 * 2 * (clocks.get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12
+    hbm_bytes = float(W) * H * 16      # reset frames: one float4 store per pixel, nothing read
+    hbm_gbs = hbm_bytes / (kernel_ms * 1e-3) / 1e9
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        # bounded sample: whole frames of the same workload until ~10 s of wall time (>= 2 frames)
+        cpu_rays, dt, frames, threads = 0, 0.0, 0, 1
+        while frames < 2 or (dt < 10.0 and frames < 8):
+            _, t1, r1, threads = cpu_sample(H, 0)
+            cpu_rays += r1
+            dt += t1
+            frames += 1
+        cpu = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+               "sample": f"{frames} full frames of the same workload ({cpu_rays} rays x {N_SPHERES} spheres) in {dt:.1f} s, "
+                         "oracle/rt_oracle.cpp (g++ -O2 -ffp-contract=off) with OpenMP"}
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(world),
+        "roofline": {"bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": achieved_tf / peak_tf, "traffic": None,
+                     "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
+                     "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
+                     "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
+                     "kernel": "update_resident_kernel"},
+        "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
+                "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
+                "algorithmic_bytes_per_launch": hbm_bytes,
+                "note": "one float4 accumulator store per pixel; the kernel is FP32-bound by design (intensity 1152 flop/B)"},
+        "cpu_baseline": cpu,
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(scene.spheres) * 32 + 176),
+                "d2h_bytes_per_step": W * H * 4, "steps": K_e2e,
+                "call": "rt_set_scene + rt_update + rt_read_rgba8 per frame, pinned host buffers", "checksum": checksum},
+        "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
+        "wall_ms_per_step": wall_ms / K,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps == 400:
+            args.steps, args.warmup = 10, 1
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

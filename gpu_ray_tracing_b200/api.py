@@ -129,6 +129,7 @@ _SIGNATURES = {
     "rt_accum_device_ptr": (C.c_int, [_P, C.POINTER(_P)]),
     "rt_rgba8_device_ptr": (C.c_int, [_P, C.POINTER(_P)]),
     "rt_quantize": (C.c_int, [_P]),
+    "rt_quantize_into": (C.c_int, [_P, _P]),
     "rt_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "rt_window": (C.c_int, [_P] + [C.POINTER(C.c_uint32)] * 4),
     "rt_set_kernel_variant": (C.c_int, [_P, C.c_int]),
@@ -291,6 +292,15 @@ class Renderer:
 
     def quantize(self):
         _check(lib().rt_quantize(self._h))
+
+    def quantize_into(self, device_ptr: int):
+        _check(lib().rt_quantize_into(self._h, C.c_void_p(device_ptr)))
+
+    def read_accum_into(self, host_ptr: int):
+        _check(lib().rt_read_accum(self._h, C.c_void_p(host_ptr)))
+
+    def set_scene_from(self, host_ptr: int, buffer_len: int, count: int):
+        _check(lib().rt_set_scene(self._h, C.c_void_p(host_ptr), buffer_len, count))
 
     def rays_traced(self) -> int:
         v = C.c_uint64(0)

@@ -231,6 +231,14 @@ int rt_quantize(RtRenderer* r) {
     return RT_OK;
 }
 
+int rt_quantize_into(RtRenderer* r, void* device_rgba8) {
+    RT_CHECK_HANDLE(r);
+    if (!device_rgba8) return fail(RT_ERR_INVALID_ARG, "device buffer is null");
+    RT_CUDA(rtk::launch_quantize(r->accum, reinterpret_cast<uchar4*>(device_rgba8), r->n_texels, r->stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
 int rt_read_rgba8(RtRenderer* r, uint8_t* host) {
     RT_CHECK_HANDLE(r);
     if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");

@@ -174,6 +174,9 @@ RT_API int rt_kernel_launches(RtRenderer* r, uint64_t* launches);
 RT_API int rt_accum_device_ptr(RtRenderer* r, void** ptr);   /* float4[row_count*width] */
 RT_API int rt_rgba8_device_ptr(RtRenderer* r, void** ptr);   /* uchar4[row_count*width], filled by rt_quantize */
 RT_API int rt_quantize(RtRenderer* r);                       /* accum -> rgba8, on the stream */
+/* Same, written straight into a caller-owned DEVICE buffer of row_count*width uchar4 (e.g. the send
+ * buffer of an NCCL gather).  Asynchronous on the renderer's stream. */
+RT_API int rt_quantize_into(RtRenderer* r, void* device_rgba8);
 RT_API int rt_stream(RtRenderer* r, void** cuda_stream);
 RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
                      uint32_t* row_begin, uint32_t* row_count);
