@@ -135,6 +135,7 @@ _SIGNATURES = {
     "rt_set_kernel_variant": (C.c_int, [_P, C.c_int]),
     "rt_render": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
     "rt_render_frames": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
+    "rt_shard_rows": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "rt_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
     "rt_multi_destroy": (C.c_int, [_P]),
     "rt_multi_set_scene": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32]),
@@ -345,6 +346,13 @@ class Renderer:
         p = C.c_void_p()
         _check(lib().rt_stream(self._h, C.byref(p)))
         return p.value or 0
+
+
+def shard_rows(height: int, n_shards: int, index: int):
+    """(row_begin, row_count) of shard `index` — rt_shard_rows."""
+    b, c = C.c_uint32(0), C.c_uint32(0)
+    _check(lib().rt_shard_rows(height, n_shards, index, C.byref(b), C.byref(c)))
+    return b.value, c.value
 
 
 class MultiRenderer:

@@ -29,6 +29,25 @@ struct RtMultiRenderer {
 
 extern "C" {
 
+int rt_shard_rows(uint32_t height, uint32_t n_shards, uint32_t index, uint32_t* row_begin, uint32_t* row_count) {
+    if (!row_begin || !row_count) return fail(RT_ERR_INVALID_ARG, "null argument");
+    if (n_shards == 0 || index >= n_shards) return fail(RT_ERR_INVALID_ARG, "shard %u of %u", index, n_shards);
+    if (height < n_shards) return fail(RT_ERR_INVALID_ARG, "fewer rows (%u) than shards (%u)", height, n_shards);
+    const uint32_t tiles = (height + 3) / 4;
+    uint32_t r0, r1;
+    if (tiles >= n_shards) {
+        r0 = (uint32_t)((uint64_t)tiles * index / n_shards) * 4;
+        r1 = (index + 1 == n_shards) ? height : (uint32_t)((uint64_t)tiles * (index + 1) / n_shards) * 4;
+    } else {   // fewer 4-row tiles than shards: fall back to single rows
+        r0 = (uint32_t)((uint64_t)height * index / n_shards);
+        r1 = (uint32_t)((uint64_t)height * (index + 1) / n_shards);
+    }
+    if (r1 > height) r1 = height;
+    *row_begin = r0;
+    *row_count = r1 - r0;
+    return RT_OK;
+}
+
 int rt_multi_destroy(RtMultiRenderer* m) {
     if (!m) return RT_OK;
     if (!m->shards.empty()) {
@@ -49,21 +68,14 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
     RtMultiRenderer* m = new (std::nothrow) RtMultiRenderer();
     if (!m) return fail(RT_ERR_OUT_OF_MEMORY, "host allocation failed");
     m->width = width; m->height = height;
-    // contiguous row blocks, sized in multiples of the 4-row warp tile where possible
-    const uint32_t tiles = (height + 3) / 4;
-    uint32_t row = 0;
     for (uint32_t i = 0; i < n_devices; ++i) {
-        uint32_t t0 = (uint32_t)((uint64_t)tiles * i / n_devices), t1 = (uint32_t)((uint64_t)tiles * (i + 1) / n_devices);
-        uint32_t r0 = t0 * 4, r1 = (i + 1 == n_devices) ? height : t1 * 4;
-        if (r1 > height) r1 = height;
-        if (r1 <= r0) { rt_multi_destroy(m); return fail(RT_ERR_INVALID_ARG, "image too small to shard %u ways", n_devices); }
+        uint32_t r0 = 0, rows = 0;
+        int rc = rt_shard_rows(height, n_devices, i, &r0, &rows);
         RtRenderer* s = nullptr;
-        int rc = rt_create_window(devices[i], width, height, r0, r1 - r0, &s);
+        if (rc == RT_OK) rc = rt_create_window(devices[i], width, height, r0, rows, &s);
         if (rc != RT_OK) { rt_multi_destroy(m); return rc; }
         m->shards.push_back(s);
-        row = r1;
     }
-    (void)row;
     // peer access devices[0] <-> devices[i]; cudaMemcpyPeerAsync falls back to staging when absent
     for (uint32_t i = 1; i < n_devices; ++i) {
         if (devices[i] == devices[0]) continue;

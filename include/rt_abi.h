@@ -203,6 +203,9 @@ RT_API int rt_render_frames(int device, const GpuSphere* spheres, uint32_t count
  * One image sharded by row tiles over several devices of one host, scene replicated,
  * result gathered to devices[0] by peer copy over NVLink.
  * ------------------------------------------------------------------------------------- */
+/* The row block shard `index` of `n_shards` owns: contiguous, multiples of the 4-row warp tile except the
+ * last.  Pure host arithmetic (usable without a device; also what a multi-process host uses per rank). */
+RT_API int rt_shard_rows(uint32_t height, uint32_t n_shards, uint32_t index, uint32_t* row_begin, uint32_t* row_count);
 RT_API int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height,
                            RtMultiRenderer** out);
 RT_API int rt_multi_destroy(RtMultiRenderer* m);

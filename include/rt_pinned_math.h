@@ -14,7 +14,7 @@
  * Every other operation of the shader (+ - * / sqrt, comparisons, integer hashing, conversions)
  * is exactly specified by IEEE-754 and needs no pinning.
  *
- * The definitions are within 2 ulp of the correctly rounded result over the argument ranges
+ * sin and cos are within 2 ulp (pow5: 3 ulp) of the correctly rounded result over the argument ranges
  * the shader produces (tests/test_oracle.py checks them against libm), far inside the WGSL
  * tolerance.  oracle/ can also be built against libm (-DRT_ORACLE_LIBM) to measure how far an
  * implementation with different builtin rounding lands from the pinned one.
