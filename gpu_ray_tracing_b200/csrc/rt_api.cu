@@ -94,7 +94,8 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     r->sm_count = prop.multiProcessorCount;
     if (e == cudaSuccess) e = cudaMalloc(&r->accum, r->n_texels * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&r->rgba8, r->n_texels * sizeof(uchar4));
-    if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMalloc(&r->first_hit, r->n_texels * sizeof(float2));
+    if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, 2 * sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMalloc(&r->counters, 2 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
@@ -122,6 +123,8 @@ int rt_destroy(RtRenderer* r) {
     cudaFree(r->rgba8);
     cudaFree(r->spheres);
     cudaFree(r->geom);
+    cudaFree(r->prim);
+    cudaFree(r->first_hit);
     cudaFree(r->tile_counter);
     cudaFree(r->counters);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
@@ -143,9 +146,11 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
         RT_CUDA(cudaStreamSynchronize(r->stream));
         cudaFree(r->spheres); r->spheres = nullptr; r->sphere_capacity = 0;
         cudaFree(r->geom); r->geom = nullptr; r->geom_capacity = 0;
+        cudaFree(r->prim); r->prim = nullptr;
         RT_CUDA(cudaMalloc(&r->spheres, (size_t)cap_needed * sizeof(GpuSphere)));
         r->sphere_capacity = cap_needed;
         RT_CUDA(cudaMalloc(&r->geom, (size_t)pad_needed * sizeof(float4)));
+        RT_CUDA(cudaMalloc(&r->prim, (size_t)pad_needed * sizeof(float4)));
         r->geom_capacity = pad_needed;
     }
     if (buffer_len > 0)
@@ -179,8 +184,11 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
     p.tile_counter = r->tile_counter;
     p.counters = r->counters;
-    RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream));
-    r->launches += 1;
+    p.prim = r->prim;
+    p.first_hit = r->first_hit;
+    int launched = 0;
+    RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched));
+    r->launches += (uint64_t)launched;
     return RT_OK;
 }
 
@@ -310,7 +318,7 @@ int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height, uint32_t* row_be
 }
 int rt_set_kernel_variant(RtRenderer* r, int variant) {
     if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
-    if (variant < 0 || variant > 3) return fail(RT_ERR_INVALID_ARG, "variant %d not in 0..3", variant);
+    if (variant < 0 || variant > 4) return fail(RT_ERR_INVALID_ARG, "variant %d not in 0..4", variant);
     r->variant = variant;
     return RT_OK;
 }

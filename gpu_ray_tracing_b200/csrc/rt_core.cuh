@@ -12,6 +12,7 @@
 
 #include <stdint.h>
 #include <math.h>
+#include <string.h>
 
 #include "../../include/rt_abi.h"
 #include "../../include/rt_pinned_math.h"
@@ -232,6 +233,106 @@ RT_DEV float broad_record_k(const GpuSphere& s) {
     float f = (float)k;
     if ((double)f > k) f = nextafterf(f, -INFINITY);
     return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Common-origin broad phase.  Primary rays start at cam.center = Oc
+// (pinhole, compute_shader.wgsl:319) or on the rim of the defocus disk around it (:327-331), i.e.
+// at O = Oc + e with |e| <= rho.  A ray from O that comes within R of a sphere centre C at some
+// t > 0 has its parallel through Oc come within R + rho of C at the same t, so with
+//     oc = C - Oc,  u = d / |d|,  R^2 = r^2 + kappa S  (kappa S absorbs every rounding of the
+//     reference's own discriminant, S = |oc|^2 + r^2 + rho^2),  c' = |oc|^2 - (R + rho)^2 > 0,
+// a hit needs  oc.u >= sqrt(c').  The test is ONE 3-term dot product against a per-sphere,
+// per-frame record (oc, -q), q = sqrt(c') minus the slack for the broad phase's own rounding:
+//     candidate  <=>  sign bit of fma(ocx, ux, fma(ocy, uy, fma(ocz, uz, -q))) clear.
+// 3 FFMA per (ray, sphere).  Spheres the bound does not cover (Oc inside or within the slack of
+// the inflated sphere, non-finite or extreme magnitudes) get the record (0, 0, 0, +1): always a
+// candidate.  Rays outside the magnitude window of primary_arm() are never candidates and must be
+// traced exactly by the caller.
+// ---------------------------------------------------------------------------------------------
+#define RT_PRIMARY_MAG 1073741824.0 /* 2^30: |oc_i|, |r|, |Oc_i|, rho window */
+
+RT_DEV float rt_double2float_rd(double v) {
+#if defined(__CUDA_ARCH__)
+    return __double2float_rd(v);
+#else
+    float f = (float)v;
+    if ((double)f > v) f = nextafterf(f, -INFINITY);
+    return f;
+#endif
+}
+
+// Upper bound of |O - cam.center| over the primary rays of this camera, or a negative value when
+// the primary pass must not be used (non-finite or extreme camera).  Pinhole: 0.  Defocus:
+// e = px ddu + py ddv with |(px, py)| = 1 up to rounding, so |e|^2 <= lambda_max of the Gram matrix
+// of (ddu, ddv); the float evaluation of O adds a few ulps of |Oc| + |e|.
+RT_DEV double primary_rho(const SceneCamera& cam) {
+    const double lim = RT_PRIMARY_MAG;
+    const double cx = cam.center.x, cy = cam.center.y, cz = cam.center.z;
+    if (!(fabs(cx) <= lim && fabs(cy) <= lim && fabs(cz) <= lim)) return -1.0;
+    if (!(cam.defocus_angle > 0.0f)) return (cam.defocus_angle <= 0.0f) ? 0.0 : -1.0;   // NaN angle: WGSL select() takes the pinhole branch, but stay out
+    const double ux = cam.defocus_disk_u.x, uy = cam.defocus_disk_u.y, uz = cam.defocus_disk_u.z;
+    const double vx = cam.defocus_disk_v.x, vy = cam.defocus_disk_v.y, vz = cam.defocus_disk_v.z;
+    const double A = ux * ux + uy * uy + uz * uz, B = vx * vx + vy * vy + vz * vz, C = ux * vx + uy * vy + uz * vz;
+    const double half = 0.5 * (A - B);
+    const double lam = 0.5 * (A + B) + sqrt(half * half + C * C);
+    const double cmax = fmax(fmax(fabs(cx), fabs(cy)), fabs(cz));
+    const double rho = sqrt(lam) * (1.0 + 1e-5) + 4.76837158203125e-07 /* 2^-21 */ * (cmax + sqrt(lam));
+    if (!(rho <= lim)) return -1.0;
+    return rho;
+}
+
+// Record of sphere `s` for rays starting within `rho` of `o`.  out = (ocx, ocy, ocz, -q).
+RT_DEV void primary_record(const GpuSphere& s, f3 o, double rho, float out[4]) {
+    const double ocx = (double)s.position.x - (double)o.x, ocy = (double)s.position.y - (double)o.y,
+                 ocz = (double)s.position.z - (double)o.z, r = fabs((double)s.radius);
+    const double cc = ocx * ocx + ocy * ocy + ocz * ocz, rr = r * r, S = cc + rr + rho * rho;
+    const double R = sqrt(rr + RT_KAPPA * S) + rho;
+    const double cp = cc - R * R * (1.0 + 9.5367431640625e-07 /* 2^-20 */);
+    const double m = fmax(fmax(fabs(ocx), fabs(ocy)), fmax(fabs(ocz), r));
+    // written so that a NaN anywhere fails the test
+    bool ok = (m <= RT_PRIMARY_MAG) && (S >= 8.673617379884035e-19 /* 2^-60 */) && (cp > 0.0);
+    double q = 0.0;
+    if (ok) {
+        q = sqrt(cp) * (1.0 - 9.5367431640625e-07) - 3.814697265625e-06 /* 2^-18 */ * sqrt(S);
+        ok = q > 0.0;
+    }
+    if (!ok) {
+        out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = 1.0f;
+        return;
+    }
+    out[0] = (float)ocx; out[1] = (float)ocy; out[2] = (float)ocz;
+    out[3] = -rt_double2float_rd(q);
+}
+
+// Record of a padding slot: never a candidate.
+RT_DEV void primary_record_pad(float out[4]) { out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = -1.0f; }
+
+// Unit direction of a ray for the common-origin test.  Returns false (and u = 0) when |d|^2 is
+// outside [2^-40, 2^40] or not finite: such a ray has to be traced with the exact test only.
+RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz) {
+    const bool ok = (a >= 9.094947017729282e-13f) && (a <= 1099511627776.0f);
+    if (!ok) {
+        *ux = 0.0f; *uy = 0.0f; *uz = 0.0f;
+        return false;
+    }
+    const float inv = 1.0f / sqrtf(a);
+    *ux = d.x * inv; *uy = d.y * inv; *uz = d.z * inv;
+    return true;
+}
+
+// h' of one (ray, record): candidate <=> sign bit clear.
+RT_DEV float primary_h(float rx, float ry, float rz, float rw, float ux, float uy, float uz) {
+    return fmaf(rx, ux, fmaf(ry, uy, fmaf(rz, uz, rw)));
+}
+RT_DEV bool primary_candidate(float h) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_int(h) >= 0;
+#else
+    int32_t b;
+    memcpy(&b, &h, 4);
+    return b >= 0;
+#endif
 }
 
 }  // namespace rtc

@@ -18,6 +18,8 @@ struct RtRenderer {
     uint32_t sphere_capacity = 0;
     float4* geom = nullptr;               // broad-phase records
     uint32_t geom_capacity = 0;
+    float4* prim = nullptr;               // per-frame common-origin records (same padded length as geom)
+    float2* first_hit = nullptr;          // (t, sphere index) per texel, written by the primary pass
     uint32_t n_spheres = 0;
     bool has_scene = false;
     unsigned int* tile_counter = nullptr;

@@ -270,6 +270,36 @@ __device__ __forceinline__ void end_tile(const UpdateParams& P, const Lanes& L, 
     }
 }
 
+// Bounce 0 when the primary pass already traced the ray: take (t, index) from first_hit and park the
+// ray (not alive) for the duration of the scan that the untraced rays (index code -2) still need.
+// Returns whether this thread has a ray left to scan; `pre` marks the parked rays.
+__device__ __forceinline__ bool adopt_first_hits(const UpdateParams& P, int row, const int (&px)[kPix], Lanes& L,
+                                                 bool (&pre)[kPix]) {
+    bool todo = false;
+#pragma unroll
+    for (int p = 0; p < kPix; ++p) {
+        pre[p] = false;
+        if (L.alive[p]) {
+            const float2 fh = P.first_hit[(size_t)row * P.width + px[p]];
+            const int code = __float_as_int(fh.y);
+            if (code != -2) {
+                L.best_t[p] = fh.x;
+                L.best_i[p] = code;
+                L.alive[p] = false;
+                pre[p] = true;
+            } else {
+                todo = true;
+            }
+        }
+    }
+    return todo;
+}
+__device__ __forceinline__ void unpark(Lanes& L, const bool (&pre)[kPix]) {
+#pragma unroll
+    for (int p = 0; p < kPix; ++p)
+        if (pre[p]) L.alive[p] = true;
+}
+
 __device__ __forceinline__ void flush_counters(const UpdateParams& P, uint32_t rays, uint32_t exact_tests, int lane) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -319,12 +349,197 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
                 rays += L.alive[p] ? 1u : 0u;
             }
             if (!__any_sync(kFull, mine)) break;
-            scan_spheres(s_geom, n_pad, 0, P.spheres, P.n_spheres, L, exact_tests);
+            if (bounce == 0 && P.first_hit != nullptr) {
+                bool pre[kPix];
+                const bool todo = adopt_first_hits(P, row, px, L, pre);
+                if (__any_sync(kFull, todo)) scan_spheres(s_geom, n_pad, 0, P.spheres, P.n_spheres, L, exact_tests);
+                unpark(L, pre);
+            } else {
+                scan_spheres(s_geom, n_pad, 0, P.spheres, P.n_spheres, L, exact_tests);
+            }
             after_traversal(P, bounce, L, J);
         }
         end_tile(P, L, J, row, px, reset);
     }
     flush_counters(P, rays, exact_tests, lane);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Common-origin primary pass (variant 4).  For a pinhole camera every
+// primary ray starts at cam.center, so the broad phase is ONE 3-term dot product per (ray, sphere)
+// against the per-frame record (C - O, -q) written by prep_primary_kernel: candidate <=> sign bit
+// of h' clear (rtc::primary_h).  A thread owns a 1 x 8 pixel strip (4 FFMA2 pairs), a warp a
+// 32 x 8 tile; per record: 12 FFMA2 + 4 LOP3 (sign bits AND-ed).  Candidates go through the
+// reference quadratic in index order (narrow phase), so the (t, index) written to first_hit is
+// exactly what sphere_list_hit returns for the primary ray.  Shading and the texel update stay in
+// the update kernel, which skips its own first traversal when first_hit is present.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+struct PrimLanes {
+    float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
+    float best_t[kPrimRays];
+    int best_i[kPrimRays];
+    uint32_t alive;   // bit p: ray p is traced here
+};
+
+__device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
+
+// Exact tests of records [slot, slot + count) for the rays whose sign test passes.
+__device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, const float* __restrict__ s_d, int slot,
+                                         int count, const UpdateParams& P, PrimLanes& L, uint32_t& exact_tests) {
+#pragma unroll 1
+    for (int u = 0; u < count; ++u) {
+        const int idx = slot + u;
+        if ((uint32_t)idx >= P.n_spheres) break;   // padding
+        const float4 rec = s_rec[idx];
+        uint32_t cand = 0;
+#pragma unroll
+        for (int p = 0; p < kPrimRays; ++p) {
+            const float h = rtc::primary_h(rec.x, rec.y, rec.z, rec.w, ray_half(L.ux[p >> 1], p), ray_half(L.uy[p >> 1], p),
+                                           ray_half(L.uz[p >> 1], p));
+            cand |= rtc::primary_candidate(h) ? (1u << p) : 0u;
+        }
+        cand &= L.alive;
+        if (!cand) continue;
+        const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
+        const f3 center = rtc::mk(g.x, g.y, g.z);
+#pragma unroll
+        for (int p = 0; p < kPrimRays; ++p) {
+            if (cand & (1u << p)) {
+                ++exact_tests;
+                const float* dp = s_d + (p * 6) * kBlockThreads;
+                const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+                const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
+                float root;
+                if (rtc::sphere_root(origin, d, rtc::dot(d, d), center, g.w, kTMin, L.best_t[p], &root)) {
+                    L.best_t[p] = root;
+                    L.best_i[p] = idx;
+                }
+            }
+        }
+    }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_dyn[];
+    const int n_pad = (int)((P.n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll);
+    float4* s_rec = s_dyn;                                                    // [n_pad + kPrimTail]
+    float* s_d = reinterpret_cast<float*>(s_dyn + n_pad + kPrimTail) + threadIdx.x;   // [kPrimRays][6][kBlockThreads] (d, o), this thread's column
+    for (int i = threadIdx.x; i < n_pad + kPrimTail; i += kBlockThreads) s_rec[i] = __ldg(&P.prim[i]);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
+    const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
+    const uint32_t rec_base = (uint32_t)__cvta_generic_to_shared(s_rec);
+    uint32_t exact_tests = 0;
+
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
+        tile = __shfl_sync(kFull, tile, 0);
+        if (tile >= n_tiles) break;
+        const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
+        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+
+        // primary rays of the strip (get_ray, compute_shader.wgsl:305-325); directions parked in shared memory
+        PrimLanes L;
+        L.alive = 0;
+        uint32_t untraced = 0;   // sampling rays outside primary_arm's window: left to the update kernel
+#pragma unroll 1
+        for (int p = 0; p < kPrimRays; ++p) {
+            const int row = row0 + p;
+            f3 d = rtc::mk(0.0f, 0.0f, 0.0f), o = d;
+            if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+                uint32_t n = 0;
+                if (!reset) n = rtc::f2u(P.accum[(size_t)row * P.width + x].w);
+                if (n < spp) {
+                    const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
+                    const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
+                    d = r.d;
+                    o = r.o;
+                    L.alive |= 1u << p;
+                }
+            }
+            float* dp = s_d + (p * 6) * kBlockThreads;
+            dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
+            dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
+        }
+#pragma unroll
+        for (int p = 0; p < kPrimRays; ++p) {
+            const float* dp = s_d + (p * 6) * kBlockThreads;
+            const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+            float ux, uy, uz;
+            const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
+            if (!ok && (L.alive & (1u << p))) {
+                untraced |= 1u << p;
+                L.alive &= ~(1u << p);
+            }
+            const int q = p >> 1;
+            if (p & 1) { L.ux[q].y = ux; L.uy[q].y = uy; L.uz[q].y = uz; }
+            else       { L.ux[q].x = ux; L.uy[q].x = uy; L.uz[q].x = uz; }
+            L.best_t[p] = kTMax;
+            L.best_i[p] = -1;
+        }
+
+        // broad phase over the resident records, kPrimUnroll per iteration, next group prefetched
+        uint32_t addr = rec_base;
+        float4 cur[kPrimUnroll];
+#pragma unroll
+        for (int u = 0; u < kPrimUnroll; ++u) cur[u] = lds128(addr + 16u * u);
+#pragma unroll 1
+        for (int s = 0; s < n_pad; s += kPrimUnroll) {
+            addr += 16u * kPrimUnroll;
+            float4 nxt[kPrimUnroll];
+#pragma unroll
+            for (int u = 0; u < kPrimUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
+            int acc = -1;
+#pragma unroll
+            for (int u = 0; u < kPrimUnroll; ++u) {
+                const float4 sp = cur[u];
+                const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z),
+                             sw = make_float2(sp.w, sp.w);
+#pragma unroll
+                for (int q = 0; q < kPrimRays / 2; ++q) {
+                    const float2 h = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
+                    acc &= __float_as_int(h.x) & __float_as_int(h.y);
+                }
+            }
+            if (acc >= 0) prim_narrow(s_rec, s_d, s, kPrimUnroll, P, L, exact_tests);
+#pragma unroll
+            for (int u = 0; u < kPrimUnroll; ++u) cur[u] = nxt[u];
+        }
+
+        // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
+#pragma unroll
+        for (int p = 0; p < kPrimRays; ++p) {
+            const int row = row0 + p;
+            if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+                const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
+                P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) exact_tests += __shfl_xor_sync(kFull, exact_tests, o);
+    if (lane == 0 && exact_tests) atomicAdd(&P.counters[1], (unsigned long long)exact_tests);
+}
+
+// Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
+__global__ void prep_primary_kernel(const GpuSphere* __restrict__ spheres, float4* __restrict__ prim, uint32_t n,
+                                    uint32_t n_slots, float ox, float oy, float oz, double rho) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_slots) return;
+    float r[4];
+    if (i < n) rtc::primary_record(spheres[i], rtc::mk(ox, oy, oz), rho, r);
+    else rtc::primary_record_pad(r);
+    prim[i] = make_float4(r[0], r[1], r[2], r[3]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -467,8 +682,19 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
                 mine |= L.alive[p];
                 rays += L.alive[p] ? 1u : 0u;
             }
-            const bool warp_alive = __any_sync(kFull, mine);
             if (!__syncthreads_or(mine ? 1 : 0)) break;   // also fences the stages against the previous bounce
+            bool pre[kPix];
+            bool todo = mine;
+            const bool adopt = bounce == 0 && P.first_hit != nullptr;
+            if (adopt) {
+                todo = adopt_first_hits(P, row, px, L, pre);
+                if (!__syncthreads_or(todo ? 1 : 0)) {   // block-uniform: nothing left to scan
+                    unpark(L, pre);
+                    after_traversal(P, bounce, L, J);
+                    continue;
+                }
+            }
+            const bool warp_alive = __any_sync(kFull, todo);
 
             // prologue: chunk 0 -> stage 0
             {
@@ -489,6 +715,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
                     scan_spheres(s_stage + (c & 1) * kStage, cnt, base, P.spheres, P.n_spheres, L, exact_tests);
                 __syncthreads();
             }
+            if (adopt) unpark(L, pre);
             after_traversal(P, bounce, L, J);
         }
         end_tile(P, L, J, row, px, reset);
@@ -499,39 +726,74 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------------
+constexpr uint32_t kPrimResidentMax = 4096;   // (4096 + 8) x 16 B records + 48 KB rays: 2 CTAs per SM
+
+static size_t prim_smem_bytes(uint32_t n_spheres) {
+    const uint32_t n_pad = (n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll;
+    return (size_t)(n_pad + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * 6 * kBlockThreads * sizeof(float);
+}
+
 cudaError_t configure_kernels() {
     cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(primary_hits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)prim_smem_bytes(kPrimResidentMax));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
 }
 
-cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream) {
+bool primary_pass_applies(const UpdateParams& p) {
+    return p.prim != nullptr && p.first_hit != nullptr && p.n_spheres > 0 && p.n_spheres <= kPrimResidentMax &&
+           rtc::primary_rho(p.cam) >= 0.0 && rtc::f2u(p.cam.max_depth) > 0u;
+}
+
+cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
+    UpdateParams p = p_in;
+    int n_launch = 0;
+    const bool primary = (variant == 0 || variant == 4) && primary_pass_applies(p);
+    if (!primary) p.first_hit = nullptr;
+    if (variant == 4) variant = 0;
     if (variant == 0) variant = (p.n_spheres <= kResidentMaxSpheres) ? 2 : 3;
     if (variant == 2 && p.n_spheres > kResidentMaxSpheres) variant = 3;
     if (variant == 1) {
         dim3 grid((p.width + 7) / 8, (p.row_count + 7) / 8);
         update_baseline_kernel<<<grid, 64, 0, stream>>>(p);
+        if (launches) *launches = 1;
         return cudaGetLastError();
     }
-    cudaError_t e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream);
+    cudaError_t e = cudaMemsetAsync(p.tile_counter, 0, 2 * sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
-    if (variant == 2) {
-        const uint32_t warps_needed = p.n_tiles;
-        uint32_t blocks = (warps_needed + 7) / 8;
-        const uint32_t resident = (uint32_t)sm_count * 2u;
+    const uint32_t resident = (uint32_t)sm_count * 2u;
+    if (primary) {
+        e = launch_prep_primary(p.spheres, const_cast<float4*>(p.prim), p.n_spheres, p.cam, stream);
+        if (e != cudaSuccess) return e;
+        const uint32_t tiles = ((p.width + kPrimTileW - 1) / kPrimTileW) * ((p.row_count + kPrimTileH - 1) / kPrimTileH);
+        uint32_t blocks = (tiles + 7) / 8;
         if (blocks > resident) blocks = resident;
-        if (blocks == 0) blocks = 1;
+        primary_hits_kernel<<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        n_launch += 2;
+    }
+    const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
+    uint32_t blocks = (p.n_tiles + 7) / 8;
+    if (blocks > resident) blocks = resident;
+    if (blocks == 0) blocks = 1;
+    if (variant == 2) {
         update_resident_kernel<<<blocks, kBlockThreads, (n_pad + kGeomTail) * sizeof(float4), stream>>>(p);
     } else {
-        uint32_t blocks = (p.n_tiles + 7) / 8;
-        const uint32_t resident = (uint32_t)sm_count * 2u;
-        if (blocks > resident) blocks = resident;
-        if (blocks == 0) blocks = 1;
         update_streamed_kernel<<<blocks, kBlockThreads, 2 * (kChunkSpheres + kGeomTail) * sizeof(float4), stream>>>(p);
     }
+    if (launches) *launches = n_launch + 1;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_prep_primary(const GpuSphere* spheres, float4* prim, uint32_t n, const SceneCamera& cam, cudaStream_t stream) {
+    const uint32_t n_slots = (n + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll + kPrimTail;
+    prep_primary_kernel<<<(n_slots + 255) / 256, 256, 0, stream>>>(spheres, prim, n, n_slots, cam.center.x, cam.center.y,
+                                                                   cam.center.z, rtc::primary_rho(cam));
     return cudaGetLastError();
 }
 

@@ -14,6 +14,12 @@ constexpr int kWarpTileH = 4;
 constexpr int kBlockThreads = 256;  // 8 warps
 constexpr int kChunkSpheres = 2048; // streamed kernel: spheres per shared-memory stage (32 KB)
 constexpr uint32_t kResidentMaxSpheres = 4096;  // 64 KB of shared memory per CTA at most
+// common-origin primary pass: a warp owns a 32 x 8 pixel tile, a thread a 1 x 8 strip
+constexpr int kPrimRays = 8;
+constexpr int kPrimTileW = 32;
+constexpr int kPrimTileH = 8;
+constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
+constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
 
 struct UpdateParams {
     SceneCamera cam;            // 176 B, lands in the kernel parameter constant bank
@@ -24,14 +30,21 @@ struct UpdateParams {
     uint32_t width, height;     // full image
     uint32_t row_begin, row_count;  // window
     uint32_t tiles_x, n_tiles;  // warp tiles over the window
-    unsigned int* tile_counter; // dynamic tile scheduler, zeroed before the launch
+    unsigned int* tile_counter; // dynamic tile schedulers, zeroed before the launch: [0] update, [1] primary pass
+    const float4* prim;         // per-frame common-origin records (oc, -q), padded like geom; null = no primary pass
+    float2* first_hit;          // window texels x (t, bits(sphere index)): nearest hit of the primary ray found by
+                                // the primary pass; index -1 = miss, -2 = not traced (the update kernel scans it)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };
 
 // variant: 1 = baseline (thread per pixel, exact test per sphere from global memory),
 //          2 = tiled broad phase with the scene resident in shared memory,
 //          3 = tiled broad phase streaming sphere chunks through shared memory.
-cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream);
+cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream, int* launches = nullptr);
+bool primary_pass_applies(const UpdateParams& p);
+// variant 4 = common-origin primary pass followed by the update kernel (chosen by variant 0 whenever the camera is
+// a pinhole, defocus_angle <= 0); p.prim / p.first_hit must be set.
+cudaError_t launch_prep_primary(const GpuSphere* spheres, float4* prim, uint32_t n, const SceneCamera& cam, cudaStream_t stream);
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream);
 cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream);
 cudaError_t configure_kernels();   // one-off cudaFuncSetAttribute calls

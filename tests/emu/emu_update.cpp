@@ -18,18 +18,26 @@ using rtc::f3;
 
 extern "C" __attribute__((visibility("default")))
 void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t count, uint32_t width, uint32_t height,
-                uint32_t row_begin, uint32_t row_count, float* accum, uint64_t* stats /* rays, exact, violations */) {
+                uint32_t row_begin, uint32_t row_count, float* accum,
+                uint64_t* stats /* rays, exact, violations, primary rays, untraced */, int variant) {
     (void)height;
     const SceneCamera& cam = *cam_p;
     std::vector<float> gk(count);
     for (uint32_t i = 0; i < count; ++i) gk[i] = rtc::broad_record_k(spheres[i]);
+    // common-origin primary pass: same applicability rule as rtk::primary_pass_applies (variant 0 / 4)
+    const double rho = rtc::primary_rho(cam);
+    const bool primary = (variant == 0 || variant == 4) && count > 0 && count <= 4096 && rho >= 0.0 && rtc::f2u(cam.max_depth) > 0u;
+    std::vector<float> prim(primary ? (size_t)count * 4 : 0);
+    if (primary)
+        for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);
+    uint64_t prim_rays = 0, untraced = 0;
     const uint32_t seed_bits = rtc::f2u(cam.random_seed * 4294967296.0f);
     const uint32_t spp = rtc::f2u(cam.samples_per_pixel);
     const uint32_t max_depth = rtc::f2u(cam.max_depth);
     const bool reset = cam.camera_has_moved > 0.5f;
     uint64_t rays = 0, exact = 0, violations = 0;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced)
 #endif
     for (int64_t row = 0; row < (int64_t)row_count; ++row) {
         const int y_abs = (int)(row_begin + row);
@@ -49,6 +57,26 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                     const rtc::BroadRay b = rtc::broad_arm(r.o, r.d, a);
                     float best_t = 3.4e35f;
                     int best_i = -1;
+                    float pux, puy, puz;
+                    const bool use_primary = primary && i == 0;
+                    if (use_primary && rtc::primary_arm(r.d, a, &pux, &puy, &puz)) {
+                        ++prim_rays;
+                        for (uint32_t s = 0; s < count; ++s) {
+                            const GpuSphere& sp = spheres[s];
+                            const float* rec = &prim[(size_t)s * 4];
+                            float root;
+                            if (rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz))) {
+                                ++exact;
+                                if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, best_t, &root)) {
+                                    best_t = root;
+                                    best_i = (int)s;
+                                }
+                            } else if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root)) {
+                                ++violations;   // rejected a sphere the reference hits inside the original (tmin, tmax)
+                            }
+                        }
+                    } else {
+                    if (use_primary) ++untraced;
                     for (uint32_t s = 0; s < count; ++s) {
                         const GpuSphere& sp = spheres[s];
                         const float g = rtc::broad_g(sp.position.x, sp.position.y, sp.position.z, gk[s], b.ux, b.uy, b.uz,
@@ -64,6 +92,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                             ++violations;   // broad phase rejected a pair whose exact discriminant is >= 0 (or NaN)
                         }
                     }
+                    }
                     if (best_i < 0) break;
                     if (!rtc::scatter(&r, &factor, best_t, spheres[best_i], rtc::hash(seed + 1u + i * 1000u))) {
                         black = true;
@@ -77,5 +106,5 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
             texel[0] = mean.x; texel[1] = mean.y; texel[2] = mean.z; texel[3] = (float)n;
         }
     }
-    if (stats) { stats[0] = rays; stats[1] = exact; stats[2] = violations; }
+    if (stats) { stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced; }
 }

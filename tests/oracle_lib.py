@@ -74,7 +74,7 @@ def emu() -> C.CDLL:
     if _EMU is None:
         build_emu()
         lib = C.CDLL(os.path.join(EMU_DIR, "libemu.so"))
-        lib.emu_update.argtypes = [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P]
+        lib.emu_update.argtypes = [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, _P, C.c_int]
         _EMU = lib
     return _EMU
 
@@ -95,15 +95,21 @@ def oracle_update(camera, scene, width, height, accum=None, row_begin=0, row_cou
     return accum, int(rays)
 
 
-def emu_update(camera, scene, width, height, accum=None, row_begin=0, row_count=None):
-    """The kernels' control flow + arithmetic on the CPU.  Returns (accum, rays, exact_tests, violations)."""
+EMU_STATS = {}
+
+
+def emu_update(camera, scene, width, height, accum=None, row_begin=0, row_count=None, variant=0):
+    """The kernels' control flow + arithmetic on the CPU.  Returns (accum, rays, exact_tests, violations);
+    EMU_STATS holds the primary-pass counters of the last call.  variant as rt_set_kernel_variant (0/4 use the
+    common-origin primary pass when it applies, 2 the general broad phase from bounce 0)."""
     if row_count is None:
         row_count = height - row_begin
     if accum is None:
         accum = np.zeros((row_count, width, 4), dtype=np.float32)
-    stats = np.zeros(3, dtype=np.uint64)
+    stats = np.zeros(5, dtype=np.uint64)
     emu().emu_update(C.byref(camera), _p(scene.spheres), scene.count, width, height, row_begin, row_count,
-                     _p(accum), _p(stats))
+                     _p(accum), _p(stats), variant)
+    EMU_STATS.update(primary_rays=int(stats[3]), untraced=int(stats[4]))
     return accum, int(stats[0]), int(stats[1]), int(stats[2])
 
 

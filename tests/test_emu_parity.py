@@ -18,11 +18,14 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("variant", [0, 2], ids=["primary-pass", "general"])
 @pytest.mark.parametrize("name,make,W,H,kw", CASES, ids=[c[0] for c in CASES])
-def test_emulated_kernel_matches_oracle(name, make, W, H, kw):
+def test_emulated_kernel_matches_oracle(name, make, W, H, kw, variant):
     scene, cam = make(), scenes.camera(W, H, **kw)
     cpu, rays = ol.oracle_update(cam, scene, W, H)
-    emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H)
+    emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
+    if variant == 0 and scene.count <= 4096:
+        assert ol.EMU_STATS["primary_rays"] == W * H and ol.EMU_STATS["untraced"] == 0
     rep = ol.compare_images(cpu, emu)
     print(name, rep, "exact tests per ray: %.2f of %d spheres" % (exact / max(rays, 1), scene.count))
     assert violations == 0
@@ -64,6 +67,7 @@ def test_broad_phase_is_conservative_on_adversarial_geometry():
         W, H = 72, 40
         cam = scenes.camera(W, H, max_depth=6, spp=500, look_from=look_from, fov=60.0)
         cpu, rays = ol.oracle_update(cam, scene, W, H)
-        emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H)
-        assert violations == 0 and rays == rays_e
-        assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))
+        for variant in (0, 2):
+            emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
+            assert violations == 0 and rays == rays_e
+            assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))

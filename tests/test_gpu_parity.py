@@ -31,7 +31,7 @@ def assert_parity(gpu, cpu, what):
     assert rep["bit_identical"], (what, rep)
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("depth", [1, 30])
 def test_default_scene_720p(variant, depth):
     """BASELINE config 1: repo default scene at 1280x720, first frame."""
@@ -43,7 +43,7 @@ def test_default_scene_720p(variant, depth):
     assert_parity(gpu, cpu, f"default 720p depth {depth} variant {variant}")
 
 
-@pytest.mark.parametrize("variant", [2, 3])
+@pytest.mark.parametrize("variant", [2, 3, 4])
 def test_default_scene_4k_depth1(variant):
     """BASELINE config 2: default scene at 3840x2160 (layout + tolerance check)."""
     W, H = 3840, 2160
@@ -54,11 +54,12 @@ def test_default_scene_4k_depth1(variant):
     assert_parity(gpu, cpu, f"default 4K variant {variant}")
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3])
-def test_random_1024_spheres(variant):
-    """BASELINE config 3 scene at a size the oracle finishes in seconds."""
+@pytest.mark.parametrize("defocus", [None, 0.0])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
+def test_random_1024_spheres(variant, defocus):
+    """BASELINE config 3 scene at a size the oracle finishes in seconds (default camera, and a pinhole)."""
     W, H = 960, 540
-    scene, cam = scenes.random_scene(1024), scenes.camera(W, H, max_depth=1, spp=1)
+    scene, cam = scenes.random_scene(1024), scenes.camera(W, H, max_depth=1, spp=1, defocus_angle=defocus)
     cpu, _ = ol.oracle_update(cam, scene, W, H)
     gpu, rays, exact = gpu_update(scene, [cam], W, H, variant)
     assert rays == W * H
@@ -88,7 +89,7 @@ def test_ragged_sizes_and_windows():
     for (W, H) in ((33, 7), (1, 1), (250, 131)):
         cam = scenes.camera(W, H, max_depth=4, spp=2)
         cpu, _ = ol.oracle_update(cam, scene, W, H)
-        for variant in (1, 2, 3):
+        for variant in (1, 2, 3, 4):
             gpu, _, _ = gpu_update(scene, [cam], W, H, variant)
             assert_parity(gpu, cpu, f"{W}x{H} variant {variant}")
     W, H = 250, 131

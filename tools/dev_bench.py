@@ -42,10 +42,11 @@ if __name__ == "__main__":
     W, H = 3840, 2160
     for name, scene, cam in (
         ("random1024 depth1", scenes.random_scene(1024), scenes.camera(W, H, 1, 1)),
+        ("random1024 d1 pinhole", scenes.random_scene(1024), scenes.camera(W, H, 1, 1, defocus_angle=0.0)),
         ("default depth1", scenes.default_scene(), scenes.camera(W, H, 1, 1)),
         ("random1024 depth30", scenes.random_scene(1024), scenes.camera(W, H, 30, 500)),
     ):
-        for variant in (2, 3, 1):
+        for variant in (4, 2, 3, 1):
             iters = 20 if variant != 1 else 3
             ms, rays, exact = time_variant(scene, cam, W, H, variant, iters)
             n = scene.count

@@ -97,6 +97,28 @@ __global__ void __launch_bounds__(256) scan_kernel(const float4* __restrict__ ge
                     }
                 }
                 any = (FORM == 3) ? (acc >= 0) : !(m < 0.0f);
+            } else if (FORM == 5 || FORM == 6) {
+                // 5: scalar FFMA for every ray; 6: pairs [0, PAIRS/2) packed, the rest scalar.  Sign bits AND-ed.
+                int acc = -1;
+                constexpr int kPacked = (FORM == 6) ? PAIRS / 2 : 0;
+#pragma unroll
+                for (int u = 0; u < UNROLL; ++u) {
+                    const float4 sp = cur[u];
+                    const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z),
+                                 sw = make_float2(sp.w, sp.w);
+#pragma unroll
+                    for (int q = 0; q < PAIRS; ++q) {
+                        if (q < kPacked) {
+                            const float2 h = __ffma2_rn(sx, ux[q], __ffma2_rn(sy, uy[q], __ffma2_rn(sz, uz[q], sw)));
+                            acc &= __float_as_int(h.x) & __float_as_int(h.y);
+                        } else {
+                            const float h0 = fmaf(sp.x, ux[q].x, fmaf(sp.y, uy[q].x, fmaf(sp.z, uz[q].x, sp.w)));
+                            const float h1 = fmaf(sp.x, ux[q].y, fmaf(sp.y, uy[q].y, fmaf(sp.z, uz[q].y, sp.w)));
+                            acc &= __float_as_int(h0) & __float_as_int(h1);
+                        }
+                    }
+                }
+                any = acc >= 0;
             } else {
 #pragma unroll
                 for (int u = 0; u < UNROLL; ++u) {
@@ -161,9 +183,9 @@ int main() {
     cudaMemcpy(geom, hg, (n + 16) * 16, cudaMemcpyHostToDevice); cudaMemcpy(dirs, hd, 4096 * 6 * 4, cudaMemcpyHostToDevice);
 #define RUN(F, P, U, B) run<F, P, U>("form " #F " pairs " #P " unroll " #U, geom, dirs, out, n, sms, B)
     for (int bps = 2; bps <= 4; ++bps) {
-        RUN(0, 4, 4, bps); RUN(1, 4, 4, bps); RUN(2, 4, 8, bps);
-        RUN(3, 2, 4, bps); RUN(3, 2, 8, bps); RUN(3, 4, 2, bps); RUN(3, 4, 4, bps); RUN(3, 4, 8, bps); RUN(3, 8, 2, bps); RUN(3, 8, 4, bps);
-        RUN(4, 2, 4, bps); RUN(4, 2, 8, bps); RUN(4, 4, 2, bps); RUN(4, 4, 4, bps); RUN(4, 4, 8, bps); RUN(4, 8, 2, bps); RUN(4, 8, 4, bps);
+        RUN(3, 4, 4, bps); RUN(3, 4, 8, bps);
+        RUN(5, 2, 4, bps); RUN(5, 2, 8, bps); RUN(5, 4, 2, bps); RUN(5, 4, 4, bps); RUN(5, 4, 8, bps); RUN(5, 8, 2, bps);
+        RUN(6, 2, 4, bps); RUN(6, 2, 8, bps); RUN(6, 4, 2, bps); RUN(6, 4, 4, bps); RUN(6, 4, 8, bps); RUN(6, 8, 2, bps);
     }
     return 0;
 }
