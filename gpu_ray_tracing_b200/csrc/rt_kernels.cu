@@ -85,6 +85,22 @@ __device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
     L.alive[p] = true;
 }
 
+// A ray whose first traversal has already been done by the primary pass: only what scatter() and the
+// sky colour need.  It is armed later if it turns out to be untraced (adopt_first_hits).
+__device__ __forceinline__ void park_ray(Lanes& L, int p, f3 o, f3 d) {
+    L.dx[p] = d.x; L.dy[p] = d.y; L.dz[p] = d.z;
+    L.ox[p] = o.x; L.oy[p] = o.y; L.oz[p] = o.z;
+    const int q = p >> 1;
+    L.a[p] = 1.0f;
+    half(L.mox[q], p) = 0.0f; half(L.moy[q], p) = 0.0f; half(L.moz[q], p) = 0.0f;
+    half(L.ux[q], p) = 0.0f; half(L.uy[q], p) = 0.0f; half(L.uz[q], p) = 0.0f;
+    half(L.h0[q], p) = 0.0f;
+    L.thr[p] = __int_as_float(0x7f800000);
+    L.best_t[p] = kTMax;
+    L.best_i[p] = -1;
+    L.alive[p] = true;
+}
+
 __device__ __forceinline__ void idle_ray(Lanes& L, int p) {
     const int q = p >> 1;
     L.dx[p] = L.dy[p] = L.dz[p] = 0.0f;
@@ -210,7 +226,8 @@ __device__ __forceinline__ void begin_tile(const UpdateParams& P, uint32_t tile,
             const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
             rtc::Ray r = rtc::get_ray(P.cam, px[p], y_abs, seed, seed_bits);
             J.bseed[p] = seed + 1u;
-            arm_ray(L, p, r.o, r.d);
+            if (P.first_hit != nullptr) park_ray(L, p, r.o, r.d);
+            else arm_ray(L, p, r.o, r.d);
         } else {
             J.bseed[p] = 0u;
             idle_ray(L, p);
@@ -219,7 +236,7 @@ __device__ __forceinline__ void begin_tile(const UpdateParams& P, uint32_t tile,
 }
 
 // After a traversal: miss -> the ray leaves for the sky; hit -> scatter (compute_shader.wgsl:267-290).
-__device__ __forceinline__ void after_traversal(const UpdateParams& P, uint32_t bounce, Lanes& L, PixelJob& J) {
+__device__ __forceinline__ void after_traversal(const UpdateParams& P, uint32_t bounce, bool last, Lanes& L, PixelJob& J) {
 #pragma unroll
     for (int p = 0; p < kPix; ++p) {
         if (!L.alive[p]) continue;
@@ -239,6 +256,10 @@ __device__ __forceinline__ void after_traversal(const UpdateParams& P, uint32_t 
             J.black[p] = true;
             L.alive[p] = false;
             L.thr[p] = __int_as_float(0x7f800000);
+            L.dx[p] = r.d.x; L.dy[p] = r.d.y; L.dz[p] = r.d.z;
+        } else if (last) {
+            // no further traversal: keep the scattered direction for the sky colour (compute_shader.wgsl:293-296)
+            L.alive[p] = false;
             L.dx[p] = r.d.x; L.dy[p] = r.d.y; L.dz[p] = r.d.z;
         } else {
             arm_ray(L, p, r.o, r.d);
@@ -288,6 +309,7 @@ __device__ __forceinline__ bool adopt_first_hits(const UpdateParams& P, int row,
                 L.alive[p] = false;
                 pre[p] = true;
             } else {
+                arm_ray(L, p, origin_of(L, p), rtc::mk(L.dx[p], L.dy[p], L.dz[p]));
                 todo = true;
             }
         }
@@ -357,7 +379,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
             } else {
                 scan_spheres(s_geom, n_pad, 0, P.spheres, P.n_spheres, L, exact_tests);
             }
-            after_traversal(P, bounce, L, J);
+            after_traversal(P, bounce, bounce + 1u >= max_depth, L, J);
         }
         end_tile(P, L, J, row, px, reset);
     }
@@ -376,6 +398,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
 // ---------------------------------------------------------------------------------------------
 namespace {
 
+constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, then (best_t, best_i) for the fused epilogue
+
 struct PrimLanes {
     float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
     float best_t[kPrimRays];
@@ -385,21 +409,28 @@ struct PrimLanes {
 
 __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
 
-// Exact tests of records [slot, slot + count) for the rays whose sign test passes.
+// Exact tests of records [slot, slot + count) for the rays whose sign test passes, in index order.
+// The sign test is re-evaluated per record with the same packed operations as the broad phase.
 __device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, const float* __restrict__ s_d, int slot,
-                                         int count, const UpdateParams& P, PrimLanes& L, uint32_t& exact_tests) {
+                                            int count, const UpdateParams& P, PrimLanes& L, uint32_t& exact_tests) {
 #pragma unroll 1
     for (int u = 0; u < count; ++u) {
         const int idx = slot + u;
         if ((uint32_t)idx >= P.n_spheres) break;   // padding
         const float4 rec = s_rec[idx];
+        const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
+                     sw = make_float2(rec.w, rec.w);
+        float2 h[kPrimRays / 2];
+        int acc = -1;
+#pragma unroll
+        for (int q = 0; q < kPrimRays / 2; ++q) {
+            h[q] = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
+            acc &= __float_as_int(h[q].x) & __float_as_int(h[q].y);
+        }
+        if (acc < 0) continue;
         uint32_t cand = 0;
 #pragma unroll
-        for (int p = 0; p < kPrimRays; ++p) {
-            const float h = rtc::primary_h(rec.x, rec.y, rec.z, rec.w, ray_half(L.ux[p >> 1], p), ray_half(L.uy[p >> 1], p),
-                                           ray_half(L.uz[p >> 1], p));
-            cand |= rtc::primary_candidate(h) ? (1u << p) : 0u;
-        }
+        for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
         cand &= L.alive;
         if (!cand) continue;
         const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
@@ -408,7 +439,7 @@ __device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, co
         for (int p = 0; p < kPrimRays; ++p) {
             if (cand & (1u << p)) {
                 ++exact_tests;
-                const float* dp = s_d + (p * 6) * kBlockThreads;
+                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
                 const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
                 const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
                 float root;
@@ -423,11 +454,16 @@ __device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, co
 
 }  // namespace
 
+// kShade = false: write (t, index) per texel to P.first_hit; the update kernel shades and continues the paths.
+// kShade = true (max_depth == 1): the whole `update` for the texel is finished here — scatter once for the
+//          attenuation and the outgoing direction, sky colour, running mean, store (compute_shader.wgsl:267-296,
+//          356-363) — and no second kernel runs.
+template <bool kShade>
 __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     const int n_pad = (int)((P.n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll);
     float4* s_rec = s_dyn;                                                    // [n_pad + kPrimTail]
-    float* s_d = reinterpret_cast<float*>(s_dyn + n_pad + kPrimTail) + threadIdx.x;   // [kPrimRays][6][kBlockThreads] (d, o), this thread's column
+    float* s_d = reinterpret_cast<float*>(s_dyn + n_pad + kPrimTail) + threadIdx.x;   // [kPrimRays][kPrimSlots][kBlockThreads], this thread's column
     for (int i = threadIdx.x; i < n_pad + kPrimTail; i += kBlockThreads) s_rec[i] = __ldg(&P.prim[i]);
     __syncthreads();
 
@@ -438,7 +474,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
     const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
     const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
     const uint32_t rec_base = (uint32_t)__cvta_generic_to_shared(s_rec);
-    uint32_t exact_tests = 0;
+    uint32_t exact_tests = 0, rays = 0;
 
     for (;;) {
         uint32_t tile = 0;
@@ -467,13 +503,13 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
                     L.alive |= 1u << p;
                 }
             }
-            float* dp = s_d + (p * 6) * kBlockThreads;
+            float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
             dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
             dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
         }
 #pragma unroll
         for (int p = 0; p < kPrimRays; ++p) {
-            const float* dp = s_d + (p * 6) * kBlockThreads;
+            const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
             const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
             float ux, uy, uz;
             const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
@@ -499,7 +535,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
             float4 nxt[kPrimUnroll];
 #pragma unroll
             for (int u = 0; u < kPrimUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
-            int acc = -1;
+            int acc = -1;   // AND of every (ray, record) sign bit of the group
 #pragma unroll
             for (int u = 0; u < kPrimUnroll; ++u) {
                 const float4 sp = cur[u];
@@ -516,19 +552,81 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
             for (int u = 0; u < kPrimUnroll; ++u) cur[u] = nxt[u];
         }
 
-        // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
+        if constexpr (!kShade) {
+            // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
+#pragma unroll
+            for (int p = 0; p < kPrimRays; ++p) {
+                const int row = row0 + p;
+                if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+                    const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
+                    P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
+                }
+            }
+        } else {
+        // fused epilogue: park the hits next to the rays, then one rolled pass over the strip
 #pragma unroll
         for (int p = 0; p < kPrimRays; ++p) {
-            const int row = row0 + p;
-            if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
-                P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
-            }
+            float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+            dp[6 * kBlockThreads] = L.best_t[p];
+            dp[7 * kBlockThreads] = __int_as_float(L.best_i[p]);
         }
+        const uint32_t sampling = L.alive | untraced;
+#pragma unroll 1
+        for (int p = 0; p < kPrimRays; ++p) {
+            const int row = row0 + p;
+            if (!((uint32_t)x < P.width && (uint32_t)row < P.row_count)) continue;
+            float4* texel = &P.accum[(size_t)row * P.width + x];
+            f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
+            uint32_t n = 0;
+            if (!reset) {
+                const float4 t = *texel;
+                mean = rtc::mk(t.x, t.y, t.z);
+                n = rtc::f2u(t.w);
+            }
+            if (sampling & (1u << p)) {
+                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+                rtc::Ray r;
+                r.d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+                r.o = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
+                float best_t = dp[6 * kBlockThreads];
+                int best_i = __float_as_int(dp[7 * kBlockThreads]);
+                if (untraced & (1u << p)) {
+                    // outside primary_arm's window: the reference loop itself (compute_shader.wgsl:164-180)
+                    const float a = rtc::dot(r.d, r.d);
+                    best_t = kTMax;
+                    best_i = -1;
+                    for (uint32_t si = 0; si < P.n_spheres; ++si) {
+                        const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + si));
+                        float root;
+                        if (rtc::sphere_root(r.o, r.d, a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, best_t, &root)) {
+                            best_t = root;
+                            best_i = (int)si;
+                        }
+                    }
+                }
+                ++rays;
+                f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
+                bool black = false;
+                if (best_i >= 0) {
+                    const GpuSphere sp = load_sphere(P.spheres, best_i);
+                    const uint32_t seed = 1u + n + seed_bits;                       // compute_shader.wgsl:353
+                    black = !rtc::scatter(&r, &factor, best_t, sp, rtc::hash(seed + 1u));   // :268 with i = 0
+                }
+                const f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times(factor, r.d);
+                mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+                n += 1u;
+            }
+            *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
+        }
+        }   // kShade
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) exact_tests += __shfl_xor_sync(kFull, exact_tests, o);
+    for (int o = 16; o > 0; o >>= 1) {
+        exact_tests += __shfl_xor_sync(kFull, exact_tests, o);
+        rays += __shfl_xor_sync(kFull, rays, o);
+    }
     if (lane == 0 && exact_tests) atomicAdd(&P.counters[1], (unsigned long long)exact_tests);
+    if (lane == 0 && rays) atomicAdd(&P.counters[0], (unsigned long long)rays);
 }
 
 // Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
@@ -690,7 +788,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
                 todo = adopt_first_hits(P, row, px, L, pre);
                 if (!__syncthreads_or(todo ? 1 : 0)) {   // block-uniform: nothing left to scan
                     unpark(L, pre);
-                    after_traversal(P, bounce, L, J);
+                    after_traversal(P, bounce, bounce + 1u >= max_depth, L, J);
                     continue;
                 }
             }
@@ -716,7 +814,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
                 __syncthreads();
             }
             if (adopt) unpark(L, pre);
-            after_traversal(P, bounce, L, J);
+            after_traversal(P, bounce, bounce + 1u >= max_depth, L, J);
         }
         end_tile(P, L, J, row, px, reset);
     }
@@ -726,18 +824,21 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t kPrimResidentMax = 4096;   // (4096 + 8) x 16 B records + 48 KB rays: 2 CTAs per SM
+constexpr uint32_t kPrimResidentMax = 4096;   // (4096 + 8) x 16 B records + 64 KB ray slots: 2 CTAs per SM
 
 static size_t prim_smem_bytes(uint32_t n_spheres) {
     const uint32_t n_pad = (n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll;
-    return (size_t)(n_pad + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * 6 * kBlockThreads * sizeof(float);
+    return (size_t)(n_pad + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float);
 }
 
 cudaError_t configure_kernels() {
     cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(primary_hits_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)prim_smem_bytes(kPrimResidentMax));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes(kPrimResidentMax));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -772,10 +873,16 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         const uint32_t tiles = ((p.width + kPrimTileW - 1) / kPrimTileW) * ((p.row_count + kPrimTileH - 1) / kPrimTileH);
         uint32_t blocks = (tiles + 7) / 8;
         if (blocks > resident) blocks = resident;
-        primary_hits_kernel<<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
+        const bool shade = rtc::f2u(p.cam.max_depth) == 1u;
+        if (shade) primary_hits_kernel<true><<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
+        else primary_hits_kernel<false><<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         n_launch += 2;
+        if (shade) {   // the texels are finished: no update kernel
+            if (launches) *launches = n_launch;
+            return cudaSuccess;
+        }
     }
     const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
     uint32_t blocks = (p.n_tiles + 7) / 8;
