@@ -30,7 +30,8 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, N_SPHERES = 3840, 2160, 1024
-FLOP_PER_TEST = 18   # oc 3 + h 5 + c 7 + disc 3, a = d.d hoisted
+FLOP_PER_TEST = 18   # oc 3 + h 5 + c 7 + disc 3, a = d.d hoisted (the reference's test as written)
+EXEC_FLOP_PER_TEST = 6   # what primary_hits_kernel executes per (ray, sphere): 3 FFMA
 METRIC = "Mrays/s at 4K/1024 spheres"
 
 
@@ -338,7 +339,14 @@ def run_ours(args):
                      "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
                      "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
                      "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
-                     "kernel": "update_resident_kernel"},
+                     "kernel": "primary_hits_kernel<true> (+ prep_primary_kernel, 3 us)",
+                     "executed_flop_per_launch": float(W) * H * N_SPHERES * EXEC_FLOP_PER_TEST,
+                     "executed_tflops": achieved_tf * EXEC_FLOP_PER_TEST / FLOP_PER_TEST,
+                     "executed_frac": achieved_tf * EXEC_FLOP_PER_TEST / FLOP_PER_TEST / peak_tf,
+                     "note": "achieved/frac count the reference's 18 flop per (ray, sphere) test (SURVEY.md 8(d)); the kernel "
+                             "reaches the same nearest hit with a 3-FFMA conservative test + exact re-test of the candidates, so "
+                             "frac can exceed 1; executed_frac is the FP32-FMA pipe share of the FFMA2 work actually issued "
+                             "(profiles/: sm__pipe_fma_cycles_active)"},
         "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_launch": hbm_bytes,
