@@ -444,3 +444,16 @@ def render_frames(scene: SphereCollection, cameras, width: int, height: int, dev
     arr = (SceneCamera * len(cameras))(*cameras)
     _check(lib().rt_render_frames(device, _ptr(scene.spheres), scene.count, arr, len(cameras), width, height, _ptr(out)))
     return out
+
+
+def write_ppm(path: str, rgba8: np.ndarray, gamma: float = None) -> None:
+    """Write an RGBA8 image (h, w, 4) — e.g. Renderer.read_rgba8() — as a binary PPM for inspection.  The shader stores
+    linear colour (the reference leaves any transfer curve to the display path, src/lib.rs:63-102); pass gamma=2.2 to
+    apply one for viewing.  File output only: no windowing on this box."""
+    img = np.asarray(rgba8)[..., :3]
+    if gamma:
+        img = np.round(255.0 * (img.astype(np.float32) / 255.0) ** (1.0 / gamma)).astype(np.uint8)
+    h, w = img.shape[:2]
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (w, h))
+        f.write(np.ascontiguousarray(img, dtype=np.uint8).tobytes())

@@ -149,3 +149,12 @@ def test_compute_shader_node_state_machine():
         states.append((node.state.name, node.index))
     assert r.calls == ["init", "update", "update", "update", "update"]
     assert states == [("Init", 0), ("Update", 1), ("Update", 0), ("Update", 1), ("Update", 0)]
+
+
+def test_write_ppm_roundtrip(tmp_path):
+    img = (np.arange(5 * 7 * 4, dtype=np.uint32) % 251).astype(np.uint8).reshape(5, 7, 4)
+    path = tmp_path / "x.ppm"
+    rt.write_ppm(str(path), img)
+    data = path.read_bytes()
+    assert data.startswith(b"P6\n7 5\n255\n")
+    assert data[len(b"P6\n7 5\n255\n"):] == img[..., :3].tobytes()
