@@ -371,6 +371,12 @@ class MultiRenderer:
 
     __del__ = close
 
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
     def set_scene(self, scene: SphereCollection):
         _check(lib().rt_multi_set_scene(self._h, _ptr(scene.spheres), len(scene.spheres), scene.count))
 

@@ -163,3 +163,25 @@ def test_node_state_machine_on_device():
             node.run(cam)
             counts.append(float(r.read_accum()[0, 0, 3]))
     assert counts == [0.0, 1.0, 2.0, 3.0, 4.0]
+
+
+@pytest.mark.parametrize("n_shards", [2, 3])
+def test_multi_renderer_row_shards(n_shards):
+    """One image sharded by row blocks (config 4 shape): gathered output == the single-renderer image.  Uses as many
+    distinct devices as the box has (a single GPU hosts all shards; the peer copies become local copies)."""
+    W, H = 320, 182
+    scene = scenes.random_scene(256)
+    have = rt.device_count()
+    devices = [i % have for i in range(n_shards)]
+    for kw in (dict(max_depth=1, spp=1), dict(max_depth=5, spp=3)):
+        cam = scenes.camera(W, H, **kw)
+        single, rays_single, _ = gpu_update(scene, [cam], W, H)
+        with rt.MultiRenderer(devices, W, H) as m:
+            m.set_scene(scene)
+            m.init()
+            m.update(cam)
+            accum = m.gather_accum()
+            rgba = m.gather_rgba8()
+            assert m.rays_traced() == rays_single
+        assert np.array_equal(accum.view(np.uint32), single.view(np.uint32))
+        assert np.array_equal(rgba, ol.quantize(single))
