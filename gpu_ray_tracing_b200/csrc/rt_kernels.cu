@@ -412,12 +412,13 @@ __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 
 // Exact tests of records [slot, slot + count) for the rays whose sign test passes, in index order.
 // The sign test is re-evaluated per record with the same packed operations as the broad phase.
 __device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, const float* __restrict__ s_d, int slot,
-                                            int count, const UpdateParams& P, PrimLanes& L, uint32_t& exact_tests) {
+                                            int count, int index0, const UpdateParams& P, PrimLanes& L,
+                                            uint32_t& exact_tests) {
 #pragma unroll 1
     for (int u = 0; u < count; ++u) {
-        const int idx = slot + u;
+        const int idx = index0 + slot + u;
         if ((uint32_t)idx >= P.n_spheres) break;   // padding
-        const float4 rec = s_rec[idx];
+        const float4 rec = s_rec[slot + u];
         const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
                      sw = make_float2(rec.w, rec.w);
         float2 h[kPrimRays / 2];
@@ -452,117 +453,101 @@ __device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, co
     }
 }
 
-}  // namespace
+// Primary rays of a strip (get_ray, compute_shader.wgsl:305-325): exact (d, o) parked in shared memory, unit
+// directions in registers.  `untraced` collects sampling rays outside primary_arm's window.
+__device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
+                                           uint32_t seed_bits, uint32_t spp, bool reset, PrimLanes& L, uint32_t& untraced) {
+    L.alive = 0;
+    untraced = 0;
+#pragma unroll 1
+    for (int p = 0; p < kPrimRays; ++p) {
+        const int row = row0 + p;
+        f3 d = rtc::mk(0.0f, 0.0f, 0.0f), o = d;
+        if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+            uint32_t n = 0;
+            if (!reset) n = rtc::f2u(P.accum[(size_t)row * P.width + x].w);
+            if (n < spp) {
+                const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
+                const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
+                d = r.d;
+                o = r.o;
+                L.alive |= 1u << p;
+            }
+        }
+        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+        dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
+        dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
+    }
+#pragma unroll
+    for (int p = 0; p < kPrimRays; ++p) {
+        const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+        const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+        float ux, uy, uz;
+        const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
+        if (!ok && (L.alive & (1u << p))) {
+            untraced |= 1u << p;
+            L.alive &= ~(1u << p);
+        }
+        const int q = p >> 1;
+        if (p & 1) { L.ux[q].y = ux; L.uy[q].y = uy; L.uz[q].y = uz; }
+        else       { L.ux[q].x = ux; L.uy[q].x = uy; L.uz[q].x = uz; }
+        L.best_t[p] = kTMax;
+        L.best_i[p] = -1;
+    }
+}
+
+// Broad phase over `count` (multiple of kPrimUnroll) records at s_rec (global sphere index of slot 0 = index0),
+// kPrimUnroll per iteration, the next group prefetched; kPrimUnroll slots after the end must be readable.
+__device__ __forceinline__ void prim_scan(const float4* __restrict__ s_rec, int count, int index0,
+                                          const float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
+                                          uint32_t& exact_tests) {
+    uint32_t addr = (uint32_t)__cvta_generic_to_shared(s_rec);
+    float4 cur[kPrimUnroll];
+#pragma unroll
+    for (int u = 0; u < kPrimUnroll; ++u) cur[u] = lds128(addr + 16u * u);
+#pragma unroll 1
+    for (int s = 0; s < count; s += kPrimUnroll) {
+        addr += 16u * kPrimUnroll;
+        float4 nxt[kPrimUnroll];
+#pragma unroll
+        for (int u = 0; u < kPrimUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
+        int acc = -1;   // AND of every (ray, record) sign bit of the group
+#pragma unroll
+        for (int u = 0; u < kPrimUnroll; ++u) {
+            const float4 sp = cur[u];
+            const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z),
+                         sw = make_float2(sp.w, sp.w);
+#pragma unroll
+            for (int q = 0; q < kPrimRays / 2; ++q) {
+                const float2 h = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
+                acc &= __float_as_int(h.x) & __float_as_int(h.y);
+            }
+        }
+        if (acc >= 0) prim_narrow(s_rec, s_d, s, kPrimUnroll, index0, P, L, exact_tests);
+#pragma unroll
+        for (int u = 0; u < kPrimUnroll; ++u) cur[u] = nxt[u];
+    }
+}
 
 // kShade = false: write (t, index) per texel to P.first_hit; the update kernel shades and continues the paths.
 // kShade = true (max_depth == 1): the whole `update` for the texel is finished here — scatter once for the
 //          attenuation and the outgoing direction, sky colour, running mean, store (compute_shader.wgsl:267-296,
 //          356-363) — and no second kernel runs.
 template <bool kShade>
-__global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
-    extern __shared__ float4 s_dyn[];
-    const int n_pad = (int)((P.n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll);
-    float4* s_rec = s_dyn;                                                    // [n_pad + kPrimTail]
-    float* s_d = reinterpret_cast<float*>(s_dyn + n_pad + kPrimTail) + threadIdx.x;   // [kPrimRays][kPrimSlots][kBlockThreads], this thread's column
-    for (int i = threadIdx.x; i < n_pad + kPrimTail; i += kBlockThreads) s_rec[i] = __ldg(&P.prim[i]);
-    __syncthreads();
-
-    const int lane = threadIdx.x & 31;
-    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
-    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
-    const bool reset = P.cam.camera_has_moved > 0.5f;
-    const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
-    const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
-    const uint32_t rec_base = (uint32_t)__cvta_generic_to_shared(s_rec);
-    uint32_t exact_tests = 0, rays = 0;
-
-    for (;;) {
-        uint32_t tile = 0;
-        if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
-        tile = __shfl_sync(kFull, tile, 0);
-        if (tile >= n_tiles) break;
-        const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
-        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
-
-        // primary rays of the strip (get_ray, compute_shader.wgsl:305-325); directions parked in shared memory
-        PrimLanes L;
-        L.alive = 0;
-        uint32_t untraced = 0;   // sampling rays outside primary_arm's window: left to the update kernel
-#pragma unroll 1
+__device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
+                                            const PrimLanes& L, uint32_t untraced, uint32_t seed_bits, bool reset,
+                                            uint32_t& rays) {
+    if constexpr (!kShade) {
+        // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
+#pragma unroll
         for (int p = 0; p < kPrimRays; ++p) {
             const int row = row0 + p;
-            f3 d = rtc::mk(0.0f, 0.0f, 0.0f), o = d;
             if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                uint32_t n = 0;
-                if (!reset) n = rtc::f2u(P.accum[(size_t)row * P.width + x].w);
-                if (n < spp) {
-                    const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
-                    const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
-                    d = r.d;
-                    o = r.o;
-                    L.alive |= 1u << p;
-                }
+                const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
+                P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
             }
-            float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-            dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
-            dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
         }
-#pragma unroll
-        for (int p = 0; p < kPrimRays; ++p) {
-            const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-            const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
-            float ux, uy, uz;
-            const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
-            if (!ok && (L.alive & (1u << p))) {
-                untraced |= 1u << p;
-                L.alive &= ~(1u << p);
-            }
-            const int q = p >> 1;
-            if (p & 1) { L.ux[q].y = ux; L.uy[q].y = uy; L.uz[q].y = uz; }
-            else       { L.ux[q].x = ux; L.uy[q].x = uy; L.uz[q].x = uz; }
-            L.best_t[p] = kTMax;
-            L.best_i[p] = -1;
-        }
-
-        // broad phase over the resident records, kPrimUnroll per iteration, next group prefetched
-        uint32_t addr = rec_base;
-        float4 cur[kPrimUnroll];
-#pragma unroll
-        for (int u = 0; u < kPrimUnroll; ++u) cur[u] = lds128(addr + 16u * u);
-#pragma unroll 1
-        for (int s = 0; s < n_pad; s += kPrimUnroll) {
-            addr += 16u * kPrimUnroll;
-            float4 nxt[kPrimUnroll];
-#pragma unroll
-            for (int u = 0; u < kPrimUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
-            int acc = -1;   // AND of every (ray, record) sign bit of the group
-#pragma unroll
-            for (int u = 0; u < kPrimUnroll; ++u) {
-                const float4 sp = cur[u];
-                const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z),
-                             sw = make_float2(sp.w, sp.w);
-#pragma unroll
-                for (int q = 0; q < kPrimRays / 2; ++q) {
-                    const float2 h = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
-                    acc &= __float_as_int(h.x) & __float_as_int(h.y);
-                }
-            }
-            if (acc >= 0) prim_narrow(s_rec, s_d, s, kPrimUnroll, P, L, exact_tests);
-#pragma unroll
-            for (int u = 0; u < kPrimUnroll; ++u) cur[u] = nxt[u];
-        }
-
-        if constexpr (!kShade) {
-            // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
-#pragma unroll
-            for (int p = 0; p < kPrimRays; ++p) {
-                const int row = row0 + p;
-                if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                    const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
-                    P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
-                }
-            }
-        } else {
+    } else {
         // fused epilogue: park the hits next to the rays, then one rolled pass over the strip
 #pragma unroll
         for (int p = 0; p < kPrimRays; ++p) {
@@ -618,8 +603,10 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
             }
             *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
         }
-        }   // kShade
     }
+}
+
+__device__ __forceinline__ void prim_flush(const UpdateParams& P, uint32_t exact_tests, uint32_t rays, int lane) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         exact_tests += __shfl_xor_sync(kFull, exact_tests, o);
@@ -627,6 +614,109 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
     }
     if (lane == 0 && exact_tests) atomicAdd(&P.counters[1], (unsigned long long)exact_tests);
     if (lane == 0 && rays) atomicAdd(&P.counters[0], (unsigned long long)rays);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// Scenes of any size: the records stream through two shared-memory stages of kPrimChunk records, filled
+// by 1-D bulk copies (cp.async.bulk, one elected thread) that signal an mbarrier per stage.  A CTA owns 8
+// warp tiles for one pass over the scene; chunk c + 2 is requested as soon as every warp has left chunk c,
+// so the copy of the next chunk always overlaps the scan of the current one.  Nearest-hit state stays in
+// registers across chunks: index order, and with it the reference's tie rule, is preserved.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+}  // namespace
+
+template <bool kShade>
+__global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_dyn[];
+    constexpr int kStage = kPrimChunk + kPrimTail;
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint32_t s_block_tile;
+    float4* s_stage = s_dyn;                                                          // [2][kStage]
+    float* s_d = reinterpret_cast<float*>(s_dyn + 2 * kStage) + threadIdx.x;          // ray slots, this thread's column
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
+    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(s_stage);
+    if (threadIdx.x == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const int n_pad = (int)((P.n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll);
+    const int n_chunks = (n_pad + kPrimChunk - 1) / kPrimChunk;
+    const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
+    const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
+    const uint32_t n_block_tiles = (n_tiles + 7u) / 8u;
+    uint32_t exact_tests = 0, rays = 0;
+    uint32_t parity = 0;   // bit s: phase parity to wait for on stage s
+
+    auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
+        const int base = c * kPrimChunk;
+        const uint32_t bytes = (uint32_t)(min(kPrimChunk, n_pad - base) + kPrimTail) * (uint32_t)sizeof(float4);
+        const uint32_t bar = bar0 + 8u * (uint32_t)(c & 1);
+        mbar_expect_tx(bar, bytes);
+        bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.prim + base, bytes, bar);
+    };
+
+    for (;;) {
+        __syncthreads();   // the previous tile is finished with s_block_tile and both stages
+        if (threadIdx.x == 0) s_block_tile = atomicAdd(P.tile_counter + 1, 1u);
+        __syncthreads();
+        const uint32_t bt = s_block_tile;
+        if (bt >= n_block_tiles) break;
+        if (threadIdx.x == 0) {
+            request(0);
+            if (n_chunks > 1) request(1);
+        }
+        const uint32_t tile = bt * 8u + (uint32_t)warp;   // tiles past the end have every ray out of bounds
+        const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
+        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+        PrimLanes L;
+        uint32_t untraced;
+        prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
+        const bool warp_live = __any_sync(kFull, L.alive != 0u);
+
+        for (int c = 0; c < n_chunks; ++c) {
+            const int st = c & 1, base = c * kPrimChunk;
+            mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
+            parity ^= 1u << st;
+            if (warp_live) prim_scan(s_stage + st * kStage, min(kPrimChunk, n_pad - base), base, s_d, P, L, exact_tests);
+            __syncthreads();   // every warp has left stage st
+            if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
+        }
+        prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
+    }
+    prim_flush(P, exact_tests, rays, lane);
 }
 
 // Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
@@ -824,11 +914,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 // Launchers
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t kPrimResidentMax = 4096;   // (4096 + 8) x 16 B records + 64 KB ray slots: 2 CTAs per SM
-
-static size_t prim_smem_bytes(uint32_t n_spheres) {
-    const uint32_t n_pad = (n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll;
-    return (size_t)(n_pad + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float);
+static size_t prim_smem_bytes() {
+    return (size_t)2 * (kPrimChunk + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float);
 }
 
 cudaError_t configure_kernels() {
@@ -836,18 +923,18 @@ cudaError_t configure_kernels() {
                                          (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(primary_hits_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)prim_smem_bytes(kPrimResidentMax));
+                             (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)prim_smem_bytes(kPrimResidentMax));
+                             (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
 }
 
 bool primary_pass_applies(const UpdateParams& p) {
-    return p.prim != nullptr && p.first_hit != nullptr && p.n_spheres > 0 && p.n_spheres <= kPrimResidentMax &&
-           rtc::primary_rho(p.cam) >= 0.0 && rtc::f2u(p.cam.max_depth) > 0u;
+    return p.prim != nullptr && p.first_hit != nullptr && p.n_spheres > 0 && rtc::primary_rho(p.cam) >= 0.0 &&
+           rtc::f2u(p.cam.max_depth) > 0u;
 }
 
 cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
@@ -874,8 +961,8 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         uint32_t blocks = (tiles + 7) / 8;
         if (blocks > resident) blocks = resident;
         const bool shade = rtc::f2u(p.cam.max_depth) == 1u;
-        if (shade) primary_hits_kernel<true><<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
-        else primary_hits_kernel<false><<<blocks, kBlockThreads, prim_smem_bytes(p.n_spheres), stream>>>(p);
+        if (shade) primary_hits_kernel<true><<<blocks, kBlockThreads, prim_smem_bytes(), stream>>>(p);
+        else primary_hits_kernel<false><<<blocks, kBlockThreads, prim_smem_bytes(), stream>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         n_launch += 2;

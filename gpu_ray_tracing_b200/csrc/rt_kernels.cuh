@@ -20,6 +20,7 @@ constexpr int kPrimTileW = 32;
 constexpr int kPrimTileH = 8;
 constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
+constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 
 struct UpdateParams {
     SceneCamera cam;            // 176 B, lands in the kernel parameter constant bank

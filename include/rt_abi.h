@@ -184,7 +184,8 @@ RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
 /* Kernel selection for experiments/tests: 0 = auto, 1 = baseline (one thread per pixel, exact
  * quadratic per sphere), 2 = tiled broad phase + exact narrow phase with the scene resident in shared
  * memory, 3 = the same streaming the scene through shared memory, 4 = common-origin primary pass
- * (pinhole cameras) followed by 2 or 3 for the bounces.  0 picks 4 when it applies, else 2 or 3. */
+ * (primary rays of pinhole and defocus cameras, records streamed through shared memory) followed by 2 or 3
+ * for the bounces.  0 picks 4 when it applies, else 2 or 3. */
 RT_API int rt_set_kernel_variant(RtRenderer* r, int variant);
 
 /* ---------------------------------------------------------------------------------------

@@ -26,7 +26,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     for (uint32_t i = 0; i < count; ++i) gk[i] = rtc::broad_record_k(spheres[i]);
     // common-origin primary pass: same applicability rule as rtk::primary_pass_applies (variant 0 / 4)
     const double rho = rtc::primary_rho(cam);
-    const bool primary = (variant == 0 || variant == 4) && count > 0 && count <= 4096 && rho >= 0.0 && rtc::f2u(cam.max_depth) > 0u;
+    const bool primary = (variant == 0 || variant == 4) && count > 0 && rho >= 0.0 && rtc::f2u(cam.max_depth) > 0u;
     std::vector<float> prim(primary ? (size_t)count * 4 : 0);
     if (primary)
         for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);

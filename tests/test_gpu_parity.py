@@ -130,11 +130,20 @@ def test_large_scene_streamed():
     gpu, rays, _ = gpu_update(scene, [cam], W, H)
     assert rays == W * H
     assert_parity(gpu, cpu, "grid 16384")
+    gpu3, _, _ = gpu_update(scene, [cam], W, H, variant=3)
+    assert_parity(gpu3, cpu, "grid 16384 general streamed")
     cam.max_depth = 6.0
     cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
     gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
     assert rays_cpu == rays_gpu
     assert_parity(gpu, cpu, "grid 16384 depth 6")
+    # 3000 spheres: three chunks with a ragged last one through the streamed primary pass, defocus camera
+    scene = scenes.random_scene(3000)
+    cam = scenes.camera(W, H, max_depth=3, spp=2)
+    cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+    gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H, variant=4)
+    assert rays_cpu == rays_gpu
+    assert_parity(gpu, cpu, "random 3000 streamed primary")
 
 
 def test_rgba8_and_headless_render():
