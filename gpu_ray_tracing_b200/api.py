@@ -120,6 +120,8 @@ _SIGNATURES = {
     "rt_read_accum": (C.c_int, [_P, _P]),
     "rt_write_accum": (C.c_int, [_P, _P]),
     "rt_read_rgba8": (C.c_int, [_P, _P]),
+    "rt_read_rgba8_async": (C.c_int, [_P, _P]),
+    "rt_read_wait": (C.c_int, [_P]),
     "rt_rays_traced": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "rt_exact_tests": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "rt_reset_counters": (C.c_int, [_P]),
@@ -290,6 +292,13 @@ class Renderer:
 
     def read_rgba8_into(self, host_ptr: int):
         _check(lib().rt_read_rgba8(self._h, C.c_void_p(host_ptr)))
+
+    def read_rgba8_async_into(self, host_ptr: int):
+        """Non-blocking read-back into a (pinned) host buffer; pair with read_wait()."""
+        _check(lib().rt_read_rgba8_async(self._h, C.c_void_p(host_ptr)))
+
+    def read_wait(self):
+        _check(lib().rt_read_wait(self._h))
 
     def quantize(self):
         _check(lib().rt_quantize(self._h))

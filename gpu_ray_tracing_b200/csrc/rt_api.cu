@@ -99,6 +99,11 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     if (e == cudaSuccess) e = cudaMalloc(&r->counters, 2 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking);
+    for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+        e = cudaEventCreateWithFlags(&r->ev_quantized[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_copied[b], cudaEventDisableTiming);
+    }
     if (e == cudaSuccess) e = cudaMemsetAsync(r->accum, 0, r->n_texels * sizeof(float4), r->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(r->counters, 0, 2 * sizeof(unsigned long long), r->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(r->stream);
@@ -119,6 +124,13 @@ int rt_destroy(RtRenderer* r) {
     if (!r) return RT_OK;
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
+    if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
+    cudaFree(r->rgba8_alt);
+    for (int b = 0; b < 2; ++b) {
+        if (r->ev_quantized[b]) cudaEventDestroy(r->ev_quantized[b]);
+        if (r->ev_copied[b]) cudaEventDestroy(r->ev_copied[b]);
+    }
+    if (r->copy_stream) cudaStreamDestroy(r->copy_stream);
     cudaFree(r->accum);
     cudaFree(r->rgba8);
     cudaFree(r->spheres);
@@ -254,6 +266,30 @@ int rt_read_rgba8(RtRenderer* r, uint8_t* host) {
     if (rc != RT_OK) return rc;
     RT_CUDA(cudaMemcpyAsync(host, r->rgba8, r->n_texels * sizeof(uchar4), cudaMemcpyDeviceToHost, r->stream));
     RT_CUDA(cudaStreamSynchronize(r->stream));
+    return RT_OK;
+}
+
+int rt_read_rgba8_async(RtRenderer* r, uint8_t* host) {
+    RT_CHECK_HANDLE(r);
+    if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
+    if (!r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
+    const int b = (int)(r->async_reads & 1u);
+    uchar4* dev = b ? r->rgba8_alt : r->rgba8;
+    // slot b was last used two reads ago: its copy must have left the buffer before it is overwritten
+    if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
+    RT_CUDA(rtk::launch_quantize(r->accum, dev, r->n_texels, r->stream));
+    r->launches += 1;
+    RT_CUDA(cudaEventRecord(r->ev_quantized[b], r->stream));
+    RT_CUDA(cudaStreamWaitEvent(r->copy_stream, r->ev_quantized[b], 0));
+    RT_CUDA(cudaMemcpyAsync(host, dev, r->n_texels * sizeof(uchar4), cudaMemcpyDeviceToHost, r->copy_stream));
+    RT_CUDA(cudaEventRecord(r->ev_copied[b], r->copy_stream));
+    r->async_reads += 1;
+    return RT_OK;
+}
+
+int rt_read_wait(RtRenderer* r) {
+    RT_CHECK_HANDLE(r);
+    RT_CUDA(cudaStreamSynchronize(r->copy_stream));
     return RT_OK;
 }
 

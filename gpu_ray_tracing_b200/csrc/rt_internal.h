@@ -25,6 +25,11 @@ struct RtRenderer {
     unsigned int* tile_counter = nullptr;
     unsigned long long* counters = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    // asynchronous read-back (rt_read_rgba8_async): second RGBA8 buffer, copy stream, per-slot events
+    cudaStream_t copy_stream = nullptr;
+    uchar4* rgba8_alt = nullptr;
+    cudaEvent_t ev_quantized[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+    uint32_t async_reads = 0;
     uint64_t launches = 0;
     int variant = 0;
 };

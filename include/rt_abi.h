@@ -157,6 +157,13 @@ RT_API int rt_read_accum(RtRenderer* r, float* host_rgba32f);
 RT_API int rt_write_accum(RtRenderer* r, const float* host_rgba32f);
 /* Linear RGBA8 of the running mean: q(x) = floor(clamp(x,0,1)*255 + 0.5), alpha = 255. */
 RT_API int rt_read_rgba8(RtRenderer* r, uint8_t* host_rgba8);
+/* The same without blocking: the frame as it stands after the work queued so far is quantised into one of two device
+ * buffers and copied to `host_rgba8` on a separate copy stream, so the next rt_update overlaps the transfer (the role
+ * the render graph's frame pipelining plays for the reference's sprite, src/lib.rs:79-102).  `host_rgba8` must stay
+ * valid (and should be pinned) until rt_read_wait returns; at most two reads are in flight, a third waits for the
+ * first on the device. */
+RT_API int rt_read_rgba8_async(RtRenderer* r, uint8_t* host_rgba8);
+RT_API int rt_read_wait(RtRenderer* r);   /* every asynchronous read issued so far has landed */
 
 /* Number of sphere_list_hit traversals (compute_shader.wgsl:266) executed since the last
  * rt_reset_counters: the "rays" of the Mrays/s metric. */

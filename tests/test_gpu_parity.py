@@ -194,3 +194,28 @@ def test_multi_renderer_row_shards(n_shards):
             assert m.rays_traced() == rays_single
         assert np.array_equal(accum.view(np.uint32), single.view(np.uint32))
         assert np.array_equal(rgba, ol.quantize(single))
+
+
+def test_async_readback_matches_blocking_read():
+    """rt_read_rgba8_async: three frames in flight through two device slots, each equal to the blocking read."""
+    import torch
+    W, H = 256, 144
+    scene = scenes.default_scene()
+    cams = [scenes.camera(W, H, max_depth=3, spp=4, random_seed=s, moved=m) for s, m in ((0.125, 1), (0.5, 0), (0.75, 0), (0.875, 1))]
+    want = []
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        for cam in cams:
+            r.update(cam)
+            want.append(r.read_rgba8().copy())
+    bufs = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in cams]
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        for cam, buf in zip(cams, bufs):
+            r.update(cam)
+            r.read_rgba8_async_into(buf.data_ptr())
+        r.read_wait()
+    for w, buf in zip(want, bufs):
+        assert np.array_equal(w, buf.numpy())
