@@ -137,6 +137,9 @@ int rt_destroy(RtRenderer* r) {
     cudaFree(r->geom);
     cudaFree(r->prim);
     cudaFree(r->first_hit);
+    cudaFree(r->wf_queue[0]);
+    cudaFree(r->wf_queue[1]);
+    cudaFree(r->wf_counts);
     cudaFree(r->tile_counter);
     cudaFree(r->counters);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
@@ -198,6 +201,16 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.counters = r->counters;
     p.prim = r->prim;
     p.first_hit = r->first_hit;
+    if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant == 4)) {
+        // first deep frame: path queues for the wavefront bounces (two queues x three float4 planes)
+        for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
+        RT_CUDA(cudaMalloc(&r->wf_counts, 2 * (rtk::kWfMaxDepth + 1) * sizeof(unsigned int)));
+    }
+    p.wf_queue[0] = r->wf_queue[0];
+    p.wf_queue[1] = r->wf_queue[1];
+    p.wf_counts = r->wf_counts;
+    p.wf_capacity = (uint32_t)r->n_texels;
+    p.wf_bounce = 0;
     int launched = 0;
     RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched));
     r->launches += (uint64_t)launched;

@@ -20,6 +20,8 @@ struct RtRenderer {
     uint32_t geom_capacity = 0;
     float4* prim = nullptr;               // per-frame common-origin records (same padded length as geom)
     float2* first_hit = nullptr;          // (t, sphere index) per texel, written by the primary pass
+    float4* wf_queue[2] = {nullptr, nullptr};   // wavefront path queues (3 planes of n_texels float4 each), on first deep frame
+    unsigned int* wf_counts = nullptr;
     uint32_t n_spheres = 0;
     bool has_scene = false;
     unsigned int* tile_counter = nullptr;

@@ -719,6 +719,279 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
     prim_flush(P, exact_tests, rays, lane);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Wavefront bounces (max_depth > 1 behind a primary pass).  Paths that survive
+// a bounce are compacted into a queue, so every traversal launch works on dense warps of live rays
+// instead of dragging finished pixels along: shade_first_kernel turns first_hit into colours or
+// queued paths, bounce_kernel traces queue b (general 7-FFMA broad phase, records streamed through
+// shared memory by bulk copies) and appends the survivors to queue b + 1.  Bounce rays are incoherent,
+// so the exact tests are DEFERRED: a thread notes the groups in which one of its rays passed the broad
+// test and the warp drains those notes together, every lane working on its own candidates, instead of
+// the whole warp stalling on one lane's candidate.  Per-ray order of exact tests is still ascending
+// index, so the result is the reference's.
+// ---------------------------------------------------------------------------------------------
+namespace {
+
+// Running mean and texel store for a finished path (compute_shader.wgsl:356-363).
+__device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t texel_index, uint32_t n, f3 color, bool reset) {
+    float4* texel = &P.accum[texel_index];
+    f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
+    if (!reset) {
+        const float4 t = *texel;
+        mean = rtc::mk(t.x, t.y, t.z);
+    }
+    mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+    *texel = make_float4(mean.x, mean.y, mean.z, (float)(n + 1u));
+}
+
+// Warp-aggregated append of one path per pushing lane.  Every lane of the warp must call this.
+__device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_bounce, bool push, f3 o, f3 d, f3 factor,
+                                          uint32_t texel_index, uint32_t bseed, uint32_t n, int lane) {
+    const unsigned m = __ballot_sync(kFull, push);
+    if (m == 0u) return;
+    const int leader = __ffs((int)m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&P.wf_counts[next_bounce], (unsigned)__popc(m));
+    base = __shfl_sync(kFull, base, leader);
+    if (push) {
+        const uint32_t j = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+        float4* q = P.wf_queue[next_bounce & 1u];
+        q[j] = make_float4(o.x, o.y, o.z, d.x);
+        q[(size_t)P.wf_capacity + j] = make_float4(d.y, d.z, factor.x, factor.y);
+        q[2 * (size_t)P.wf_capacity + j] =
+            make_float4(factor.z, __uint_as_float(texel_index), __uint_as_float(bseed), __uint_as_float(n));
+    }
+}
+
+// What happens to a traced ray (compute_shader.wgsl:267-296): returns true when the path continues (then o, d,
+// factor are the scattered ray), false when the texel has been finished.
+__device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
+                                            f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
+                                            bool reset) {
+    if (best_i < 0) {
+        finalize_texel(P, texel_index, n, rtc::sky_times(factor, d), reset);
+        return false;
+    }
+    const GpuSphere sp = load_sphere(P.spheres, best_i);
+    rtc::Ray r;
+    r.o = o;
+    r.d = d;
+    const bool ok = rtc::scatter(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
+    if (!ok) {
+        finalize_texel(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
+        return false;
+    }
+    if (last) {
+        finalize_texel(P, texel_index, n, rtc::sky_times(factor, r.d), reset);
+        return false;
+    }
+    o = r.o;
+    d = r.d;
+    return true;
+}
+
+// scan_spheres with the exact tests deferred (see the section header).  s_note: this thread's column of
+// [kWfDefer][kBlockThreads] group offsets.
+__device__ __forceinline__ void drain_notes(const float4* __restrict__ s_geom, int index0, const unsigned short* __restrict__ s_note,
+                                            int& n_notes, const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
+                                            uint32_t& exact_tests) {
+    for (int e = 0; __any_sync(kFull, e < n_notes); ++e) {
+        if (e < n_notes) {
+            const int s = (int)s_note[e * kBlockThreads];
+            narrow_phase(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
+        }
+    }
+    n_notes = 0;
+}
+
+__device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__ s_geom, int count, int index0,
+                                                      unsigned short* __restrict__ s_note, const GpuSphere* __restrict__ spheres,
+                                                      uint32_t n_spheres, Lanes& L, uint32_t& exact_tests) {
+    uint32_t addr = (uint32_t)__cvta_generic_to_shared(s_geom);
+    int n_notes = 0;
+    float4 cur[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) cur[u] = lds128(addr + 16u * u);
+#pragma unroll 1
+    for (int s = 0; s < count; s += kUnroll) {
+        addr += 16u * kUnroll;
+        float4 nxt[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
+        bool any = false;
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+#pragma unroll
+            for (int q = 0; q < kPairs; ++q) {
+                const float2 g = broad_g2(cur[u], L, q);
+                any |= !(g.x < L.thr[2 * q]);
+                any |= !(g.y < L.thr[2 * q + 1]);
+            }
+        }
+        if (any) {
+            s_note[n_notes * kBlockThreads] = (unsigned short)s;
+            ++n_notes;
+        }
+        if (__any_sync(kFull, n_notes >= kWfDefer)) drain_notes(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) cur[u] = nxt[u];
+    }
+    drain_notes(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
+}
+
+}  // namespace
+
+// One thread per texel: the `update` bookkeeping around the primary hit found by primary_hits_kernel<false>.
+__global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant__ UpdateParams P) {
+    const uint64_t n_texels = (uint64_t)P.width * P.row_count;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
+    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    bool push = false;
+    f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = rtc::mk(1.0f, 1.0f, 1.0f);
+    uint32_t bseed = 0, n = 0, rays = 0, exact_tests = 0;
+    if (t < n_texels) {
+        const int row = (int)(t / P.width), x = (int)(t % P.width);
+        if (!reset) n = rtc::f2u(P.accum[t].w);
+        if (n < spp) {
+            const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
+            const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
+            o = r.o;
+            d = r.d;
+            bseed = seed + 1u;
+            const float2 fh = P.first_hit[t];
+            float best_t = fh.x;
+            int best_i = __float_as_int(fh.y);
+            if (best_i == -2) {
+                // not traced by the primary pass: the reference loop itself (compute_shader.wgsl:164-180)
+                const float a = rtc::dot(d, d);
+                best_t = kTMax;
+                best_i = -1;
+                for (uint32_t si = 0; si < P.n_spheres; ++si) {
+                    const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + si));
+                    float root;
+                    ++exact_tests;
+                    if (rtc::sphere_root(o, d, a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, best_t, &root)) {
+                        best_t = root;
+                        best_i = (int)si;
+                    }
+                }
+            }
+            rays = 1;
+            push = resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, (uint32_t)t, bseed, n, reset);
+        } else if (reset) {
+            P.accum[t] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // reset rule with nothing to sample (spp == 0)
+        }
+    }
+    push_path(P, 1u, push, o, d, factor, (uint32_t)t, bseed, n, lane);
+    prim_flush(P, exact_tests, rays, lane);
+}
+
+// Traces queue P.wf_bounce.  A CTA takes batches of 1024 rays (4 per thread); the general records stream
+// through two bulk-copied stages exactly as in primary_hits_kernel.
+__global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_dyn[];
+    constexpr int kStage = kWfChunk + kGeomTail;
+    __shared__ __align__(8) uint64_t s_bar[2];
+    __shared__ uint32_t s_batch;
+    float4* s_stage = s_dyn;                                                                                // [2][kStage]
+    unsigned short* s_note = reinterpret_cast<unsigned short*>(s_dyn + 2 * kStage) + threadIdx.x;           // [kWfDefer][kBlockThreads]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
+    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(s_stage);
+    if (threadIdx.x == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t bounce = P.wf_bounce;
+    const uint32_t count = P.wf_counts[bounce];
+    const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool last = bounce + 1u >= max_depth;
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const float4* qin = P.wf_queue[bounce & 1u];
+    const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
+    const int n_chunks = (n_pad + kWfChunk - 1) / kWfChunk;
+    uint32_t exact_tests = 0, rays = 0, parity = 0;
+
+    auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
+        const int base = c * kWfChunk;
+        const uint32_t bytes = (uint32_t)(min(kWfChunk, n_pad - base) + kGeomTail) * (uint32_t)sizeof(float4);
+        const uint32_t bar = bar0 + 8u * (uint32_t)(c & 1);
+        mbar_expect_tx(bar, bytes);
+        bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.geom + base, bytes, bar);
+    };
+
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_batch = atomicAdd(&P.wf_counts[kWfMaxDepth + 1u + bounce], 1u);
+        __syncthreads();
+        const uint32_t batch = s_batch;
+        if (batch >= n_batches) break;
+        if (threadIdx.x == 0) {
+            request(0);
+            if (n_chunks > 1) request(1);
+        }
+        const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)lane;
+        Lanes L;
+#pragma unroll
+        for (int p = 0; p < kPix; ++p) {
+            const uint32_t j = j0 + 32u * (uint32_t)p;
+            if (j < count) {
+                const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
+                arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
+                ++rays;
+            } else {
+                idle_ray(L, p);
+            }
+        }
+        for (int c = 0; c < n_chunks; ++c) {
+            const int st = c & 1, base = c * kWfChunk;
+            mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
+            parity ^= 1u << st;
+            scan_spheres_deferred(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres, P.n_spheres, L,
+                                  exact_tests);
+            __syncthreads();   // every warp has left stage st
+            if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
+        }
+#pragma unroll 1
+        for (int p = 0; p < kPix; ++p) {
+            const uint32_t j = j0 + 32u * (uint32_t)p;
+            bool push = false;
+            f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
+            uint32_t texel_index = 0, bseed = 0, n = 0;
+            if (j < count) {
+                const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+                factor = rtc::mk(B.z, B.w, C.x);
+                texel_index = __float_as_uint(C.y);
+                bseed = __float_as_uint(C.z);
+                n = __float_as_uint(C.w);
+                float best_t = kTMax;
+                int best_i = -1;
+                // p is a run-time index here: pick this ray's state without dynamic register indexing
+#pragma unroll
+                for (int k = 0; k < kPix; ++k) {
+                    if (k == p) {
+                        o = origin_of(L, k);
+                        d = rtc::mk(L.dx[k], L.dy[k], L.dz[k]);
+                        best_t = L.best_t[k];
+                        best_i = L.best_i[k];
+                    }
+                }
+                push = resolve_hit(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+            }
+            push_path(P, bounce + 1u, push, o, d, factor, texel_index, bseed, n, lane);
+        }
+    }
+    prim_flush(P, exact_tests, rays, lane);
+}
+
 // Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
 __global__ void prep_primary_kernel(const GpuSphere* __restrict__ spheres, float4* __restrict__ prim, uint32_t n,
                                     uint32_t n_slots, float ox, float oy, float oz, double rho) {
@@ -918,6 +1191,10 @@ static size_t prim_smem_bytes() {
     return (size_t)2 * (kPrimChunk + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float);
 }
 
+static size_t bounce_smem_bytes() {
+    return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
+}
+
 cudaError_t configure_kernels() {
     cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
@@ -927,6 +1204,8 @@ cudaError_t configure_kernels() {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bounce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
@@ -969,6 +1248,22 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         if (shade) {   // the texels are finished: no update kernel
             if (launches) *launches = n_launch;
             return cudaSuccess;
+        }
+        const uint32_t depth = rtc::f2u(p.cam.max_depth);
+        if (p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth) {
+            // wavefront: shade the primary hits, then one launch per bounce over the compacted survivors
+            e = cudaMemsetAsync(p.wf_counts, 0, 2 * (kWfMaxDepth + 1) * sizeof(unsigned int), stream);
+            if (e != cudaSuccess) return e;
+            const uint64_t n_texels = (uint64_t)p.width * p.row_count;
+            shade_first_kernel<<<(unsigned)((n_texels + 255) / 256), 256, 0, stream>>>(p);
+            n_launch += 1;
+            for (uint32_t b = 1; b < depth; ++b) {
+                p.wf_bounce = b;
+                bounce_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                n_launch += 1;
+            }
+            if (launches) *launches = n_launch;
+            return cudaGetLastError();
         }
     }
     const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;

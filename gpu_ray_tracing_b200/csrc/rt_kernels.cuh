@@ -21,6 +21,9 @@ constexpr int kPrimTileH = 8;
 constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
+constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
+constexpr int kWfChunk = 2048;      // wavefront bounce kernel: general records per stage (32 KB)
+constexpr int kWfDefer = 24;        // per-thread queue of broad-phase groups awaiting their exact tests
 
 struct UpdateParams {
     SceneCamera cam;            // 176 B, lands in the kernel parameter constant bank
@@ -33,6 +36,12 @@ struct UpdateParams {
     uint32_t tiles_x, n_tiles;  // warp tiles over the window
     unsigned int* tile_counter; // dynamic tile schedulers, zeroed before the launch: [0] update, [1] primary pass
     const float4* prim;         // per-frame common-origin records (oc, -q), padded like geom; null = no primary pass
+    // wavefront bounces (max_depth > 1 after a primary pass): compacted path queues, three float4 planes of
+    // `wf_capacity` entries each: (o.xyz, d.x) (d.yz, factor.xy) (factor.z, bits(texel), bits(seed), bits(n))
+    float4* wf_queue[2];
+    unsigned int* wf_counts;    // [kWfMaxDepth + 1] queue lengths per bounce, then [kWfMaxDepth + 1] batch tickets
+    uint32_t wf_capacity;
+    uint32_t wf_bounce;         // bounce index this launch traces
     float2* first_hit;          // window texels x (t, bits(sphere index)): nearest hit of the primary ray found by
                                 // the primary pass; index -1 = miss, -2 = not traced (the update kernel scans it)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
