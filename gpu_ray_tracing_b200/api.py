@@ -121,6 +121,7 @@ _SIGNATURES = {
     "rt_write_accum": (C.c_int, [_P, _P]),
     "rt_read_rgba8": (C.c_int, [_P, _P]),
     "rt_read_rgba8_async": (C.c_int, [_P, _P]),
+    "rt_wavefront_counts": (C.c_int, [_P, _P, C.c_uint32, _P]),
     "rt_read_wait": (C.c_int, [_P]),
     "rt_rays_traced": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "rt_exact_tests": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
@@ -321,6 +322,13 @@ class Renderer:
         v = C.c_uint64(0)
         _check(lib().rt_exact_tests(self._h, C.byref(v)))
         return v.value
+
+    def wavefront_counts(self):
+        """Rays traced per bounce (index = bounce, >= 1) by the last deep update."""
+        buf = (C.c_uint32 * 80)()
+        n = C.c_uint32(0)
+        _check(lib().rt_wavefront_counts(self._h, buf, 80, C.byref(n)))
+        return [int(buf[i]) for i in range(n.value)]
 
     def reset_counters(self):
         _check(lib().rt_reset_counters(self._h))

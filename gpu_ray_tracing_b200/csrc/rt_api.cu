@@ -323,6 +323,21 @@ int rt_reset_counters(RtRenderer* r) {
     return RT_OK;
 }
 
+int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacity, uint32_t* n_out) {
+    RT_CHECK_HANDLE(r);
+    if (!counts || !n_out) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *n_out = 0;
+    if (!r->wf_counts) return RT_OK;   // no deep frame has run
+    unsigned int host[rtk::kWfMaxDepth + 1];
+    RT_CUDA(cudaMemcpyAsync(host, r->wf_counts, sizeof(host), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    uint32_t n = rtk::kWfMaxDepth + 1;
+    if (n > capacity) n = capacity;
+    for (uint32_t i = 0; i < n; ++i) counts[i] = host[i];
+    *n_out = n;
+    return RT_OK;
+}
+
 int rt_timer_begin(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
     RT_CUDA(cudaEventRecord(r->ev_begin, r->stream));

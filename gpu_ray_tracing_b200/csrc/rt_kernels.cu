@@ -790,6 +790,43 @@ __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t boun
     return true;
 }
 
+// narrow_phase with the broad test re-evaluated by the same packed operations as the scan (half the instructions
+// of the scalar form; the values are identical, each half of an FFMA2 being the IEEE fused operation).
+__device__ __forceinline__ void narrow_phase_packed(const float4* __restrict__ s_geom, int slot, int count, int index0,
+                                                    const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
+                                                    uint32_t& exact_tests) {
+#pragma unroll 1
+    for (int u = 0; u < count; ++u) {
+        const int idx = index0 + u;
+        if ((uint32_t)idx >= n_spheres) break;   // padding
+        const float4 sp = s_geom[slot + u];
+        bool cand[kPix];
+        bool some = false;
+#pragma unroll
+        for (int q = 0; q < kPairs; ++q) {
+            const float2 g = broad_g2(sp, L, q);
+            cand[2 * q] = L.alive[2 * q] && !(g.x < L.thr[2 * q]);
+            cand[2 * q + 1] = L.alive[2 * q + 1] && !(g.y < L.thr[2 * q + 1]);
+            some |= cand[2 * q] | cand[2 * q + 1];
+        }
+        if (!some) continue;
+        const float radius = __ldg(&spheres[idx].radius);
+        const f3 center = rtc::mk(sp.x, sp.y, sp.z);
+#pragma unroll
+        for (int p = 0; p < kPix; ++p) {
+            if (cand[p]) {
+                ++exact_tests;
+                float root;
+                if (rtc::sphere_root(origin_of(L, p), rtc::mk(L.dx[p], L.dy[p], L.dz[p]), L.a[p], center, radius, kTMin,
+                                     L.best_t[p], &root)) {
+                    L.best_t[p] = root;
+                    L.best_i[p] = idx;
+                }
+            }
+        }
+    }
+}
+
 // scan_spheres with the exact tests deferred (see the section header).  s_note: this thread's column of
 // [kWfDefer][kBlockThreads] group offsets.
 __device__ __forceinline__ void drain_notes(const float4* __restrict__ s_geom, int index0, const unsigned short* __restrict__ s_note,
@@ -798,7 +835,7 @@ __device__ __forceinline__ void drain_notes(const float4* __restrict__ s_geom, i
     for (int e = 0; __any_sync(kFull, e < n_notes); ++e) {
         if (e < n_notes) {
             const int s = (int)s_note[e * kBlockThreads];
-            narrow_phase(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
+            narrow_phase_packed(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
         }
     }
     n_notes = 0;
@@ -828,10 +865,8 @@ __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__
                 any |= !(g.y < L.thr[2 * q + 1]);
             }
         }
-        if (any) {
-            s_note[n_notes * kBlockThreads] = (unsigned short)s;
-            ++n_notes;
-        }
+        s_note[n_notes * kBlockThreads] = (unsigned short)s;   // slot n_notes < kWfDefer is free; kept only if `any`
+        n_notes += any ? 1 : 0;
         if (__any_sync(kFull, n_notes >= kWfDefer)) drain_notes(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) cur[u] = nxt[u];
@@ -890,8 +925,64 @@ __global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant_
     prim_flush(P, exact_tests, rays, lane);
 }
 
-// Traces queue P.wf_bounce.  A CTA takes batches of 1024 rays (4 per thread); the general records stream
-// through two bulk-copied stages exactly as in primary_hits_kernel.
+namespace {
+
+// Rays j0 + 32 p (p < kPix) of the queue into the thread's lanes.
+__device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
+                                             uint32_t j0, Lanes& L, uint32_t& rays) {
+#pragma unroll
+    for (int p = 0; p < kPix; ++p) {
+        const uint32_t j = j0 + 32u * (uint32_t)p;
+        if (j < count) {
+            const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
+            arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
+            ++rays;
+        } else {
+            idle_ray(L, p);
+        }
+    }
+}
+
+// Scatter / finish / re-queue the traced rays of the thread.  Called by whole warps.
+__device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
+                                           const Lanes& L, uint32_t bounce, bool last, bool reset, int lane) {
+#pragma unroll 1
+    for (int p = 0; p < kPix; ++p) {
+        const uint32_t j = j0 + 32u * (uint32_t)p;
+        bool push = false;
+        f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
+        uint32_t texel_index = 0, bseed = 0, n = 0;
+        if (j < count) {
+            const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+            factor = rtc::mk(B.z, B.w, C.x);
+            texel_index = __float_as_uint(C.y);
+            bseed = __float_as_uint(C.z);
+            n = __float_as_uint(C.w);
+            float best_t = kTMax;
+            int best_i = -1;
+            // p is a run-time index here: pick this ray's state without dynamic register indexing
+#pragma unroll
+            for (int k = 0; k < kPix; ++k) {
+                if (k == p) {
+                    o = origin_of(L, k);
+                    d = rtc::mk(L.dx[k], L.dy[k], L.dz[k]);
+                    best_t = L.best_t[k];
+                    best_i = L.best_i[k];
+                }
+            }
+            push = resolve_hit(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+        }
+        push_path(P, bounce + 1u, push, o, d, factor, texel_index, bseed, n, lane);
+    }
+}
+
+}  // namespace
+
+// Traces queue P.wf_bounce, 4 rays per thread.  The general records reach shared memory by bulk copies.
+//   scene fits one stage (<= kWfChunk records): copied once per CTA, then every WARP pulls batches of 128 rays on
+//     its own — no block barrier in the loop, so a warp with long exact-test queues delays nobody;
+//   larger scenes: a CTA takes batches of 1024 rays and streams the records through two stages as
+//     primary_hits_kernel does.
 __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     constexpr int kStage = kWfChunk + kGeomTail;
@@ -911,14 +1002,15 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
 
     const uint32_t bounce = P.wf_bounce;
     const uint32_t count = P.wf_counts[bounce];
-    const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
     const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
     const bool last = bounce + 1u >= max_depth;
     const bool reset = P.cam.camera_has_moved > 0.5f;
     const float4* qin = P.wf_queue[bounce & 1u];
+    unsigned int* ticket = &P.wf_counts[kWfMaxDepth + 1u + bounce];
     const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
     const int n_chunks = (n_pad + kWfChunk - 1) / kWfChunk;
     uint32_t exact_tests = 0, rays = 0, parity = 0;
+    if (count == 0u) return;
 
     auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
         const int base = c * kWfChunk;
@@ -928,65 +1020,46 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
         bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.geom + base, bytes, bar);
     };
 
-    for (;;) {
-        __syncthreads();
-        if (threadIdx.x == 0) s_batch = atomicAdd(&P.wf_counts[kWfMaxDepth + 1u + bounce], 1u);
-        __syncthreads();
-        const uint32_t batch = s_batch;
-        if (batch >= n_batches) break;
-        if (threadIdx.x == 0) {
-            request(0);
-            if (n_chunks > 1) request(1);
+    if (n_chunks == 1) {
+        if (threadIdx.x == 0) request(0);
+        mbar_wait(bar0, 0u);
+        const uint32_t n_batches = (count + 32u * kPix - 1u) / (32u * kPix);
+        for (;;) {
+            uint32_t batch = 0;
+            if (lane == 0) batch = atomicAdd(ticket, 1u);
+            batch = __shfl_sync(kFull, batch, 0);
+            if (batch >= n_batches) break;
+            const uint32_t j0 = batch * (32u * kPix) + (uint32_t)lane;
+            Lanes L;
+            wf_load_rays(P, qin, count, j0, L, rays);
+            scan_spheres_deferred(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+            wf_resolve(P, qin, count, j0, L, bounce, last, reset, lane);
         }
-        const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)lane;
-        Lanes L;
-#pragma unroll
-        for (int p = 0; p < kPix; ++p) {
-            const uint32_t j = j0 + 32u * (uint32_t)p;
-            if (j < count) {
-                const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
-                arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
-                ++rays;
-            } else {
-                idle_ray(L, p);
+    } else {
+        const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
+        for (;;) {
+            __syncthreads();
+            if (threadIdx.x == 0) s_batch = atomicAdd(ticket, 1u);
+            __syncthreads();
+            const uint32_t batch = s_batch;
+            if (batch >= n_batches) break;
+            if (threadIdx.x == 0) {
+                request(0);
+                request(1);
             }
-        }
-        for (int c = 0; c < n_chunks; ++c) {
-            const int st = c & 1, base = c * kWfChunk;
-            mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
-            parity ^= 1u << st;
-            scan_spheres_deferred(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres, P.n_spheres, L,
-                                  exact_tests);
-            __syncthreads();   // every warp has left stage st
-            if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
-        }
-#pragma unroll 1
-        for (int p = 0; p < kPix; ++p) {
-            const uint32_t j = j0 + 32u * (uint32_t)p;
-            bool push = false;
-            f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
-            uint32_t texel_index = 0, bseed = 0, n = 0;
-            if (j < count) {
-                const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
-                factor = rtc::mk(B.z, B.w, C.x);
-                texel_index = __float_as_uint(C.y);
-                bseed = __float_as_uint(C.z);
-                n = __float_as_uint(C.w);
-                float best_t = kTMax;
-                int best_i = -1;
-                // p is a run-time index here: pick this ray's state without dynamic register indexing
-#pragma unroll
-                for (int k = 0; k < kPix; ++k) {
-                    if (k == p) {
-                        o = origin_of(L, k);
-                        d = rtc::mk(L.dx[k], L.dy[k], L.dz[k]);
-                        best_t = L.best_t[k];
-                        best_i = L.best_i[k];
-                    }
-                }
-                push = resolve_hit(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+            const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)lane;
+            Lanes L;
+            wf_load_rays(P, qin, count, j0, L, rays);
+            for (int c = 0; c < n_chunks; ++c) {
+                const int st = c & 1, base = c * kWfChunk;
+                mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
+                parity ^= 1u << st;
+                scan_spheres_deferred(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres,
+                                      P.n_spheres, L, exact_tests);
+                __syncthreads();   // every warp has left stage st
+                if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
             }
-            push_path(P, bounce + 1u, push, o, d, factor, texel_index, bseed, n, lane);
+            wf_resolve(P, qin, count, j0, L, bounce, last, reset, lane);
         }
     }
     prim_flush(P, exact_tests, rays, lane);

@@ -20,3 +20,5 @@ with rt.Renderer(W, H) as r:
         r.update(cam)
     r.synchronize()
     print("rays", r.rays_traced())
+    if depth > 1:
+        print("per-bounce queue lengths", r.wavefront_counts()[:depth + 1])
