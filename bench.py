@@ -281,6 +281,24 @@ def run_ours(args):
     flops_per_launch = float(W) * H * N_SPHERES * FLOP_PER_TEST
     achieved_tf = flops_per_launch / (kernel_ms * 1e-3) / 1e12
 
+    # ---- the reference's default depth (max_depth 30), rays counted by the kernels -------
+    deep = None
+    if rank == 0:
+        cam30 = scenes.camera(W, H, 30, 500)
+        r.init()
+        r.update(cam30)
+        r.synchronize()
+        r.reset_counters()
+        r.timer_begin()
+        n_deep = 5
+        for _ in range(n_deep):
+            r.update(cam30)            # camera_has_moved = 1: every frame restarts the same first sample
+        deep_ms = r.timer_end() / n_deep
+        deep_rays = r.rays_traced() / n_deep
+        deep = {"max_depth": 30, "ms_per_frame": deep_ms, "rays_per_frame": deep_rays, "mrays_s": deep_rays / deep_ms / 1e3,
+                "note": "primary pass + shade_first_kernel + 29 wavefront bounce launches over compacted path queues"}
+        r.init()
+
     # ---- end to end through the C ABI with HOST buffers ----------------------------------------
     # per step: sphere buffer uploaded from pinned host memory (the reference re-creates its buffers
     # from host memory every frame, src/lib.rs:151-207), the 176-byte camera uniform rides in the
@@ -371,7 +389,7 @@ def run_ours(args):
                 "call": "rt_set_scene + rt_update + rt_read_rgba8_async per frame (two pinned host frames, read-back of "
                         "frame i overlaps the kernel of frame i+1), rt_read_wait before the clock stops",
                 "blocking_read_value": e2e_sync_value, "checksum": checksum},
-        "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
+        "deep": deep, "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
         "wall_ms_per_step": wall_ms / K,
     }
     print(json.dumps(line), flush=True)

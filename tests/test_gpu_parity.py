@@ -219,3 +219,25 @@ def test_async_readback_matches_blocking_read():
         r.read_wait()
     for w, buf in zip(want, bufs):
         assert np.array_equal(w, buf.numpy())
+
+
+def test_wavefront_counts_and_depth_fallback():
+    """Deep frames: the per-bounce queue lengths add up to the rays the oracle traces; max_depth beyond the
+    wavefront's 64-bounce bookkeeping takes the in-kernel bounce loop and still matches."""
+    W, H = 200, 120
+    scene = scenes.default_scene()
+    cam = scenes.camera(W, H, max_depth=12, spp=500)
+    cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        r.update(cam)
+        gpu, rays_gpu, counts = r.read_accum(), r.rays_traced(), r.wavefront_counts()
+    assert_parity(gpu, cpu, "wavefront depth 12")
+    assert rays_gpu == rays_cpu == W * H + sum(counts[1:12]) and counts[12] == 0 and counts[1] > 0
+    for depth in (64, 65):
+        cam = scenes.camera(W, H, max_depth=depth, spp=500, defocus_angle=0.0)
+        cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+        gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
+        assert rays_gpu == rays_cpu
+        assert_parity(gpu, cpu, f"depth {depth}")
