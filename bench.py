@@ -39,6 +39,25 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# stdout carries exactly ONE line, the JSON: everything else that libraries write to fd 1 (e.g. NCCL's
+# "NCCL version ..." banner) is sent to stderr by pointing fd 1 at fd 2 for the duration of the run.
+_JSON_FD = None
+
+
+def capture_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_json(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, data)
+
+
 def workload_config(n_gpus):
     return {
         "workload": f"{N_SPHERES} random spheres (seed 1234) at {W}x{H}, max_depth 1, 1 sample/pixel, one frame per GPU per step",
@@ -163,7 +182,7 @@ def run_reference(args):
         "note": "CPU restatement of compute_shader.wgsl (oracle/rt_oracle.cpp, g++ -O2 -ffp-contract=off, OpenMP); "
                 "the reference shader via wgpu/lavapipe is unavailable on this box",
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -392,7 +411,7 @@ def run_ours(args):
         "deep": deep, "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
         "wall_ms_per_step": wall_ms / K,
     }
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -406,6 +425,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    capture_stdout()
     if args.impl == "reference":
         if args.steps == 400:
             args.steps, args.warmup = 10, 1
