@@ -108,3 +108,12 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     }
     if (stats) { stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced; }
 }
+
+// Direct access to the primary-pass record functions for invariant tests.
+extern "C" __attribute__((visibility("default")))
+double emu_primary_rho(const SceneCamera* cam) { return rtc::primary_rho(*cam); }
+
+extern "C" __attribute__((visibility("default")))
+void emu_primary_record(const SceneCamera* cam, const GpuSphere* sphere, float* out4) {
+    rtc::primary_record(*sphere, rtc::mk(cam->center), rtc::primary_rho(*cam), out4);
+}

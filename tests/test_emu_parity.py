@@ -71,3 +71,64 @@ def test_broad_phase_is_conservative_on_adversarial_geometry():
             emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
             assert violations == 0 and rays == rays_e
             assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))
+
+
+def test_randomised_scenes_and_cameras_audit():
+    """Seeded random scenes (log-uniform radii over 5 decades, clustered and overlapping spheres) seen by random
+    cameras — pinhole and wide defocus disks, inside clusters, far away, huge and tiny fields of view: neither broad
+    phase may reject a pair the reference hits, and the image stays bit-identical."""
+    rng = np.random.default_rng(20261104)
+    for case in range(24):
+        n = int(rng.integers(1, 400))
+        sp = np.zeros(n, dtype=rt.SPHERE_DTYPE)
+        spread = float(np.exp(rng.uniform(np.log(0.5), np.log(500.0))))
+        sp["position"] = rng.normal(0.0, spread, (n, 3)).astype(np.float32)
+        sp["radius"] = np.exp(rng.uniform(np.log(1e-3), np.log(1e2), n)).astype(np.float32) * np.float32(spread / 10.0)
+        sp["color"] = rng.uniform(0, 1, (n, 4)).astype(np.float32)
+        sp["color"][:, 3] = rng.choice([-2.0, 0.0, 0.3, 2.0], n)
+        sp["color"][sp["color"][:, 3] == 2.0, 0] = 1.5
+        scene = rt.SphereCollection(sp, n)
+        look_from = tuple(float(v) for v in rng.normal(0.0, spread * float(rng.choice([0.3, 1.0, 4.0, 40.0])), 3))
+        W, H = 40, 22
+        cam = scenes.camera(W, H, max_depth=int(rng.integers(1, 6)), spp=500, look_from=look_from,
+                            fov=float(rng.choice([1.0, 20.0, 90.0, 150.0])),
+                            defocus_angle=float(rng.choice([0.0, 0.6, 10.0, 60.0])), random_seed=float(rng.uniform(0, 1)))
+        cpu, rays = ol.oracle_update(cam, scene, W, H)
+        for variant in (0, 2):
+            emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
+            assert violations == 0, (case, variant, violations)
+            assert rays_e == rays
+            assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32)), (case, variant)
+
+
+def test_primary_records_are_conservative_by_construction():
+    """primary_rho / primary_record invariants checked directly: always-candidate record when the camera centre is
+    inside or within the slack of the (inflated) sphere, a negative threshold otherwise, and rho >= the largest
+    |origin - centre| the shader itself produces for that camera."""
+    import ctypes as C
+    lib = ol.emu()
+    lib.emu_primary_record.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.emu_primary_rho.restype = C.c_double
+    lib.emu_primary_rho.argtypes = [C.c_void_p]
+    W, H = 64, 36
+    for defocus in (0.0, 0.6, 25.0):
+        cam = scenes.camera(W, H, defocus_angle=defocus)
+        rho = lib.emu_primary_rho(C.byref(cam))
+        assert rho >= 0.0 and (rho == 0.0) == (defocus == 0.0)
+        # origins the shader generates (oracle_get_ray) never leave the rho ball
+        out = np.zeros(6, dtype=np.float32)
+        worst = 0.0
+        for s in range(0, 4000, 7):
+            ol.oracle().oracle_get_ray(C.byref(cam), s % W, (s // W) % H, 12345 + s, out.ctypes.data_as(C.c_void_p))
+            worst = max(worst, float(np.linalg.norm(out[:3].astype(np.float64) - np.array(cam.center.tuple(), dtype=np.float64))))
+        assert worst <= rho
+        sp = np.zeros(3, dtype=rt.SPHERE_DTYPE)
+        c = np.array(cam.center.tuple(), dtype=np.float32)
+        sp["position"][0], sp["radius"][0] = c + np.float32(0.5), 2.0          # centre inside
+        sp["position"][1], sp["radius"][1] = c + np.array([3.0, 0, 0], np.float32), 3.0 - 1e-5   # just outside, within the slack
+        sp["position"][2], sp["radius"][2] = c + np.array([0, 0, -50.0], np.float32), 1.0        # well outside
+        rec = np.zeros((3, 4), dtype=np.float32)
+        for i in range(3):
+            lib.emu_primary_record(C.byref(cam), sp[i:i + 1].ctypes.data_as(C.c_void_p), rec[i].ctypes.data_as(C.c_void_p))
+        assert tuple(rec[0]) == (0.0, 0.0, 0.0, 1.0) and tuple(rec[1]) == (0.0, 0.0, 0.0, 1.0)
+        assert rec[2][3] < 0.0 and abs(-rec[2][3] - np.sqrt(50.0 ** 2 - (1.0 + rho) ** 2)) < 0.02

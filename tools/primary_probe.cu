@@ -131,6 +131,25 @@ __global__ void __launch_bounds__(256) scan_kernel(const float4* __restrict__ ge
                     }
                 }
                 any = (FORM == 3) ? (acc >= 0) : !(m < 0.0f);
+            } else if (FORM == 9) {
+                // sphere-pair layout: cur[2k] = (x0, x1, y0, y1), cur[2k+1] = (z0, z1, w0, w1) of spheres (2k, 2k+1);
+                // the ray components are the broadcast scalars, the 64-bit sphere operands repeat across rays
+                int acc = -1;
+#pragma unroll
+                for (int k = 0; k < UNROLL / 2; ++k) {
+                    const float2 sx = make_float2(cur[2 * k].x, cur[2 * k].y), sy = make_float2(cur[2 * k].z, cur[2 * k].w);
+                    const float2 sz = make_float2(cur[2 * k + 1].x, cur[2 * k + 1].y), sw = make_float2(cur[2 * k + 1].z, cur[2 * k + 1].w);
+#pragma unroll
+                    for (int q = 0; q < PAIRS; ++q) {
+                        const float2 h0 = __ffma2_rn(sx, make_float2(ux[q].x, ux[q].x),
+                                          __ffma2_rn(sy, make_float2(uy[q].x, uy[q].x), __ffma2_rn(sz, make_float2(uz[q].x, uz[q].x), sw)));
+                        const float2 h1 = __ffma2_rn(sx, make_float2(ux[q].y, ux[q].y),
+                                          __ffma2_rn(sy, make_float2(uy[q].y, uy[q].y), __ffma2_rn(sz, make_float2(uz[q].y, uz[q].y), sw)));
+                        acc &= __float_as_int(h0.x) & __float_as_int(h0.y);
+                        acc &= __float_as_int(h1.x) & __float_as_int(h1.y);
+                    }
+                }
+                any = acc >= 0;
             } else if (FORM == 8) {
                 // like 3, but ray-pair major: the 64-bit ray operand repeats across consecutive FFMA2s
                 int acc = -1;
@@ -258,7 +277,7 @@ int main() {
     cudaMemcpyToSymbol(c_geom, hg, (n + 16) * 16);
     for (int bps = 2; bps <= 3; ++bps) {
         RUN(3, 4, 4, bps); RUN(3, 4, 8, bps);
-        RUN(8, 2, 4, bps); RUN(8, 2, 8, bps); RUN(8, 4, 4, bps); RUN(8, 4, 8, bps); RUN(8, 8, 4, bps);
+        RUN(9, 2, 4, bps); RUN(9, 2, 8, bps); RUN(9, 4, 4, bps); RUN(9, 4, 8, bps); RUN(9, 8, 4, bps);
     }
     return 0;
 }
