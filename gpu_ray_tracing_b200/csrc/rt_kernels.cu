@@ -792,6 +792,7 @@ __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t boun
 
 // narrow_phase with the broad test re-evaluated by the same packed operations as the scan (half the instructions
 // of the scalar form; the values are identical, each half of an FFMA2 being the IEEE fused operation).
+template <int NP>
 __device__ __forceinline__ void narrow_phase_packed(const float4* __restrict__ s_geom, int slot, int count, int index0,
                                                     const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
                                                     uint32_t& exact_tests) {
@@ -800,10 +801,10 @@ __device__ __forceinline__ void narrow_phase_packed(const float4* __restrict__ s
         const int idx = index0 + u;
         if ((uint32_t)idx >= n_spheres) break;   // padding
         const float4 sp = s_geom[slot + u];
-        bool cand[kPix];
+        bool cand[2 * NP];
         bool some = false;
 #pragma unroll
-        for (int q = 0; q < kPairs; ++q) {
+        for (int q = 0; q < NP; ++q) {
             const float2 g = broad_g2(sp, L, q);
             cand[2 * q] = L.alive[2 * q] && !(g.x < L.thr[2 * q]);
             cand[2 * q + 1] = L.alive[2 * q + 1] && !(g.y < L.thr[2 * q + 1]);
@@ -813,7 +814,7 @@ __device__ __forceinline__ void narrow_phase_packed(const float4* __restrict__ s
         const float radius = __ldg(&spheres[idx].radius);
         const f3 center = rtc::mk(sp.x, sp.y, sp.z);
 #pragma unroll
-        for (int p = 0; p < kPix; ++p) {
+        for (int p = 0; p < 2 * NP; ++p) {
             if (cand[p]) {
                 ++exact_tests;
                 float root;
@@ -829,18 +830,20 @@ __device__ __forceinline__ void narrow_phase_packed(const float4* __restrict__ s
 
 // scan_spheres with the exact tests deferred (see the section header).  s_note: this thread's column of
 // [kWfDefer][kBlockThreads] group offsets.
+template <int NP>
 __device__ __forceinline__ void drain_notes(const float4* __restrict__ s_geom, int index0, const unsigned short* __restrict__ s_note,
                                             int& n_notes, const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
                                             uint32_t& exact_tests) {
     for (int e = 0; __any_sync(kFull, e < n_notes); ++e) {
         if (e < n_notes) {
             const int s = (int)s_note[e * kBlockThreads];
-            narrow_phase_packed(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
+            narrow_phase_packed<NP>(s_geom, s, kUnroll, index0 + s, spheres, n_spheres, L, exact_tests);
         }
     }
     n_notes = 0;
 }
 
+template <int NP>
 __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__ s_geom, int count, int index0,
                                                       unsigned short* __restrict__ s_note, const GpuSphere* __restrict__ spheres,
                                                       uint32_t n_spheres, Lanes& L, uint32_t& exact_tests) {
@@ -859,7 +862,7 @@ __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
 #pragma unroll
-            for (int q = 0; q < kPairs; ++q) {
+            for (int q = 0; q < NP; ++q) {
                 const float2 g = broad_g2(cur[u], L, q);
                 any |= !(g.x < L.thr[2 * q]);
                 any |= !(g.y < L.thr[2 * q + 1]);
@@ -867,11 +870,11 @@ __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__
         }
         s_note[n_notes * kBlockThreads] = (unsigned short)s;   // slot n_notes < kWfDefer is free; kept only if `any`
         n_notes += any ? 1 : 0;
-        if (__any_sync(kFull, n_notes >= kWfDefer)) drain_notes(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
+        if (__any_sync(kFull, n_notes >= kWfDefer)) drain_notes<NP>(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) cur[u] = nxt[u];
     }
-    drain_notes(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
+    drain_notes<NP>(s_geom, index0, s_note, n_notes, spheres, n_spheres, L, exact_tests);
 }
 
 }  // namespace
@@ -927,13 +930,14 @@ __global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant_
 
 namespace {
 
-// Rays j0 + 32 p (p < kPix) of the queue into the thread's lanes.
+// Rays j0 + 32 p (p < NR) of the queue into the thread's first NR lanes; the others idle.
+template <int NR>
 __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                              uint32_t j0, Lanes& L, uint32_t& rays) {
 #pragma unroll
     for (int p = 0; p < kPix; ++p) {
         const uint32_t j = j0 + 32u * (uint32_t)p;
-        if (j < count) {
+        if (p < NR && j < count) {
             const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
             arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
             ++rays;
@@ -944,10 +948,11 @@ __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4
 }
 
 // Scatter / finish / re-queue the traced rays of the thread.  Called by whole warps.
+template <int NR>
 __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
                                            const Lanes& L, uint32_t bounce, bool last, bool reset, int lane) {
 #pragma unroll 1
-    for (int p = 0; p < kPix; ++p) {
+    for (int p = 0; p < NR; ++p) {
         const uint32_t j = j0 + 32u * (uint32_t)p;
         bool push = false;
         f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
@@ -1023,17 +1028,36 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
     if (n_chunks == 1) {
         if (threadIdx.x == 0) request(0);
         mbar_wait(bar0, 0u);
-        const uint32_t n_batches = (count + 32u * kPix - 1u) / (32u * kPix);
-        for (;;) {
-            uint32_t batch = 0;
-            if (lane == 0) batch = atomicAdd(ticket, 1u);
-            batch = __shfl_sync(kFull, batch, 0);
-            if (batch >= n_batches) break;
-            const uint32_t j0 = batch * (32u * kPix) + (uint32_t)lane;
-            Lanes L;
-            wf_load_rays(P, qin, count, j0, L, rays);
-            scan_spheres_deferred(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
-            wf_resolve(P, qin, count, j0, L, bounce, last, reset, lane);
+        // A warp's batch costs a full pass over the records however many of its ray slots are in use, so once the
+        // queue no longer fills every resident warp with 4 rays per thread, batches shrink to 2 rays per thread (one
+        // FFMA2 pair): a quarter of the latency per batch, twice the batches, and the machine stays busy.
+        const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
+        if (count >= resident_warps * (32u * kPix)) {
+            const uint32_t n_batches = (count + 32u * kPix - 1u) / (32u * kPix);
+            for (;;) {
+                uint32_t batch = 0;
+                if (lane == 0) batch = atomicAdd(ticket, 1u);
+                batch = __shfl_sync(kFull, batch, 0);
+                if (batch >= n_batches) break;
+                const uint32_t j0 = batch * (32u * kPix) + (uint32_t)lane;
+                Lanes L;
+                wf_load_rays<kPix>(P, qin, count, j0, L, rays);
+                scan_spheres_deferred<kPairs>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+                wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
+            }
+        } else {
+            const uint32_t n_batches = (count + 63u) / 64u;
+            for (;;) {
+                uint32_t batch = 0;
+                if (lane == 0) batch = atomicAdd(ticket, 1u);
+                batch = __shfl_sync(kFull, batch, 0);
+                if (batch >= n_batches) break;
+                const uint32_t j0 = batch * 64u + (uint32_t)lane;
+                Lanes L;
+                wf_load_rays<2>(P, qin, count, j0, L, rays);
+                scan_spheres_deferred<1>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+                wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
+            }
         }
     } else {
         const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
@@ -1049,17 +1073,17 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
             }
             const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)lane;
             Lanes L;
-            wf_load_rays(P, qin, count, j0, L, rays);
+            wf_load_rays<kPix>(P, qin, count, j0, L, rays);
             for (int c = 0; c < n_chunks; ++c) {
                 const int st = c & 1, base = c * kWfChunk;
                 mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
                 parity ^= 1u << st;
-                scan_spheres_deferred(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres,
+                scan_spheres_deferred<kPairs>(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres,
                                       P.n_spheres, L, exact_tests);
                 __syncthreads();   // every warp has left stage st
                 if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
             }
-            wf_resolve(P, qin, count, j0, L, bounce, last, reset, lane);
+            wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
         }
     }
     prim_flush(P, exact_tests, rays, lane);
