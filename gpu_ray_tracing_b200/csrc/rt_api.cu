@@ -204,7 +204,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant == 4)) {
         // first deep frame: path queues for the wavefront bounces (two queues x three float4 planes)
         for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
-        RT_CUDA(cudaMalloc(&r->wf_counts, 2 * (rtk::kWfMaxDepth + 1) * sizeof(unsigned int)));
+        RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
     }
     p.wf_queue[0] = r->wf_queue[0];
     p.wf_queue[1] = r->wf_queue[1];
@@ -329,7 +329,7 @@ int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacity, uint
     *n_out = 0;
     if (!r->wf_counts) return RT_OK;   // no deep frame has run
     unsigned int host[rtk::kWfMaxDepth + 1];
-    RT_CUDA(cudaMemcpyAsync(host, r->wf_counts, sizeof(host), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaMemcpyAsync(host, r->wf_counts + 2 * (rtk::kWfMaxDepth + 1), sizeof(host), cudaMemcpyDeviceToHost, r->stream));
     RT_CUDA(cudaStreamSynchronize(r->stream));
     uint32_t n = rtk::kWfMaxDepth + 1;
     if (n > capacity) n = capacity;

@@ -981,6 +981,71 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
     }
 }
 
+
+// Few paths left (less than RT_WF_COMPLETE_BELOW rays per resident warp): finish them inside ONE launch, every
+// remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
+// queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
+// costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
+#ifndef RT_WF_COMPLETE_BELOW
+#define RT_WF_COMPLETE_BELOW 32u
+#endif
+__device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
+                                          const float4* __restrict__ s_stage, int n_pad, unsigned short* __restrict__ s_note,
+                                          unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
+                                          uint32_t& exact_tests_out, uint32_t& rays_out, uint32_t& rays_later_out) {
+    const uint32_t n_batches = (count + 63u) / 64u;
+    unsigned int* traced = &P.wf_counts[2u * (kWfMaxDepth + 1u)];
+    uint32_t exact_tests = 0, rays = 0, rays_later = 0;
+    for (;;) {
+        uint32_t batch = 0;
+        if (lane == 0) batch = atomicAdd(ticket, 1u);
+        batch = __shfl_sync(kFull, batch, 0);
+        if (batch >= n_batches) break;
+        const uint32_t j0 = batch * 64u + (uint32_t)lane;
+        Lanes L;
+        wf_load_rays<2>(P, qin, count, j0, L, rays);
+        f3 factor[2];
+        uint32_t texel_index[2], bseed[2], n_samples[2];
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const uint32_t j = j0 + 32u * (uint32_t)p;
+            factor[p] = rtc::mk(0.0f, 0.0f, 0.0f);
+            texel_index[p] = bseed[p] = n_samples[p] = 0u;
+            if (j < count) {
+                const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+                factor[p] = rtc::mk(B.z, B.w, C.x);
+                texel_index[p] = __float_as_uint(C.y);
+                bseed[p] = __float_as_uint(C.z);
+                n_samples[p] = __float_as_uint(C.w);
+            }
+        }
+        for (uint32_t b = bounce;; ++b) {
+            scan_spheres_deferred<1>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+#pragma unroll
+            for (int p = 0; p < 2; ++p) {
+                if (!L.alive[p]) continue;
+                f3 o = origin_of(L, p), d = rtc::mk(L.dx[p], L.dy[p], L.dz[p]);
+                const bool go = resolve_hit(P, b, b + 1u >= max_depth, L.best_i[p], L.best_t[p], o, d, factor[p],
+                                            texel_index[p], bseed[p], n_samples[p], reset);
+                if (go) {
+                    arm_ray(L, p, o, d);
+                } else {
+                    idle_ray(L, p);
+                }
+            }
+            const unsigned m0 = __ballot_sync(kFull, L.alive[0]), m1 = __ballot_sync(kFull, L.alive[1]);
+            if ((m0 | m1) == 0u) break;
+            if (lane == 0) atomicAdd(&traced[b + 1u], (unsigned)(__popc(m0) + __popc(m1)));
+            const uint32_t mine = (L.alive[0] ? 1u : 0u) + (L.alive[1] ? 1u : 0u);
+            rays += mine;
+            rays_later += mine;
+        }
+    }
+    exact_tests_out += exact_tests;
+    rays_out += rays;
+    rays_later_out += rays_later;
+}
+
 }  // namespace
 
 // Traces queue P.wf_bounce, 4 rays per thread.  The general records reach shared memory by bulk copies.
@@ -988,6 +1053,10 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 //     its own — no block barrier in the loop, so a warp with long exact-test queues delays nobody;
 //   larger scenes: a CTA takes batches of 1024 rays and streams the records through two stages as
 //     primary_hits_kernel does.
+// kFinish: the instantiation the later bounces (>= kWfFinishFrom) use, which may finish a short queue in one launch
+// (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code: its
+// mere presence costs the full-queue loops 1.6 % (out of line) to 3 % (inlined), measured on the depth-30 4K frame.
+template <bool kFinish>
 __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     constexpr int kStage = kWfChunk + kGeomTail;
@@ -1014,7 +1083,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
     unsigned int* ticket = &P.wf_counts[kWfMaxDepth + 1u + bounce];
     const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
     const int n_chunks = (n_pad + kWfChunk - 1) / kWfChunk;
-    uint32_t exact_tests = 0, rays = 0, parity = 0;
+    uint32_t exact_tests = 0, rays = 0, rays_later = 0, parity = 0;
     if (count == 0u) return;
 
     auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
@@ -1045,7 +1114,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
                 scan_spheres_deferred<kPairs>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
                 wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
             }
-        } else {
+        } else if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
             const uint32_t n_batches = (count + 63u) / 64u;
             for (;;) {
                 uint32_t batch = 0;
@@ -1058,6 +1127,9 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
                 scan_spheres_deferred<1>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
                 wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
             }
+        } else {
+            finish_paths(P, qin, count, s_stage, n_pad, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays,
+                         rays_later);
         }
     } else {
         const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
@@ -1085,6 +1157,12 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
             }
             wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
         }
+    }
+    {   // rays traced at this bounce (the to-completion path adds its later bounces itself)
+        uint32_t mine = rays - rays_later;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(kFull, mine, o);
+        if (lane == 0 && mine) atomicAdd(&P.wf_counts[2u * (kWfMaxDepth + 1u) + bounce], mine);
     }
     prim_flush(P, exact_tests, rays, lane);
 }
@@ -1302,7 +1380,9 @@ cudaError_t configure_kernels() {
     e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
+    e = cudaFuncSetAttribute(bounce_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bounce_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
@@ -1349,14 +1429,25 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         const uint32_t depth = rtc::f2u(p.cam.max_depth);
         if (p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth) {
             // wavefront: shade the primary hits, then one launch per bounce over the compacted survivors
-            e = cudaMemsetAsync(p.wf_counts, 0, 2 * (kWfMaxDepth + 1) * sizeof(unsigned int), stream);
+            e = cudaMemsetAsync(p.wf_counts, 0, kWfWords * sizeof(unsigned int), stream);
             if (e != cudaSuccess) return e;
             const uint64_t n_texels = (uint64_t)p.width * p.row_count;
             shade_first_kernel<<<(unsigned)((n_texels + 255) / 256), 256, 0, stream>>>(p);
             n_launch += 1;
+            // First bounce launched with the finishing code compiled in: not before the queue can be short enough to
+            // use it, assuming it shrinks by no more than a fifth per bounce (texels * 0.8^b < 8 * the short-queue
+            // threshold).  A scene that sheds paths faster only delays the switch by a few cheap launches.
+            const double short_queue = (double)resident * (kBlockThreads / 32) * RT_WF_COMPLETE_BELOW;
+            uint32_t finish_from = kWfFinishFrom;
+            for (double q = (double)n_texels; q > 8.0 * short_queue && finish_from < depth; q *= 0.8) ++finish_from;
+            finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                bounce_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                if (b < finish_from) {
+                    bounce_kernel<false><<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                } else {
+                    bounce_kernel<true><<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                }
                 n_launch += 1;
             }
             if (launches) *launches = n_launch;

@@ -22,6 +22,8 @@ constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
+constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
+constexpr uint32_t kWfFinishFrom = 3;                   // first bounce whose launch may finish a short queue to the end
 constexpr int kWfChunk = 2048;      // wavefront bounce kernel: general records per stage (32 KB)
 constexpr int kWfDefer = 24;        // per-thread queue of broad-phase groups awaiting their exact tests
 
@@ -39,7 +41,7 @@ struct UpdateParams {
     // wavefront bounces (max_depth > 1 after a primary pass): compacted path queues, three float4 planes of
     // `wf_capacity` entries each: (o.xyz, d.x) (d.yz, factor.xy) (factor.z, bits(texel), bits(seed), bits(n))
     float4* wf_queue[2];
-    unsigned int* wf_counts;    // [kWfMaxDepth + 1] queue lengths per bounce, then [kWfMaxDepth + 1] batch tickets
+    unsigned int* wf_counts;    // 3 x [kWfMaxDepth + 1]: queue length per bounce, batch tickets, rays traced per bounce (kWfWords)
     uint32_t wf_capacity;
     uint32_t wf_bounce;         // bounce index this launch traces
     float2* first_hit;          // window texels x (t, bits(sphere index)): nearest hit of the primary ray found by

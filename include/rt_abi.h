@@ -171,8 +171,8 @@ RT_API int rt_rays_traced(RtRenderer* r, uint64_t* rays);
 /* Number of (ray, sphere) pairs that went through the exact quadratic after the broad phase. */
 RT_API int rt_exact_tests(RtRenderer* r, uint64_t* tests);
 RT_API int rt_reset_counters(RtRenderer* r);
-/* Lengths of the wavefront path queues of the last deep (max_depth > 1) update: counts[b] = rays traced at bounce b
- * for b >= 1 (counts[0] is unused: bounce 0 is the primary pass).  *n_out = entries written (0 before any deep frame). */
+/* Rays the wavefront traced per bounce in the last deep (max_depth > 1) update: counts[b] for b >= 1 (counts[0] is
+ * unused: bounce 0 is the primary pass).  *n_out = entries written (0 before any deep frame). */
 RT_API int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacity, uint32_t* n_out);
 
 /* Device-side timing of the update kernels on the renderer's own stream (CUDA events). */

@@ -44,6 +44,9 @@ if __name__ == "__main__":
         ms, rays, exact = time_variant(scene5, cam5, 1920, 1080, variant, 3)
         print(f"grid65536 1080p d1     variant {variant}: {ms:8.3f} ms  {rays / ms / 1e3:9.1f} Mrays/s  "
               f"{rays * 18 * 65536 / ms / 1e9:7.2f} TFLOP/s(alg)  exact/ray {exact / max(rays, 1):.2f}", flush=True)
+    for variant in (4, 2):
+        ms, rays, exact = time_variant(scenes.default_scene(), scenes.camera(1280, 720, 30, 500), 1280, 720, variant, 20)
+        print(f"default 720p depth30   variant {variant}: {ms:8.3f} ms  {rays / ms / 1e3:9.1f} Mrays/s  rays/frame {rays:.0f}", flush=True)
     W, H = 3840, 2160
     for name, scene, cam in (
         ("random1024 depth1", scenes.random_scene(1024), scenes.camera(W, H, 1, 1)),
