@@ -4,7 +4,7 @@ The product is the CUDA shared library behind include/rt_abi.h; this package is 
 layer that mirrors the reference's names for tests, benchmarks and headless use.
 """
 from .api import (  # noqa: F401
-    CameraSettings, ComputeShaderNode, ComputeShaderState, GpuSphere, MultiRenderer, Renderer, RtError, RtVec3,
+    CameraSettings, ComputeShaderNode, Key, camera_movement_system, camera_script, ComputeShaderState, GpuSphere, MultiRenderer, Renderer, RtError, RtVec3,
     SceneCamera, SphereCollection, SPHERE_DTYPE, create_default_spheres, create_grid_spheres,
     create_random_spheres, device_count, lib, orbit_camera, render, render_frames, shard_rows, write_ppm,
 )

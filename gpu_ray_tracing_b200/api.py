@@ -154,6 +154,9 @@ _SIGNATURES = {
     "rt_create_random_spheres": (C.c_int, [C.c_uint64, C.c_uint32, _P]),
     "rt_create_grid_spheres": (C.c_int, [C.c_uint64, C.c_uint32, _P]),
     "rt_orbit_camera": (C.c_int, [C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.POINTER(SceneCamera)]),
+    "rt_camera_step": (C.c_int, [C.POINTER(CameraSettings), C.c_uint32, C.c_float]),
+    "rt_camera_script": (C.c_int, [C.POINTER(CameraSettings), C.POINTER(C.c_uint32), C.c_uint32, C.c_float, C.POINTER(C.c_float),
+                                   C.c_uint32, C.c_uint32, C.POINTER(SceneCamera)]),
 }
 
 
@@ -230,6 +233,36 @@ def orbit_camera(k: int, n: int, width: int, height: int, radius: float = 60.0, 
     out = SceneCamera()
     _check(lib().rt_orbit_camera(k, n, radius, cam_height, fov_deg, width, height, C.byref(out)))
     return out
+
+
+class Key(enum.IntFlag):
+    """Keys of camera_movement_system (src/camera.rs:125-253); values are the RT_KEY_* masks of rt_abi.h."""
+    W = 0x001
+    S = 0x002
+    A = 0x004
+    D = 0x008
+    ARROW_UP = 0x010
+    ARROW_DOWN = 0x020
+    ARROW_LEFT = 0x040
+    ARROW_RIGHT = 0x080
+    DIGIT1 = 0x100
+    DIGIT2 = 0x200
+
+
+def camera_movement_system(settings: CameraSettings, keys: int, dt: float) -> CameraSettings:
+    """One frame of the reference's keyboard controller, in place (camera.rs:125-253)."""
+    _check(lib().rt_camera_step(C.byref(settings), int(keys), dt))
+    return settings
+
+
+def camera_script(settings: CameraSettings, keys, dt: float, width: int, height: int, seeds=None):
+    """Scripted fly-through: one controller frame + uniform derivation per entry of `keys`; returns the SceneCameras."""
+    n = len(keys)
+    key_arr = (C.c_uint32 * n)(*[int(k) for k in keys])
+    seed_arr = (C.c_float * n)(*seeds) if seeds is not None else None
+    out = (SceneCamera * n)()
+    _check(lib().rt_camera_script(C.byref(settings), key_arr, n, dt, seed_arr, width, height, out))
+    return [out[i].copy() for i in range(n)]
 
 
 # ------------------------------------------------------------------------------------------------

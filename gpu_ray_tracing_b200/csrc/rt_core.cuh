@@ -335,4 +335,41 @@ RT_DEV bool primary_candidate(float h) {
 #endif
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tile level of the common-origin test.  The per-ray test  oc.u - q >= 0  says: the angle between u and oc is at
+// most alpha, cos(alpha) = q / |oc| (alpha = the angular radius of the inflated sphere seen from the camera).  If
+// every ray direction of a pixel tile is within the angle eps of a tile axis m (|m| = 1), a record can only be a
+// candidate of one of them when the angle between m and oc is at most alpha + eps:
+//     oc.m >= |oc| cos(alpha + eps) = q cos(eps) - R sin(eps),    R = |oc| sin(alpha) = sqrt(|oc|^2 - q^2).
+// ONE such test per (tile, record) discards the record for all the tile's rays.  eps enters through the chord
+// k = max |u - m| (cos(eps) = 1 - k^2/2, sin(eps) <= k for k < 1).  Floating point: the per-ray test is evaluated in
+// floats (primary_h), h_fl >= 0 implies oc.u - q >= -2^-21 |oc|; the dot product here carries the same error, u and
+// m are unit to 2^-22.  k is rounded up by 2^-10 relative + 2^-18 absolute, R^2 by 2^-18 |oc|^2, and 2^-18 |oc| is
+// added to the left side — each several times the error it covers — so the tile test keeps every record that any
+// per-ray test of the tile keeps: the set of exact tests, and with it the result, is unchanged.
+// ---------------------------------------------------------------------------------------------
+// Axis of a tile from the bounding box [lo, hi] of its rays' unit directions.
+RT_DEV f3 primary_tile_axis(f3 lo, f3 hi) {
+    const f3 m = mk(0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z));
+    const float inv = 1.0f / sqrtf(dot(m, m));
+    return mk(m.x * inv, m.y * inv, m.z * inv);
+}
+RT_DEV float primary_tile_e2(float ux, float uy, float uz, f3 m) {
+    const float dx = ux - m.x, dy = uy - m.y, dz = uz - m.z;
+    return fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+}
+// e2max: the largest primary_tile_e2 over the tile's traced rays.  Returns the chord bound k.
+RT_DEV float primary_tile_chord(float e2max) { return sqrtf(e2max) * 1.0009765625f + 3.814697265625e-06f; }
+// A NaN anywhere (degenerate axis) and k >= 1 (a tile wider than 60 degrees) keep the record.
+RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m, float k) {
+    if (!(k < 1.0f)) return true;
+    const float q = -rw;
+    const float t = fmaf(rx, m.x, fmaf(ry, m.y, rz * m.z));
+    const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+    const float R = sqrtf(fmaxf(fmaf(n2, 1.000003814697265625f, -((q * q) * 0.999996185302734375f)), 0.0f));
+    const float ce = fmaf(-0.5f * k, k, 1.0f);
+    const float lhs = fmaf(sqrtf(n2), 3.814697265625e-06f, fmaf(R, k, fmaf(-q, ce, t)));
+    return !(lhs < 0.0f);
+}
+
 }  // namespace rtc

@@ -44,6 +44,46 @@ struct Rng {
     float f32() { return (float)(next() >> 40) * (1.0f / 16777216.0f); }
 };
 
+
+// glam 0.29 Quat as the controller uses it (camera.rs:168-232): from_rotation_y / from_axis_angle build
+// (axis * sin(angle/2), cos(angle/2)); mul_vec3 is glam's scalar formula
+//   v * (w*w - b.b) + b * (2 * v.b) + (b x v) * (2 * w),  b = (x, y, z).
+// glam is a Cargo dependency whose source is not under /root/reference, so this follows its published definition;
+// the last bits of a pose may differ from a real build (sin/cos come from libm here).
+struct Quat {
+    float x, y, z, w;
+};
+inline Quat quat_axis_angle(Vec3 axis, float angle) {
+    const float s = std::sin(angle * 0.5f), c = std::cos(angle * 0.5f);
+    return Quat{axis.x * s, axis.y * s, axis.z * s, c};
+}
+inline Vec3 quat_mul_vec3(Quat q, Vec3 v) {
+    const Vec3 b{q.x, q.y, q.z};
+    const float b2 = dot(b, b);
+    return (v * (q.w * q.w - b2) + b * (dot(v, b) * 2.0f)) + cross(b, v) * (q.w * 2.0f);
+}
+inline float length(Vec3 a) { return std::sqrt(dot(a, a)); }
+
+// One yaw step of the arrow keys: look_from swings about look_at, distance kept (camera.rs:167-186).
+inline void yaw_about_target(CameraSettings* c, float angle) {
+    const Quat rot = quat_axis_angle(Vec3{0.0f, 1.0f, 0.0f}, angle);
+    const Vec3 view = V(c->look_from) - V(c->look_at);
+    const float len = length(view);
+    c->look_from = R(V(c->look_at) + normalize(quat_mul_vec3(rot, view)) * len);
+}
+
+// One pitch step of the 1 / 2 keys, refused within ~18 degrees of the poles (camera.rs:209-243).
+inline bool pitch_about_target(CameraSettings* c, float angle) {
+    const Vec3 view = V(c->look_from) - V(c->look_at);
+    const float len = length(view);
+    const Vec3 forward = normalize(view);
+    const Vec3 right = normalize(cross(forward, Vec3{0.0f, 1.0f, 0.0f}));
+    const Vec3 dir = normalize(quat_mul_vec3(quat_axis_angle(right, angle), forward));
+    if (!(std::fabs(dir.y) < 0.95f)) return false;
+    c->look_from = R(V(c->look_at) + dir * len);
+    return true;
+}
+
 inline GpuSphere sphere(Vec3 c, float r, float cx, float cy, float cz, float cw) {
     GpuSphere s;
     s.position = R(c);
@@ -204,6 +244,47 @@ int rt_orbit_camera(uint32_t k, uint32_t n, float radius, float height, float fo
     c.samples_per_pixel = 1;
     c.camera_has_moved = 1;
     return rt_camera_from_settings(&c, width, height_px, (float)k / (float)n, out);
+}
+
+// camera_movement_system (src/camera.rs:125-253) for one frame of `dt` seconds with the keys in `keys` held.
+// Kept as the reference has it, including: "forward" points from look_at to look_from, so W moves AWAY from the
+// target; the arrow-left/right block appears twice in the reference, so a held arrow key yaws by 2 * dt radians per
+// frame; camera_has_moved is set on any movement and cleared by the first idle frame.
+int rt_camera_step(CameraSettings* c, uint32_t keys, float dt) {
+    if (!c) return rti::fail(RT_ERR_INVALID_ARG, "settings is null");
+    const float move_speed = 2.0f, rotate_speed = 1.0f, vertical_speed = 1.0f;   // camera.rs:115-117
+    bool moved = false;
+    const Vec3 forward = normalize(V(c->look_from) - V(c->look_at));
+    const Vec3 right = normalize(cross(forward, Vec3{0.0f, 1.0f, 0.0f}));
+    const Vec3 up{0.0f, 1.0f, 0.0f};
+    if (keys & RT_KEY_W) { c->look_from = R(V(c->look_from) + forward * move_speed * dt); moved = true; }
+    if (keys & RT_KEY_S) { c->look_from = R(V(c->look_from) - forward * move_speed * dt); moved = true; }
+    if (keys & RT_KEY_A) { c->look_from = R(V(c->look_from) - right * move_speed * dt); moved = true; }
+    if (keys & RT_KEY_D) { c->look_from = R(V(c->look_from) + right * move_speed * dt); moved = true; }
+    if (keys & RT_KEY_ARROW_UP) { c->look_from = R(V(c->look_from) + up * vertical_speed * dt); moved = true; }
+    if (keys & RT_KEY_ARROW_DOWN) { c->look_from = R(V(c->look_from) - up * vertical_speed * dt); moved = true; }
+    for (int pass = 0; pass < 2; ++pass) {   // camera.rs:166-186 and its verbatim repeat at :187-207
+        if (keys & RT_KEY_ARROW_LEFT) { yaw_about_target(c, rotate_speed * dt); moved = true; }
+        if (keys & RT_KEY_ARROW_RIGHT) { yaw_about_target(c, -rotate_speed * dt); moved = true; }
+    }
+    if (keys & RT_KEY_DIGIT1) moved |= pitch_about_target(c, rotate_speed * dt);
+    if (keys & RT_KEY_DIGIT2) moved |= pitch_about_target(c, -rotate_speed * dt);
+    c->camera_has_moved = moved ? 1u : 0u;   // camera.rs:245-252
+    return RT_OK;
+}
+
+// A scripted fly-through: frame f applies rt_camera_step(keys[f], dt) and derives the 176-byte uniform the render
+// world would extract that frame (lib.rs:117; random_seed = seeds[f], or f / n_frames when seeds is null).
+int rt_camera_script(CameraSettings* c, const uint32_t* keys, uint32_t n_frames, float dt, const float* seeds,
+                     uint32_t width, uint32_t height_px, SceneCamera* out) {
+    if (!c || (n_frames && (!keys || !out))) return rti::fail(RT_ERR_INVALID_ARG, "null argument");
+    for (uint32_t f = 0; f < n_frames; ++f) {
+        int rc = rt_camera_step(c, keys[f], dt);
+        if (rc != RT_OK) return rc;
+        rc = rt_camera_from_settings(c, width, height_px, seeds ? seeds[f] : (float)f / (float)n_frames, out + f);
+        if (rc != RT_OK) return rc;
+    }
+    return RT_OK;
 }
 
 }  // extern "C"

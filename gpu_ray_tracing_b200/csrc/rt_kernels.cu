@@ -409,45 +409,22 @@ struct PrimLanes {
 
 __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
 
-// Exact tests of records [slot, slot + count) for the rays whose sign test passes, in index order.
-// The sign test is re-evaluated per record with the same packed operations as the broad phase.
-__device__ __forceinline__ void prim_narrow(const float4* __restrict__ s_rec, const float* __restrict__ s_d, int slot,
-                                            int count, int index0, const UpdateParams& P, PrimLanes& L,
-                                            uint32_t& exact_tests) {
-#pragma unroll 1
-    for (int u = 0; u < count; ++u) {
-        const int idx = index0 + slot + u;
-        if ((uint32_t)idx >= P.n_spheres) break;   // padding
-        const float4 rec = s_rec[slot + u];
-        const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
-                     sw = make_float2(rec.w, rec.w);
-        float2 h[kPrimRays / 2];
-        int acc = -1;
+// Exact tests (the reference quadratic, shrinking t_max) of sphere `idx` for the rays in `cand`.
+__device__ __forceinline__ void prim_exact(uint32_t cand, int idx, const float* __restrict__ s_d, const UpdateParams& P,
+                                           PrimLanes& L, uint32_t& exact_tests) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
+    const f3 center = rtc::mk(g.x, g.y, g.z);
 #pragma unroll
-        for (int q = 0; q < kPrimRays / 2; ++q) {
-            h[q] = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
-            acc &= __float_as_int(h[q].x) & __float_as_int(h[q].y);
-        }
-        if (acc < 0) continue;
-        uint32_t cand = 0;
-#pragma unroll
-        for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
-        cand &= L.alive;
-        if (!cand) continue;
-        const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
-        const f3 center = rtc::mk(g.x, g.y, g.z);
-#pragma unroll
-        for (int p = 0; p < kPrimRays; ++p) {
-            if (cand & (1u << p)) {
-                ++exact_tests;
-                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-                const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
-                const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
-                float root;
-                if (rtc::sphere_root(origin, d, rtc::dot(d, d), center, g.w, kTMin, L.best_t[p], &root)) {
-                    L.best_t[p] = root;
-                    L.best_i[p] = idx;
-                }
+    for (int p = 0; p < kPrimRays; ++p) {
+        if (cand & (1u << p)) {
+            ++exact_tests;
+            const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+            const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+            const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
+            float root;
+            if (rtc::sphere_root(origin, d, rtc::dot(d, d), center, g.w, kTMin, L.best_t[p], &root)) {
+                L.best_t[p] = root;
+                L.best_i[p] = idx;
             }
         }
     }
@@ -496,36 +473,93 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
     }
 }
 
-// Broad phase over `count` (multiple of kPrimUnroll) records at s_rec (global sphere index of slot 0 = index0),
-// kPrimUnroll per iteration, the next group prefetched; kPrimUnroll slots after the end must be readable.
-__device__ __forceinline__ void prim_scan(const float4* __restrict__ s_rec, int count, int index0,
-                                          const float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
-                                          uint32_t& exact_tests) {
-    uint32_t addr = (uint32_t)__cvta_generic_to_shared(s_rec);
-    float4 cur[kPrimUnroll];
+// Axis and chord bound of the warp's tile (rt_core.cuh, "Tile level"): bounding box of the traced rays' unit
+// directions, reduced over the warp with min / max (exact, so the CPU emulation reproduces it bit for bit).
+__device__ __forceinline__ void prim_tile_bound(const PrimLanes& L, f3& m, float& chord) {
+    const float inf = __int_as_float(0x7f800000);
+    f3 lo = rtc::mk(inf, inf, inf), hi = rtc::mk(-inf, -inf, -inf);
 #pragma unroll
-    for (int u = 0; u < kPrimUnroll; ++u) cur[u] = lds128(addr + 16u * u);
+    for (int p = 0; p < kPrimRays; ++p) {
+        if (L.alive & (1u << p)) {
+            const float ux = ray_half(L.ux[p >> 1], p), uy = ray_half(L.uy[p >> 1], p), uz = ray_half(L.uz[p >> 1], p);
+            lo = rtc::mk(fminf(lo.x, ux), fminf(lo.y, uy), fminf(lo.z, uz));
+            hi = rtc::mk(fmaxf(hi.x, ux), fmaxf(hi.y, uy), fmaxf(hi.z, uz));
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = rtc::mk(fminf(lo.x, __shfl_xor_sync(kFull, lo.x, o)), fminf(lo.y, __shfl_xor_sync(kFull, lo.y, o)),
+                     fminf(lo.z, __shfl_xor_sync(kFull, lo.z, o)));
+        hi = rtc::mk(fmaxf(hi.x, __shfl_xor_sync(kFull, hi.x, o)), fmaxf(hi.y, __shfl_xor_sync(kFull, hi.y, o)),
+                     fmaxf(hi.z, __shfl_xor_sync(kFull, hi.z, o)));
+    }
+    m = rtc::primary_tile_axis(lo, hi);
+    float e2 = 0.0f;
+#pragma unroll
+    for (int p = 0; p < kPrimRays; ++p) {
+        if (L.alive & (1u << p))
+            e2 = fmaxf(e2, rtc::primary_tile_e2(ray_half(L.ux[p >> 1], p), ray_half(L.uy[p >> 1], p), ray_half(L.uz[p >> 1], p), m));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e2 = fmaxf(e2, __shfl_xor_sync(kFull, e2, o));
+    chord = rtc::primary_tile_chord(e2);
+}
+
+// Two-level broad phase over `count` records at s_rec (global sphere index of slot 0 = index0).
+//   cull: the warp's lanes test 32 records at a time against the TILE (primary_tile_candidate) and compact the
+//         survivors' slots, in ascending order, into the warp's list (kPrimListCap records per pass);
+//   scan: every lane runs the per-ray sign test (3 FFMA per ray, as FFMA2 pairs) on the listed records only, the
+//         next one prefetched, and puts its candidates through the exact test.
+// A 32 x 8 pixel tile of a 4K frame keeps about 6 of 1024 records, so the scan that used to be the whole cost of the
+// pass is now a small part of it; index order, and with it the reference's tie and NaN behaviour, is preserved.
+__device__ __forceinline__ void prim_cull_scan(const float4* __restrict__ s_rec, int count, int index0,
+                                               unsigned short* __restrict__ s_list, f3 m, float chord,
+                                               const float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
+                                               uint32_t& exact_tests, int lane) {
 #pragma unroll 1
-    for (int s = 0; s < count; s += kPrimUnroll) {
-        addr += 16u * kPrimUnroll;
-        float4 nxt[kPrimUnroll];
-#pragma unroll
-        for (int u = 0; u < kPrimUnroll; ++u) nxt[u] = lds128(addr + 16u * u);
-        int acc = -1;   // AND of every (ray, record) sign bit of the group
-#pragma unroll
-        for (int u = 0; u < kPrimUnroll; ++u) {
-            const float4 sp = cur[u];
-            const float2 sx = make_float2(sp.x, sp.x), sy = make_float2(sp.y, sp.y), sz = make_float2(sp.z, sp.z),
-                         sw = make_float2(sp.w, sp.w);
+    for (int base = 0; base < count; base += kPrimListCap) {
+        const int n = min(kPrimListCap, count - base);
+        int n_list = 0;
+#pragma unroll 1
+        for (int j0 = 0; j0 < n; j0 += 32) {
+            const int j = j0 + lane;
+            bool keep = false;
+            if (j < n) {
+                const float4 r = s_rec[base + j];
+                keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord);
+            }
+            const unsigned b = __ballot_sync(kFull, keep);
+            if (keep) s_list[n_list + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(base + j);
+            n_list += __popc(b);
+        }
+        if (lane == 0) s_list[n_list] = (unsigned short)base;   // the prefetch of the last iteration reads one entry further
+        __syncwarp();
+        int j = s_list[0];
+        float4 rec = s_rec[j];
+#pragma unroll 1
+        for (int e = 0; e < n_list; ++e) {
+            const int jn = s_list[e + 1];
+            const float4 recn = s_rec[jn];
+            const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
+                         sw = make_float2(rec.w, rec.w);
+            float2 h[kPrimRays / 2];
+            int acc = -1;   // AND of the rays' sign bits
 #pragma unroll
             for (int q = 0; q < kPrimRays / 2; ++q) {
-                const float2 h = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
-                acc &= __float_as_int(h.x) & __float_as_int(h.y);
+                h[q] = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
+                acc &= __float_as_int(h[q].x) & __float_as_int(h[q].y);
             }
-        }
-        if (acc >= 0) prim_narrow(s_rec, s_d, s, kPrimUnroll, index0, P, L, exact_tests);
+            if (acc >= 0) {
+                uint32_t cand = 0;
 #pragma unroll
-        for (int u = 0; u < kPrimUnroll; ++u) cur[u] = nxt[u];
+                for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
+                cand &= L.alive;
+                if (cand) prim_exact(cand, index0 + j, s_d, P, L, exact_tests);
+            }
+            j = jn;
+            rec = recn;
+        }
+        __syncwarp();   // the list is rewritten by the next pass
     }
 }
 
@@ -659,6 +693,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
     __shared__ uint32_t s_block_tile;
     float4* s_stage = s_dyn;                                                          // [2][kStage]
     float* s_d = reinterpret_cast<float*>(s_dyn + 2 * kStage) + threadIdx.x;          // ray slots, this thread's column
+    unsigned short* s_list = reinterpret_cast<unsigned short*>(s_dyn + 2 * kStage + kPrimRays * kPrimSlots * kBlockThreads / 4) +
+                             (threadIdx.x >> 5) * (kPrimListCap + 8);                 // this warp's candidate list
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
     const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(s_stage);
@@ -688,33 +724,63 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
         bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.prim + base, bytes, bar);
     };
 
-    for (;;) {
-        __syncthreads();   // the previous tile is finished with s_block_tile and both stages
-        if (threadIdx.x == 0) s_block_tile = atomicAdd(P.tile_counter + 1, 1u);
-        __syncthreads();
-        const uint32_t bt = s_block_tile;
-        if (bt >= n_block_tiles) break;
-        if (threadIdx.x == 0) {
-            request(0);
-            if (n_chunks > 1) request(1);
+    if (n_chunks == 1) {
+        // The scene fits one stage: copied once per CTA, then every WARP pulls tiles on its own — no block barrier
+        // and no copy in the loop, so a warp on a crowded tile delays nobody.
+        if (threadIdx.x == 0) request(0);
+        mbar_wait(bar0, 0u);
+        for (;;) {
+            uint32_t tile = 0;
+            if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
+            tile = __shfl_sync(kFull, tile, 0);
+            if (tile >= n_tiles) break;
+            const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
+            const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+            PrimLanes L;
+            uint32_t untraced;
+            prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
+            if (__any_sync(kFull, L.alive != 0u)) {
+                f3 m;
+                float chord;
+                prim_tile_bound(L, m, chord);
+                prim_cull_scan(s_stage, n_pad, 0, s_list, m, chord, s_d, P, L, exact_tests, lane);
+            }
+            prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
         }
-        const uint32_t tile = bt * 8u + (uint32_t)warp;   // tiles past the end have every ray out of bounds
-        const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
-        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
-        PrimLanes L;
-        uint32_t untraced;
-        prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
-        const bool warp_live = __any_sync(kFull, L.alive != 0u);
+    } else {
+        for (;;) {
+            __syncthreads();   // the previous tile is finished with s_block_tile and both stages
+            if (threadIdx.x == 0) s_block_tile = atomicAdd(P.tile_counter + 1, 1u);
+            __syncthreads();
+            const uint32_t bt = s_block_tile;
+            if (bt >= n_block_tiles) break;
+            if (threadIdx.x == 0) {
+                request(0);
+                request(1);
+            }
+            const uint32_t tile = bt * 8u + (uint32_t)warp;   // tiles past the end have every ray out of bounds
+            const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
+            const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+            PrimLanes L;
+            uint32_t untraced;
+            prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
+            const bool warp_live = __any_sync(kFull, L.alive != 0u);
+            f3 m = rtc::mk(0.0f, 0.0f, 0.0f);
+            float chord = 0.0f;
+            if (warp_live) prim_tile_bound(L, m, chord);
 
-        for (int c = 0; c < n_chunks; ++c) {
-            const int st = c & 1, base = c * kPrimChunk;
-            mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
-            parity ^= 1u << st;
-            if (warp_live) prim_scan(s_stage + st * kStage, min(kPrimChunk, n_pad - base), base, s_d, P, L, exact_tests);
-            __syncthreads();   // every warp has left stage st
-            if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
+            for (int c = 0; c < n_chunks; ++c) {
+                const int st = c & 1, base = c * kPrimChunk;
+                mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
+                parity ^= 1u << st;
+                if (warp_live)
+                    prim_cull_scan(s_stage + st * kStage, min(kPrimChunk, n_pad - base), base, s_list, m, chord, s_d, P, L,
+                                   exact_tests, lane);
+                __syncthreads();   // every warp has left stage st
+                if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
+            }
+            prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
         }
-        prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
     }
     prim_flush(P, exact_tests, rays, lane);
 }
@@ -1363,7 +1429,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // Launchers
 // ---------------------------------------------------------------------------------------------
 static size_t prim_smem_bytes() {
-    return (size_t)2 * (kPrimChunk + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float);
+    return (size_t)2 * (kPrimChunk + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float) +
+           (size_t)(kBlockThreads / 32) * (kPrimListCap + 8) * sizeof(unsigned short);
 }
 
 static size_t bounce_smem_bytes() {

@@ -20,6 +20,7 @@ constexpr int kPrimTileW = 32;
 constexpr int kPrimTileH = 8;
 constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
+constexpr int kPrimListCap = 512;   // records per cull pass of a warp: capacity of its candidate list (2-byte slots)
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts

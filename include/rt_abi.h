@@ -252,6 +252,24 @@ RT_API int rt_create_grid_spheres(uint64_t seed, uint32_t n, GpuSphere* out);
 RT_API int rt_orbit_camera(uint32_t k, uint32_t n, float radius, float height, float fov_deg,
                            uint32_t width, uint32_t height_px, SceneCamera* out);
 
+/* Keys of camera_movement_system (src/camera.rs:125-253), as a bit mask of the keys held during a frame. */
+#define RT_KEY_W           0x001u  /* look_from += forward * 2 dt (forward = from look_at TO look_from) */
+#define RT_KEY_S           0x002u
+#define RT_KEY_A           0x004u  /* strafe along forward x Y */
+#define RT_KEY_D           0x008u
+#define RT_KEY_ARROW_UP    0x010u  /* look_from.y +/- dt */
+#define RT_KEY_ARROW_DOWN  0x020u
+#define RT_KEY_ARROW_LEFT  0x040u  /* yaw look_from about look_at; applied twice per frame, as in the reference */
+#define RT_KEY_ARROW_RIGHT 0x080u
+#define RT_KEY_DIGIT1      0x100u  /* pitch about look_at, refused when |dir.y| >= 0.95 */
+#define RT_KEY_DIGIT2      0x200u
+/* One frame of the keyboard controller: updates look_from and camera_has_moved in place. */
+RT_API int rt_camera_step(CameraSettings* settings, uint32_t keys, float dt);
+/* n_frames controller frames, each followed by the uniform derivation: out[f] is what `update` would see at frame f.
+ * seeds may be null (random_seed = f / n_frames). */
+RT_API int rt_camera_script(CameraSettings* settings, const uint32_t* keys, uint32_t n_frames, float dt,
+                            const float* seeds, uint32_t width, uint32_t height_px, SceneCamera* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,7 @@ using rtc::f3;
 extern "C" __attribute__((visibility("default")))
 void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t count, uint32_t width, uint32_t height,
                 uint32_t row_begin, uint32_t row_count, float* accum,
-                uint64_t* stats /* rays, exact, violations, primary rays, untraced */, int variant) {
+                uint64_t* stats /* rays, exact, violations, primary rays, untraced, (tile, record) pairs kept, ray candidates a tile dropped */, int variant) {
     (void)height;
     const SceneCamera& cam = *cam_p;
     std::vector<float> gk(count);
@@ -30,14 +30,57 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     std::vector<float> prim(primary ? (size_t)count * 4 : 0);
     if (primary)
         for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);
-    uint64_t prim_rays = 0, untraced = 0;
+    uint64_t prim_rays = 0, untraced = 0, tile_pairs = 0, tile_dropped = 0;
+    const uint32_t seed_bits_early = rtc::f2u(cam.random_seed * 4294967296.0f);
+    // tile level of the primary pass (rtk::prim_tile_bound / prim_cull): per 32 x 8 pixel tile of the window, the
+    // records that survive the tile test.  tile_cand[tile * count + s] != 0 <=> record s is scanned for that tile.
+    const uint32_t tiles_x = (width + 31u) / 32u, tiles_y = (row_count + 7u) / 8u;
+    std::vector<uint8_t> tile_cand(primary ? (size_t)tiles_x * tiles_y * count : 0);
+    if (primary) {
+        const uint32_t spp_e = rtc::f2u(cam.samples_per_pixel);
+        const bool reset_e = cam.camera_has_moved > 0.5f;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : tile_pairs)
+#endif
+        for (int64_t tile = 0; tile < (int64_t)tiles_x * tiles_y; ++tile) {
+            const uint32_t x0 = (uint32_t)(tile % tiles_x) * 32u, r0 = (uint32_t)(tile / tiles_x) * 8u;
+            float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+            std::vector<float> us;
+            for (uint32_t row = r0; row < r0 + 8u && row < row_count; ++row)
+                for (uint32_t x = x0; x < x0 + 32u && x < width; ++x) {
+                    const float* texel = accum + ((size_t)row * width + x) * 4;
+                    const uint32_t n = reset_e ? 0u : rtc::f2u(texel[3]);
+                    if (!(n < spp_e)) continue;
+                    const uint32_t seed = 1u + n + seed_bits_early;
+                    const rtc::Ray r = rtc::get_ray(cam, (int)x, (int)(row_begin + row), seed, seed_bits_early);
+                    float u[3];
+                    if (!rtc::primary_arm(r.d, rtc::dot(r.d, r.d), &u[0], &u[1], &u[2])) continue;
+                    for (int k = 0; k < 3; ++k) {
+                        lo[k] = fminf(lo[k], u[k]);
+                        hi[k] = fmaxf(hi[k], u[k]);
+                        us.push_back(u[k]);
+                    }
+                }
+            if (us.empty()) continue;
+            const f3 m = rtc::primary_tile_axis(rtc::mk(lo[0], lo[1], lo[2]), rtc::mk(hi[0], hi[1], hi[2]));
+            float e2 = 0.0f;
+            for (size_t k = 0; k < us.size(); k += 3) e2 = fmaxf(e2, rtc::primary_tile_e2(us[k], us[k + 1], us[k + 2], m));
+            const float chord = rtc::primary_tile_chord(e2);
+            for (uint32_t sidx = 0; sidx < count; ++sidx) {
+                const float* rec = &prim[(size_t)sidx * 4];
+                const bool c = rtc::primary_tile_candidate(rec[0], rec[1], rec[2], rec[3], m, chord);
+                tile_cand[(size_t)tile * count + sidx] = c ? 1 : 0;
+                tile_pairs += c ? 1 : 0;
+            }
+        }
+    }
     const uint32_t seed_bits = rtc::f2u(cam.random_seed * 4294967296.0f);
     const uint32_t spp = rtc::f2u(cam.samples_per_pixel);
     const uint32_t max_depth = rtc::f2u(cam.max_depth);
     const bool reset = cam.camera_has_moved > 0.5f;
     uint64_t rays = 0, exact = 0, violations = 0;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced, tile_dropped)
 #endif
     for (int64_t row = 0; row < (int64_t)row_count; ++row) {
         const int y_abs = (int)(row_begin + row);
@@ -61,11 +104,14 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                     const bool use_primary = primary && i == 0;
                     if (use_primary && rtc::primary_arm(r.d, a, &pux, &puy, &puz)) {
                         ++prim_rays;
+                        const uint8_t* tc = &tile_cand[((size_t)(row / 8) * tiles_x + x / 32u) * count];
                         for (uint32_t s = 0; s < count; ++s) {
                             const GpuSphere& sp = spheres[s];
                             const float* rec = &prim[(size_t)s * 4];
                             float root;
-                            if (rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz))) {
+                            const bool ray_cand = rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz));
+                            if (ray_cand && !tc[s]) ++tile_dropped;   // expected 0: the tile test keeps what any ray test keeps
+                            if (ray_cand && tc[s]) {
                                 ++exact;
                                 if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, best_t, &root)) {
                                     best_t = root;
@@ -106,7 +152,10 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
             texel[0] = mean.x; texel[1] = mean.y; texel[2] = mean.z; texel[3] = (float)n;
         }
     }
-    if (stats) { stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced; }
+    if (stats) {
+        stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced;
+        stats[5] = tile_pairs; stats[6] = tile_dropped;
+    }
 }
 
 // Direct access to the primary-pass record functions for invariant tests.

@@ -158,3 +158,103 @@ def test_write_ppm_roundtrip(tmp_path):
     data = path.read_bytes()
     assert data.startswith(b"P6\n7 5\n255\n")
     assert data[len(b"P6\n7 5\n255\n"):] == img[..., :3].tobytes()
+
+
+# ------------------------------------------------------------------------------------------------
+# keyboard controller restatement (camera.rs:125-253), SURVEY.md section 8(f) row 3
+# ------------------------------------------------------------------------------------------------
+def _v(v):
+    return np.array(v.tuple(), dtype=np.float64)
+
+
+def test_camera_step_translations_follow_reference_axes():
+    K = rt.Key
+    dt = 0.25
+    base = rt.CameraSettings.default()
+    f0, a0 = _v(base.look_from), _v(base.look_at)
+    forward = (f0 - a0) / np.linalg.norm(f0 - a0)          # from the target TO the camera (camera.rs:135-136)
+    right = np.cross(forward, [0.0, 1.0, 0.0])
+    right /= np.linalg.norm(right)
+    cases = {K.W: forward * 2.0 * dt, K.S: -forward * 2.0 * dt, K.A: -right * 2.0 * dt, K.D: right * 2.0 * dt,
+             K.ARROW_UP: np.array([0.0, dt, 0.0]), K.ARROW_DOWN: np.array([0.0, -dt, 0.0])}
+    for key, delta in cases.items():
+        s = rt.CameraSettings.default()
+        s.camera_has_moved = 0
+        rt.camera_movement_system(s, key, dt)
+        np.testing.assert_allclose(_v(s.look_from), f0 + delta, rtol=0, atol=2e-6)
+        np.testing.assert_array_equal(_v(s.look_at), a0)     # keys never move the target
+        assert s.camera_has_moved == 1
+    s = rt.CameraSettings.default()
+    rt.camera_movement_system(s, K.W | K.S | K.A | K.D, dt)  # opposite keys cancel (up to rounding) but count as movement
+    np.testing.assert_allclose(_v(s.look_from), f0, rtol=0, atol=4e-6)
+    assert s.camera_has_moved == 1
+
+
+def test_camera_step_flag_clears_on_first_idle_frame():
+    s = rt.CameraSettings.default()
+    assert s.camera_has_moved == 1                          # default starts with the reset flag on (camera.rs:35)
+    before = _v(s.look_from)
+    rt.camera_movement_system(s, 0, 0.016)
+    assert s.camera_has_moved == 0
+    np.testing.assert_array_equal(_v(s.look_from), before)
+    rt.camera_movement_system(s, rt.Key.ARROW_LEFT, 0.016)
+    assert s.camera_has_moved == 1
+    rt.camera_movement_system(s, 0, 0.016)
+    assert s.camera_has_moved == 0
+
+
+def test_camera_step_yaw_is_applied_twice_per_frame_and_keeps_distance():
+    # the arrow block is duplicated in the reference (camera.rs:166-186 and :187-207): one frame yaws by 2 * dt
+    s = rt.CameraSettings.default()
+    f0, a0 = _v(s.look_from), _v(s.look_at)
+    dt = 0.1
+    rt.camera_movement_system(s, rt.Key.ARROW_LEFT, dt)
+    ang = 2.0 * dt
+    c, sn = np.cos(ang), np.sin(ang)
+    v = f0 - a0
+    want = a0 + np.array([c * v[0] + sn * v[2], v[1], -sn * v[0] + c * v[2]])   # rotation about +Y by +ang
+    np.testing.assert_allclose(_v(s.look_from), want, rtol=0, atol=5e-6)
+    rt.camera_movement_system(s, rt.Key.ARROW_RIGHT, dt)
+    np.testing.assert_allclose(_v(s.look_from), f0, rtol=0, atol=1e-5)
+    # a full orbit: 2 pi / (2 dt) frames come back to the start, radius and height kept all the way
+    n = 200
+    dt = float(np.float32(2.0 * np.pi / (2.0 * n)))
+    r0 = np.linalg.norm(f0 - a0)
+    for _ in range(n):
+        rt.camera_movement_system(s, rt.Key.ARROW_LEFT, dt)
+        assert abs(np.linalg.norm(_v(s.look_from) - a0) - r0) < 2e-4
+        assert abs(s.look_from.y - f0[1]) < 2e-5
+    np.testing.assert_allclose(_v(s.look_from), f0, rtol=0, atol=2e-3)
+
+
+def test_camera_step_pitch_stops_before_the_pole():
+    s = rt.CameraSettings.default()
+    a0 = _v(s.look_at)
+    r0 = np.linalg.norm(_v(s.look_from) - a0)
+    y_prev = s.look_from.y
+    rose = 0
+    for _ in range(400):                                    # far more than needed to reach the pole
+        rt.camera_movement_system(s, rt.Key.DIGIT1, 0.02)
+        d = (_v(s.look_from) - a0) / np.linalg.norm(_v(s.look_from) - a0)
+        assert abs(d[1]) < 0.95                             # camera.rs:221, 238
+        assert abs(np.linalg.norm(_v(s.look_from) - a0) - r0) < 5e-4
+        rose += s.look_from.y != y_prev
+        y_prev = s.look_from.y
+    assert 10 < rose < 400                                  # it moved for a while, then every frame was refused
+    assert s.camera_has_moved == 0                          # a refused pitch is not movement
+    d = (_v(s.look_from) - a0) / r0
+    assert abs(d[1]) > 0.9
+
+
+def test_camera_script_matches_stepping_by_hand():
+    W, H, n, dt = 64, 48, 12, 1.0 / 60.0
+    keys = [rt.Key.ARROW_LEFT if f % 3 else rt.Key.W | rt.Key.ARROW_UP for f in range(n)]
+    keys[5] = 0
+    seeds = [f / 16.0 for f in range(n)]
+    cams = rt.camera_script(rt.CameraSettings.default(), keys, dt, W, H, seeds=seeds)
+    s = rt.CameraSettings.default()
+    for f in range(n):
+        rt.camera_movement_system(s, keys[f], dt)
+        want = rt.SceneCamera.from_settings(s, W, H, random_seed=seeds[f])
+        assert cams[f].to_bytes() == want.to_bytes()
+        assert cams[f].camera_has_moved == (0.0 if f == 5 else 1.0)

@@ -26,6 +26,7 @@ def test_emulated_kernel_matches_oracle(name, make, W, H, kw, variant):
     emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
     if variant == 0:
         assert ol.EMU_STATS["primary_rays"] == W * H and ol.EMU_STATS["untraced"] == 0
+        assert ol.EMU_STATS["tile_dropped"] == 0       # the tile level never removes a record a ray test keeps
     rep = ol.compare_images(cpu, emu)
     print(name, rep, "exact tests per ray: %.2f of %d spheres" % (exact / max(rays, 1), scene.count))
     assert violations == 0
@@ -97,8 +98,29 @@ def test_randomised_scenes_and_cameras_audit():
         for variant in (0, 2):
             emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
             assert violations == 0, (case, variant, violations)
+            if variant == 0:
+                assert ol.EMU_STATS["tile_dropped"] == 0, (case, ol.EMU_STATS)
             assert rays_e == rays
             assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32)), (case, variant)
+
+
+def test_tile_level_culls_and_changes_nothing():
+    """The per-tile test of the primary pass (32 x 8 pixel tiles): it keeps a small part of the (tile, record) pairs
+    at a resolution where tiles are narrow, never drops a record one of the tile's rays would test, and the exact-test
+    count is the per-ray broad phase's own."""
+    W, H = 640, 360
+    scene = scenes.random_scene(1024)
+    for defocus in (None, 0.0):
+        cam = scenes.camera(W, H, max_depth=1, spp=1, defocus_angle=defocus)
+        cpu, rays = ol.oracle_update(cam, scene, W, H)
+        emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=0)
+        st = dict(ol.EMU_STATS)
+        n_tiles = ((W + 31) // 32) * ((H + 7) // 8)
+        kept = st["tile_pairs"] / (n_tiles * scene.count)
+        print("defocus", defocus, "tile level keeps %.2f %% of the pairs, %.1f records per tile" % (100 * kept, kept * scene.count), st)
+        assert violations == 0 and st["tile_dropped"] == 0 and rays_e == rays == W * H
+        assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))
+        assert kept < 0.10
 
 
 def test_primary_records_are_conservative_by_construction():

@@ -241,3 +241,27 @@ def test_wavefront_counts_and_depth_fallback():
         gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
         assert rays_gpu == rays_cpu
         assert_parity(gpu, cpu, f"depth {depth}")
+
+
+def test_scripted_flythrough_frames():
+    """the keyboard controller scripted (yaw, dolly, an idle frame that accumulates instead of
+    resetting); every frame's accumulator equals the oracle's fed the same 176-byte uniforms."""
+    W, H, dt = 320, 200, 1.0 / 30.0
+    K = rt.Key
+    keys = [K.ARROW_LEFT, K.ARROW_LEFT | K.W, 0, 0, K.DIGIT1, K.S | K.D, 0]
+    settings = rt.CameraSettings.default()
+    settings.max_depth = 6
+    cams = rt.camera_script(settings, keys, dt, W, H, seeds=[0.0625 * (f + 1) for f in range(len(keys))])
+    assert [c.camera_has_moved for c in cams] == [1.0, 1.0, 0.0, 0.0, 1.0, 1.0, 0.0]
+    scene = scenes.default_scene()
+    cpu = None
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        for f, cam in enumerate(cams):
+            cpu, _ = ol.oracle_update(cam, scene, W, H, accum=cpu)
+            r.update(cam)
+            gpu = r.read_accum()
+            assert_parity(gpu, cpu, f"fly-through frame {f}")
+            assert gpu[..., 3].max() == (1.0 if cam.camera_has_moved else gpu[..., 3].max())
+        assert cpu[..., 3].max() == 2.0     # frames 5, 6: one moved frame then one idle frame
