@@ -15,6 +15,7 @@
 #include "../../include/rt_abi.h"
 #include "rt_kernels.cuh"
 #include "rt_internal.h"
+#include "rt_cluster.h"
 
 namespace rti {
 
@@ -140,6 +141,7 @@ int rt_destroy(RtRenderer* r) {
     cudaFree(r->wf_queue[0]);
     cudaFree(r->wf_queue[1]);
     cudaFree(r->wf_counts);
+    cudaFree(r->cl_blob);
     cudaFree(r->tile_counter);
     cudaFree(r->counters);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
@@ -171,6 +173,9 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
     if (buffer_len > 0)
         RT_CUDA(cudaMemcpyAsync(r->spheres, spheres, (size_t)buffer_len * sizeof(GpuSphere), cudaMemcpyHostToDevice, r->stream));
     r->n_spheres = count;
+    r->host_spheres.assign(spheres, spheres + count);   // for the lazily built clusters of the bounce rays
+    r->clusters_stale = true;
+    r->cl_n_top = 0;
     RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
     r->launches += 1;
     // the source is borrowed for the call only (pageable memory: the copy above has been staged,
@@ -206,6 +211,31 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
         RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
     }
+    if (camera->max_depth > 1.0f && r->clusters_stale && r->wf_counts) {
+        // first deep frame of this scene: cluster the spheres for the bounce rays (skipped when the image would not
+        // fit the bounce kernel's shared-memory stages; that kernel then streams the plain records instead)
+        r->clusters_stale = false;
+        rtcl::Clusters cl;
+        if (rtcl::build(r->host_spheres.data(), r->n_spheres, cl) && cl.bytes() <= rtk::kClusterImageMax) {
+            if (cl.bytes() > r->cl_capacity) {
+                RT_CUDA(cudaStreamSynchronize(r->stream));
+                cudaFree(r->cl_blob); r->cl_blob = nullptr; r->cl_capacity = 0;
+                RT_CUDA(cudaMalloc(&r->cl_blob, cl.bytes()));
+                r->cl_capacity = cl.bytes();
+            }
+            std::vector<unsigned char> image(cl.bytes());
+            cl.pack(image.data());
+            RT_CUDA(cudaMemcpyAsync(r->cl_blob, image.data(), image.size(), cudaMemcpyHostToDevice, r->stream));
+            RT_CUDA(cudaStreamSynchronize(r->stream));   // `image` is about to go away
+            r->cl_n_top = cl.n_top;
+            r->cl_bytes = (uint32_t)cl.bytes();
+            r->cl_extra_r = cl.extra_r;
+        }
+    }
+    p.cl_blob = r->cl_blob;
+    p.cl_n_top = r->cl_n_top;
+    p.cl_bytes = r->cl_bytes;
+    p.cl_extra_r = r->cl_extra_r;
     p.wf_queue[0] = r->wf_queue[0];
     p.wf_queue[1] = r->wf_queue[1];
     p.wf_counts = r->wf_counts;

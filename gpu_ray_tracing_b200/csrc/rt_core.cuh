@@ -372,4 +372,35 @@ RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m,
     return !(lhs < 0.0f);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Cluster level of the general broad phase (rt_cluster.h).  A cluster's bounding sphere has an ordinary record
+// (Cc, k(Rc')); the ray's own share of the bound, m = 2^-7 |O|, enters through the threshold:
+// (Rc' + m)^2 <= Rc'^2 + 2 Rmax m + m^2, so the cluster is descended into when g >= thr - (2 Rmax m + m^2).
+// oo = dot(O, O); extra_r = Rmax, the largest cluster radius of the scene.
+// ---------------------------------------------------------------------------------------------
+#ifndef RT_CLUSTER_SLOTS
+#define RT_CLUSTER_SLOTS 8 /* member slots per cluster: rtcl::kSlots (host build) = rtk::kClusterSlots (kernels) */
+#endif
+
+RT_DEV float cluster_thr(float thr, float oo, float extra_r) {
+    const float m = sqrtf(oo) * 0.00782012939453125f;   // 2^-7 (1 + 2^-10)
+    const float extra = fmaf(m, m, (2.0f * extra_r) * m) * 1.0009765625f;
+    return thr - extra;
+}
+
+// Nearest-hit update that does not depend on the order of the tests: the reference's sequential loop returns the
+// lexicographic minimum of (first valid root, index) when no root is NaN.  Returns
+// false when the root is NaN: the caller must then retrace the ray with the sequential loop.
+RT_DEV bool nearest_update(f3 o, f3 d, float a, f3 center, float radius, float tmin, float tmax0, int idx, float* best_t,
+                           int* best_i) {
+    float root;
+    if (!sphere_root(o, d, a, center, radius, tmin, tmax0, &root)) return true;
+    if (root != root) return false;
+    if (root < *best_t || (root == *best_t && idx < *best_i)) {
+        *best_t = root;
+        *best_i = idx;
+    }
+    return true;
+}
+
 }  // namespace rtc

@@ -28,6 +28,7 @@ constexpr float kTMin = 0.001f;    // compute_shader.wgsl:266
 constexpr float kTMax = 3.4e35f;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kUnroll = 4;         // spheres per broad-phase iteration
+static_assert(2 * kClusterSlots <= 32, "cluster_members keeps one candidate bit per (member, ray)");
 constexpr int kGeomPad = 8;        // geometry arrays are padded to a multiple of this ...
 constexpr int kGeomTail = 8;       // ... plus a tail the software prefetch may read (never computed)
 
@@ -996,13 +997,14 @@ __global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant_
 
 namespace {
 
-// Rays j0 + 32 p (p < NR) of the queue into the thread's first NR lanes; the others idle.
+// Rays j0 + p (p < NR) of the queue — consecutive entries, paths of neighbouring pixels, so the two rays of an FFMA2
+// pair tend to meet the same clusters — into the thread's first NR lanes; the others idle.
 template <int NR>
 __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                              uint32_t j0, Lanes& L, uint32_t& rays) {
 #pragma unroll
     for (int p = 0; p < kPix; ++p) {
-        const uint32_t j = j0 + 32u * (uint32_t)p;
+        const uint32_t j = j0 + (uint32_t)p;
         if (p < NR && j < count) {
             const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
             arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
@@ -1019,7 +1021,7 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
                                            const Lanes& L, uint32_t bounce, bool last, bool reset, int lane) {
 #pragma unroll 1
     for (int p = 0; p < NR; ++p) {
-        const uint32_t j = j0 + 32u * (uint32_t)p;
+        const uint32_t j = j0 + (uint32_t)p;
         bool push = false;
         f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
         uint32_t texel_index = 0, bseed = 0, n = 0;
@@ -1048,6 +1050,184 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 }
 
 
+// ---------------------------------------------------------------------------------------------
+// Clustered traversal for incoherent rays (rt_cluster.h).  The scene image in shared memory is
+// [cluster records | member records | member -> sphere index | members per cluster].  A thread first runs its rays
+// against the CLUSTER records (7-FFMA2 test with the ray's lowered threshold, rtc::cluster_thr) and notes the
+// (cluster, ray pair) combinations that pass; the warp then drains the notes together, each lane scanning the
+// members of its own cluster with the ordinary broad test and putting the survivors through the reference quadratic.
+// The exact tests no longer come in index order, so the nearest hit is kept with rtc::nearest_update (ties to the
+// lower index); a NaN root makes the reference's result order dependent, and such a ray is retraced sequentially.
+// ---------------------------------------------------------------------------------------------
+struct ClusterView {
+    const float4* top;
+    const float4* mem;
+    const unsigned short* order;
+    const unsigned char* count;
+    int n_top_pad;
+    float extra_r;
+};
+
+__device__ __forceinline__ ClusterView cluster_view(const void* blob, uint32_t n_top, float extra_r) {
+    const uint32_t n_top_pad = (n_top + 7u) / 8u * 8u;
+    const unsigned char* b = static_cast<const unsigned char*>(blob);
+    ClusterView cv;
+    cv.top = reinterpret_cast<const float4*>(b);
+    cv.mem = reinterpret_cast<const float4*>(b + (size_t)n_top_pad * 16u);
+    const size_t off_order = (size_t)n_top_pad * 16u + (size_t)n_top * kClusterStride * 16u;
+    cv.order = reinterpret_cast<const unsigned short*>(b + off_order);
+    cv.count = b + off_order + ((size_t)n_top * kClusterStride * 2u + 15u) / 16u * 16u;
+    cv.n_top_pad = (int)n_top_pad;
+    cv.extra_r = extra_r;
+    return cv;
+}
+
+// The reference loop itself (compute_shader.wgsl:164-180) for a ray whose clustered traversal met a NaN root.
+__device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ spheres, uint32_t n_spheres, float ox, float oy,
+                                                  float oz, float dx, float dy, float dz, float a) {
+    float bt = kTMax;
+    int bi = -1;
+    for (uint32_t si = 0; si < n_spheres; ++si) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(spheres + si));
+        float root;
+        if (rtc::sphere_root(rtc::mk(ox, oy, oz), rtc::mk(dx, dy, dz), a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, bt, &root)) {
+            bt = root;
+            bi = (int)si;
+        }
+    }
+    return make_float2(bt, __int_as_float(bi));
+}
+
+// Members of cluster c against ray pair Q of the thread (rays 2Q and 2Q + 1).  The broad tests of all the member
+// slots run branch-free (padding slots never pass) and leave a bit per (member, ray) candidate; the candidates are
+// appended to the thread's list (s_cand column: member slot << 2 | ray) for drain_candidates.
+template <int Q>
+__device__ __forceinline__ void cluster_members(const ClusterView& cv, int c, const Lanes& L, unsigned short* __restrict__ s_cand,
+                                                int& n_cand) {
+    const int base = c * kClusterStride;
+    const float thr0 = L.alive[2 * Q] ? L.thr[2 * Q] : __int_as_float(0x7f800000);
+    const float thr1 = L.alive[2 * Q + 1] ? L.thr[2 * Q + 1] : __int_as_float(0x7f800000);
+    uint32_t cand = 0;
+#pragma unroll
+    for (int u = 0; u < kClusterSlots; ++u) {
+        const float2 g = broad_g2(cv.mem[base + u], L, Q);
+        cand |= (!(g.x < thr0) ? 1u : 0u) << (2 * u);
+        cand |= (!(g.y < thr1) ? 1u : 0u) << (2 * u + 1);
+    }
+    while (cand) {
+        const int bit = __ffs((int)cand) - 1;
+        cand &= cand - 1u;
+        s_cand[n_cand * kBlockThreads] = (unsigned short)(((base + (bit >> 1)) << 2) | (2 * Q + (bit & 1)));
+        ++n_cand;
+    }
+}
+
+// One exact test per lane and iteration: every lane works on its own (member, ray) candidate, so the reference
+// quadratic runs on full warps instead of on the one lane that happened to find a candidate.
+template <int NP>
+__device__ __forceinline__ void drain_candidates(const ClusterView& cv, const unsigned short* __restrict__ s_cand, int& n_cand,
+                                                 const GpuSphere* __restrict__ spheres, Lanes& L, uint32_t& exact_tests,
+                                                 uint32_t& nan_rays) {
+    for (int e = 0; __any_sync(kFull, e < n_cand); ++e) {
+        if (e < n_cand) {
+            const int code = (int)s_cand[e * kBlockThreads];
+            const int idx = (int)cv.order[code >> 2], p = code & 3;
+            if (idx != 0xFFFF) {   // (a padding slot can only get here through a NaN threshold)
+                const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
+                // the ray is picked with selects: one copy of the quadratic for all the thread's rays
+                f3 o = origin_of(L, 0), d = rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
+                float a = L.a[0], bt = L.best_t[0];
+                int bi = L.best_i[0];
+#pragma unroll
+                for (int k = 1; k < 2 * NP; ++k) {
+                    if (p == k) {
+                        o = origin_of(L, k);
+                        d = rtc::mk(L.dx[k], L.dy[k], L.dz[k]);
+                        a = L.a[k];
+                        bt = L.best_t[k];
+                        bi = L.best_i[k];
+                    }
+                }
+                ++exact_tests;
+                if (!rtc::nearest_update(o, d, a, rtc::mk(gs.x, gs.y, gs.z), gs.w, kTMin, kTMax, idx, &bt, &bi)) nan_rays |= 1u << p;
+#pragma unroll
+                for (int k = 0; k < 2 * NP; ++k) {
+                    if (p == k) {
+                        L.best_t[k] = bt;
+                        L.best_i[k] = bi;
+                    }
+                }
+            }
+        }
+    }
+    n_cand = 0;
+}
+
+template <int NP>
+__device__ __forceinline__ void drain_cluster_notes(const ClusterView& cv, const unsigned short* __restrict__ s_note, int& n_notes,
+                                                    unsigned short* __restrict__ s_cand, int& n_cand,
+                                                    const GpuSphere* __restrict__ spheres, Lanes& L, uint32_t& exact_tests,
+                                                    uint32_t& nan_rays) {
+    for (int e = 0; __any_sync(kFull, e < n_notes); ++e) {
+        if (e < n_notes) {
+            const int note = (int)s_note[e * kBlockThreads];
+            if (NP > 1 && (note >> 15)) cluster_members<NP - 1>(cv, note & 0x7fff, L, s_cand, n_cand);
+            else cluster_members<0>(cv, note & 0x7fff, L, s_cand, n_cand);
+        }
+        // a note adds at most 2 * kClusterSlots candidates
+        if (__any_sync(kFull, n_cand > kWfCand - 2 * kClusterSlots)) drain_candidates<NP>(cv, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+    }
+    n_notes = 0;
+}
+
+// Nearest hits of the thread's first 2 NP rays through the clusters.
+template <int NP>
+__device__ __forceinline__ void trace_clustered(const ClusterView& cv, unsigned short* __restrict__ s_note,
+                                                const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
+                                                uint32_t& exact_tests) {
+    unsigned short* s_cand = s_note + kWfDefer * kBlockThreads;   // [kWfCand][kBlockThreads], this thread's column
+    int n_cand = 0;
+    float thr2[2 * NP];
+#pragma unroll
+    for (int p = 0; p < 2 * NP; ++p) {
+        const f3 o = origin_of(L, p);
+        thr2[p] = rtc::cluster_thr(L.thr[p], rtc::dot(o, o), cv.extra_r);
+    }
+    uint32_t nan_rays = 0;
+    int n_notes = 0;
+#pragma unroll 1
+    for (int c0 = 0; c0 < cv.n_top_pad; c0 += 4) {
+        float4 rec[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) rec[u] = cv.top[c0 + u];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int q = 0; q < NP; ++q) {
+                const float2 g = broad_g2(rec[u], L, q);
+                const bool pass = (L.alive[2 * q] && !(g.x < thr2[2 * q])) || (L.alive[2 * q + 1] && !(g.y < thr2[2 * q + 1]));
+                s_note[n_notes * kBlockThreads] = (unsigned short)((c0 + u) | (q << 15));   // slot n_notes is free; kept only if `pass`
+                n_notes += pass ? 1 : 0;
+            }
+        }
+        if (__any_sync(kFull, n_notes > kWfDefer - 4 * NP))
+            drain_cluster_notes<NP>(cv, s_note, n_notes, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+    }
+    drain_cluster_notes<NP>(cv, s_note, n_notes, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+    drain_candidates<NP>(cv, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+    if (nan_rays) {
+#pragma unroll
+        for (int p = 0; p < 2 * NP; ++p) {
+            if (nan_rays & (1u << p)) {
+                const float2 hit = retrace_sequential(spheres, n_spheres, L.ox[p], L.oy[p], L.oz[p], L.dx[p], L.dy[p], L.dz[p], L.a[p]);
+                L.best_t[p] = hit.x;
+                L.best_i[p] = __float_as_int(hit.y);
+                exact_tests += n_spheres;
+            }
+        }
+    }
+}
+
 // Few paths left (less than RT_WF_COMPLETE_BELOW rays per resident warp): finish them inside ONE launch, every
 // remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
@@ -1056,7 +1236,7 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 #define RT_WF_COMPLETE_BELOW 32u
 #endif
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
-                                          const float4* __restrict__ s_stage, int n_pad, unsigned short* __restrict__ s_note,
+                                          const ClusterView& cv, unsigned short* __restrict__ s_note,
                                           unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
                                           uint32_t& exact_tests_out, uint32_t& rays_out, uint32_t& rays_later_out) {
     const uint32_t n_batches = (count + 63u) / 64u;
@@ -1067,14 +1247,14 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
         if (lane == 0) batch = atomicAdd(ticket, 1u);
         batch = __shfl_sync(kFull, batch, 0);
         if (batch >= n_batches) break;
-        const uint32_t j0 = batch * 64u + (uint32_t)lane;
+        const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
         Lanes L;
         wf_load_rays<2>(P, qin, count, j0, L, rays);
         f3 factor[2];
         uint32_t texel_index[2], bseed[2], n_samples[2];
 #pragma unroll
         for (int p = 0; p < 2; ++p) {
-            const uint32_t j = j0 + 32u * (uint32_t)p;
+            const uint32_t j = j0 + (uint32_t)p;
             factor[p] = rtc::mk(0.0f, 0.0f, 0.0f);
             texel_index[p] = bseed[p] = n_samples[p] = 0u;
             if (j < count) {
@@ -1086,7 +1266,7 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
             }
         }
         for (uint32_t b = bounce;; ++b) {
-            scan_spheres_deferred<1>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+            trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
                 if (!L.alive[p]) continue;
@@ -1122,6 +1302,9 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
 // kFinish: the instantiation the later bounces (>= kWfFinishFrom) use, which may finish a short queue in one launch
 // (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code: its
 // mere presence costs the full-queue loops 1.6 % (out of line) to 3 % (inlined), measured on the depth-30 4K frame.
+#ifndef RT_WF_FOUR_RAYS
+#define RT_WF_FOUR_RAYS 0
+#endif
 template <bool kFinish>
 __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
@@ -1160,24 +1343,29 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
         bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.geom + base, bytes, bar);
     };
 
-    if (n_chunks == 1) {
-        if (threadIdx.x == 0) request(0);
+    if (P.cl_n_top != 0u) {
+        // clustered scene image (rt_cluster.h) resident in shared memory: copied once per CTA
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar0, P.cl_bytes);
+            bulk_copy_g2s(stage0, P.cl_blob, P.cl_bytes, bar0);
+        }
         mbar_wait(bar0, 0u);
+        const ClusterView cv = cluster_view(s_stage, P.cl_n_top, P.cl_extra_r);
         // A warp's batch costs a full pass over the records however many of its ray slots are in use, so once the
         // queue no longer fills every resident warp with 4 rays per thread, batches shrink to 2 rays per thread (one
         // FFMA2 pair): a quarter of the latency per batch, twice the batches, and the machine stays busy.
         const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
-        if (count >= resident_warps * (32u * kPix)) {
+        if (RT_WF_FOUR_RAYS && count >= resident_warps * (32u * kPix)) {
             const uint32_t n_batches = (count + 32u * kPix - 1u) / (32u * kPix);
             for (;;) {
                 uint32_t batch = 0;
                 if (lane == 0) batch = atomicAdd(ticket, 1u);
                 batch = __shfl_sync(kFull, batch, 0);
                 if (batch >= n_batches) break;
-                const uint32_t j0 = batch * (32u * kPix) + (uint32_t)lane;
+                const uint32_t j0 = batch * (32u * kPix) + (uint32_t)(kPix * lane);
                 Lanes L;
                 wf_load_rays<kPix>(P, qin, count, j0, L, rays);
-                scan_spheres_deferred<kPairs>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+                trace_clustered<kPairs>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
                 wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
             }
         } else if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
@@ -1187,15 +1375,14 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
                 if (lane == 0) batch = atomicAdd(ticket, 1u);
                 batch = __shfl_sync(kFull, batch, 0);
                 if (batch >= n_batches) break;
-                const uint32_t j0 = batch * 64u + (uint32_t)lane;
+                const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
                 Lanes L;
                 wf_load_rays<2>(P, qin, count, j0, L, rays);
-                scan_spheres_deferred<1>(s_stage, n_pad, 0, s_note, P.spheres, P.n_spheres, L, exact_tests);
+                trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
                 wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
             }
         } else {
-            finish_paths(P, qin, count, s_stage, n_pad, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays,
-                         rays_later);
+            finish_paths(P, qin, count, cv, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
         }
     } else {
         const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
@@ -1207,9 +1394,9 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
             if (batch >= n_batches) break;
             if (threadIdx.x == 0) {
                 request(0);
-                request(1);
+                if (n_chunks > 1) request(1);
             }
-            const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)lane;
+            const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)(kPix * lane);
             Lanes L;
             wf_load_rays<kPix>(P, qin, count, j0, L, rays);
             for (int c = 0; c < n_chunks; ++c) {
@@ -1434,7 +1621,7 @@ static size_t prim_smem_bytes() {
 }
 
 static size_t bounce_smem_bytes() {
-    return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
+    return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)(kWfDefer + kWfCand) * kBlockThreads * sizeof(unsigned short);
 }
 
 cudaError_t configure_kernels() {

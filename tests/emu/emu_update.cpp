@@ -13,6 +13,7 @@
 #endif
 
 #include "../../gpu_ray_tracing_b200/csrc/rt_core.cuh"
+#include "../../gpu_ray_tracing_b200/csrc/rt_cluster.h"
 
 using rtc::f3;
 
@@ -30,6 +31,10 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     std::vector<float> prim(primary ? (size_t)count * 4 : 0);
     if (primary)
         for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);
+    // clustered traversal of the bounce rays (rtk::trace_clustered): the wavefront path uses it behind a primary pass
+    rtcl::Clusters cl;
+    const bool clustered = primary && rtcl::build(spheres, count, cl) && cl.bytes() <= (size_t)2 * (2048 + 8) * 16;
+    uint64_t cluster_rays = 0, cluster_tests = 0, member_tests = 0, retraced = 0;
     uint64_t prim_rays = 0, untraced = 0, tile_pairs = 0, tile_dropped = 0;
     const uint32_t seed_bits_early = rtc::f2u(cam.random_seed * 4294967296.0f);
     // tile level of the primary pass (rtk::prim_tile_bound / prim_cull): per 32 x 8 pixel tile of the window, the
@@ -80,7 +85,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     const bool reset = cam.camera_has_moved > 0.5f;
     uint64_t rays = 0, exact = 0, violations = 0;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced, tile_dropped)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced, tile_dropped, cluster_rays, cluster_tests, member_tests, retraced)
 #endif
     for (int64_t row = 0; row < (int64_t)row_count; ++row) {
         const int y_abs = (int)(row_begin + row);
@@ -121,6 +126,48 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                                 ++violations;   // rejected a sphere the reference hits inside the original (tmin, tmax)
                             }
                         }
+                    } else if (clustered && i >= 1) {
+                        ++cluster_rays;
+                        const float thr2 = rtc::cluster_thr(b.thr, rtc::dot(r.o, r.o), cl.extra_r);
+                        std::vector<uint8_t> tested(count, 0);
+                        bool nan_root = false;
+                        for (uint32_t c = 0; c < cl.n_top; ++c) {
+                            const float* crec = &cl.top[(size_t)c * 4];
+                            ++cluster_tests;
+                            if (rtc::broad_g(crec[0], crec[1], crec[2], crec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < thr2)
+                                continue;
+                            for (uint32_t u = 0; u < cl.count[c]; ++u) {
+                                const float* mrec = &cl.mem[((size_t)c * rtcl::kStride + u) * 4];
+                                ++member_tests;
+                                if (rtc::broad_g(mrec[0], mrec[1], mrec[2], mrec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < b.thr)
+                                    continue;
+                                const uint32_t s = cl.order[(size_t)c * rtcl::kStride + u];
+                                const GpuSphere& sp = spheres[s];
+                                ++exact;
+                                tested[s] = 1;
+                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)s,
+                                                         &best_t, &best_i))
+                                    nan_root = true;
+                            }
+                        }
+                        for (uint32_t s = 0; s < count; ++s) {
+                            float root;
+                            if (!tested[s] && rtc::sphere_root(r.o, r.d, a, rtc::mk(spheres[s].position), spheres[s].radius, 0.001f,
+                                                               3.4e35f, &root))
+                                ++violations;   // the clusters skipped a sphere the reference hits
+                        }
+                        if (nan_root) {   // order matters once a root is NaN: the reference loop itself
+                            ++retraced;
+                            best_t = 3.4e35f;
+                            best_i = -1;
+                            for (uint32_t s = 0; s < count; ++s) {
+                                float root;
+                                if (rtc::sphere_root(r.o, r.d, a, rtc::mk(spheres[s].position), spheres[s].radius, 0.001f, best_t, &root)) {
+                                    best_t = root;
+                                    best_i = (int)s;
+                                }
+                            }
+                        }
                     } else {
                     if (use_primary) ++untraced;
                     for (uint32_t s = 0; s < count; ++s) {
@@ -155,6 +202,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     if (stats) {
         stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced;
         stats[5] = tile_pairs; stats[6] = tile_dropped;
+        stats[7] = cluster_rays; stats[8] = cluster_tests; stats[9] = member_tests; stats[10] = retraced;
     }
 }
 
