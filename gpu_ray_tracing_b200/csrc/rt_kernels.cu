@@ -1294,19 +1294,78 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
 
 }  // namespace
 
-// Traces queue P.wf_bounce, 4 rays per thread.  The general records reach shared memory by bulk copies.
-//   scene fits one stage (<= kWfChunk records): copied once per CTA, then every WARP pulls batches of 128 rays on
-//     its own — no block barrier in the loop, so a warp with long exact-test queues delays nobody;
-//   larger scenes: a CTA takes batches of 1024 rays and streams the records through two stages as
-//     primary_hits_kernel does.
-// kFinish: the instantiation the later bounces (>= kWfFinishFrom) use, which may finish a short queue in one launch
-// (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code: its
-// mere presence costs the full-queue loops 1.6 % (out of line) to 3 % (inlined), measured on the depth-30 4K frame.
-#ifndef RT_WF_FOUR_RAYS
-#define RT_WF_FOUR_RAYS 0
-#endif
+// Rays traced at this bounce (the to-completion path adds its later bounces itself) and the frame counters.
+__device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce, uint32_t exact_tests, uint32_t rays,
+                                         uint32_t rays_later, int lane) {
+    uint32_t mine = rays - rays_later;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(kFull, mine, o);
+    if (lane == 0 && mine) atomicAdd(&P.wf_counts[2u * (kWfMaxDepth + 1u) + bounce], mine);
+    prim_flush(P, exact_tests, rays, lane);
+}
+
+// Traces queue P.wf_bounce through the clustered scene image (rt_cluster.h), which is copied into shared memory once
+// per CTA; every WARP then pulls batches of 64 rays (2 per thread, one FFMA2 pair) on its own — no block barrier in
+// the loop, so a warp with long note or candidate queues delays nobody.  Two rays per thread rather than four: the
+// drains run as long as the busiest lane's queue, and the queues of a thread grow with its rays.
+// kFinish: the instantiation the later bounces use (launch_update), which may finish a short queue in one launch
+// (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code.
+// Three CTAs per SM for the full-queue instantiation (77 registers, ~60 KB of shared memory for 1024 spheres); the
+// finishing one would spill at that budget and runs when the machine is mostly idle anyway.
 template <bool kFinish>
-__global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_constant__ UpdateParams P) {
+__global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_dyn[];
+    __shared__ __align__(8) uint64_t s_bar;
+    const uint32_t image_slots = (P.cl_bytes + 15u) / 16u;
+    unsigned short* s_note = reinterpret_cast<unsigned short*>(s_dyn + image_slots) + threadIdx.x;   // [kWfDefer + kWfCand][kBlockThreads]
+    const int lane = threadIdx.x & 31;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const uint32_t bounce = P.wf_bounce;
+    const uint32_t count = P.wf_counts[bounce];
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool last = bounce + 1u >= max_depth;
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const float4* qin = P.wf_queue[bounce & 1u];
+    unsigned int* ticket = &P.wf_counts[kWfMaxDepth + 1u + bounce];
+    uint32_t exact_tests = 0, rays = 0, rays_later = 0;
+    if (count == 0u) return;
+
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, P.cl_bytes);
+        bulk_copy_g2s((uint32_t)__cvta_generic_to_shared(s_dyn), P.cl_blob, P.cl_bytes, bar);
+    }
+    mbar_wait(bar, 0u);
+    const ClusterView cv = cluster_view(s_dyn, P.cl_n_top, P.cl_extra_r);
+    const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
+    if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
+        const uint32_t n_batches = (count + 63u) / 64u;
+        for (;;) {
+            uint32_t batch = 0;
+            if (lane == 0) batch = atomicAdd(ticket, 1u);
+            batch = __shfl_sync(kFull, batch, 0);
+            if (batch >= n_batches) break;
+            const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
+            Lanes L;
+            wf_load_rays<2>(P, qin, count, j0, L, rays);
+            trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
+            wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
+        }
+    } else {
+        finish_paths(P, qin, count, cv, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+    }
+    wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
+}
+
+// Traces queue P.wf_bounce for scenes without a clustered image (more spheres than its shared-memory budget): 4 rays
+// per thread, a CTA takes batches of 1024 rays and streams the plain records through two stages as
+// primary_hits_kernel does.
+__global__ void __launch_bounds__(kBlockThreads, 2) bounce_streamed_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     constexpr int kStage = kWfChunk + kGeomTail;
     __shared__ __align__(8) uint64_t s_bar[2];
@@ -1332,7 +1391,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
     unsigned int* ticket = &P.wf_counts[kWfMaxDepth + 1u + bounce];
     const int n_pad = (int)((P.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad);
     const int n_chunks = (n_pad + kWfChunk - 1) / kWfChunk;
-    uint32_t exact_tests = 0, rays = 0, rays_later = 0, parity = 0;
+    uint32_t exact_tests = 0, rays = 0, parity = 0;
     if (count == 0u) return;
 
     auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
@@ -1343,81 +1402,32 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_kernel(const __grid_c
         bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.geom + base, bytes, bar);
     };
 
-    if (P.cl_n_top != 0u) {
-        // clustered scene image (rt_cluster.h) resident in shared memory: copied once per CTA
+    const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_batch = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const uint32_t batch = s_batch;
+        if (batch >= n_batches) break;
         if (threadIdx.x == 0) {
-            mbar_expect_tx(bar0, P.cl_bytes);
-            bulk_copy_g2s(stage0, P.cl_blob, P.cl_bytes, bar0);
+            request(0);
+            if (n_chunks > 1) request(1);
         }
-        mbar_wait(bar0, 0u);
-        const ClusterView cv = cluster_view(s_stage, P.cl_n_top, P.cl_extra_r);
-        // A warp's batch costs a full pass over the records however many of its ray slots are in use, so once the
-        // queue no longer fills every resident warp with 4 rays per thread, batches shrink to 2 rays per thread (one
-        // FFMA2 pair): a quarter of the latency per batch, twice the batches, and the machine stays busy.
-        const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
-        if (RT_WF_FOUR_RAYS && count >= resident_warps * (32u * kPix)) {
-            const uint32_t n_batches = (count + 32u * kPix - 1u) / (32u * kPix);
-            for (;;) {
-                uint32_t batch = 0;
-                if (lane == 0) batch = atomicAdd(ticket, 1u);
-                batch = __shfl_sync(kFull, batch, 0);
-                if (batch >= n_batches) break;
-                const uint32_t j0 = batch * (32u * kPix) + (uint32_t)(kPix * lane);
-                Lanes L;
-                wf_load_rays<kPix>(P, qin, count, j0, L, rays);
-                trace_clustered<kPairs>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
-                wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
-            }
-        } else if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
-            const uint32_t n_batches = (count + 63u) / 64u;
-            for (;;) {
-                uint32_t batch = 0;
-                if (lane == 0) batch = atomicAdd(ticket, 1u);
-                batch = __shfl_sync(kFull, batch, 0);
-                if (batch >= n_batches) break;
-                const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
-                Lanes L;
-                wf_load_rays<2>(P, qin, count, j0, L, rays);
-                trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
-                wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
-            }
-        } else {
-            finish_paths(P, qin, count, cv, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+        const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)(kPix * lane);
+        Lanes L;
+        wf_load_rays<kPix>(P, qin, count, j0, L, rays);
+        for (int c = 0; c < n_chunks; ++c) {
+            const int st = c & 1, base = c * kWfChunk;
+            mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
+            parity ^= 1u << st;
+            scan_spheres_deferred<kPairs>(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres,
+                                          P.n_spheres, L, exact_tests);
+            __syncthreads();   // every warp has left stage st
+            if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
         }
-    } else {
-        const uint32_t n_batches = (count + 8u * 32u * kPix - 1u) / (8u * 32u * kPix);
-        for (;;) {
-            __syncthreads();
-            if (threadIdx.x == 0) s_batch = atomicAdd(ticket, 1u);
-            __syncthreads();
-            const uint32_t batch = s_batch;
-            if (batch >= n_batches) break;
-            if (threadIdx.x == 0) {
-                request(0);
-                if (n_chunks > 1) request(1);
-            }
-            const uint32_t j0 = batch * (8u * 32u * kPix) + (uint32_t)warp * (32u * kPix) + (uint32_t)(kPix * lane);
-            Lanes L;
-            wf_load_rays<kPix>(P, qin, count, j0, L, rays);
-            for (int c = 0; c < n_chunks; ++c) {
-                const int st = c & 1, base = c * kWfChunk;
-                mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
-                parity ^= 1u << st;
-                scan_spheres_deferred<kPairs>(s_stage + st * kStage, min(kWfChunk, n_pad - base), base, s_note, P.spheres,
-                                      P.n_spheres, L, exact_tests);
-                __syncthreads();   // every warp has left stage st
-                if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
-            }
-            wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
-        }
+        wf_resolve<kPix>(P, qin, count, j0, L, bounce, last, reset, lane);
     }
-    {   // rays traced at this bounce (the to-completion path adds its later bounces itself)
-        uint32_t mine = rays - rays_later;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(kFull, mine, o);
-        if (lane == 0 && mine) atomicAdd(&P.wf_counts[2u * (kWfMaxDepth + 1u) + bounce], mine);
-    }
-    prim_flush(P, exact_tests, rays, lane);
+    wf_flush(P, bounce, exact_tests, rays, 0u, lane);
 }
 
 // Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
@@ -1621,7 +1631,10 @@ static size_t prim_smem_bytes() {
 }
 
 static size_t bounce_smem_bytes() {
-    return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)(kWfDefer + kWfCand) * kBlockThreads * sizeof(unsigned short);
+    return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
+}
+static size_t clustered_smem_bytes(uint32_t image_bytes) {
+    return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(kWfDefer + kWfCand) * kBlockThreads * sizeof(unsigned short);
 }
 
 cudaError_t configure_kernels() {
@@ -1634,9 +1647,13 @@ cudaError_t configure_kernels() {
     e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
+    e = cudaFuncSetAttribute(bounce_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
@@ -1697,10 +1714,12 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (b < finish_from) {
-                    bounce_kernel<false><<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                if (p.cl_n_top == 0u) {
+                    bounce_streamed_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                } else if (b < finish_from) {
+                    bounce_clustered_kernel<false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes), stream>>>(p);
                 } else {
-                    bounce_kernel<true><<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+                    bounce_clustered_kernel<true><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes), stream>>>(p);
                 }
                 n_launch += 1;
             }
