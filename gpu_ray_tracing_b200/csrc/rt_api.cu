@@ -15,7 +15,7 @@
 #include "../../include/rt_abi.h"
 #include "rt_kernels.cuh"
 #include "rt_internal.h"
-#include "rt_cluster.h"
+#include "rt_tree.h"
 
 namespace rti {
 
@@ -175,7 +175,7 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
     r->n_spheres = count;
     r->host_spheres.assign(spheres, spheres + count);   // for the lazily built clusters of the bounce rays
     r->clusters_stale = true;
-    r->cl_n_top = 0;
+    r->cl_n_nodes = 0;
     RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
     r->launches += 1;
     // the source is borrowed for the call only (pageable memory: the copy above has been staged,
@@ -212,30 +212,39 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
     }
     if (camera->max_depth > 1.0f && r->clusters_stale && r->wf_counts) {
-        // first deep frame of this scene: cluster the spheres for the bounce rays (skipped when the image would not
-        // fit the bounce kernel's shared-memory stages; that kernel then streams the plain records instead)
+        // first deep frame of this scene: the tree of bounding spheres for the bounce rays (skipped when its image
+        // would not fit the bounce kernel's shared memory; that kernel then streams the plain records instead)
         r->clusters_stale = false;
-        rtcl::Clusters cl;
-        if (rtcl::build(r->host_spheres.data(), r->n_spheres, cl) && cl.bytes() <= rtk::kClusterImageMax) {
-            if (cl.bytes() > r->cl_capacity) {
+        rtt::Tree tree;
+        const bool built = rtt::build(r->host_spheres.data(), r->n_spheres, tree);
+        // per-thread node stack: the entry backlog, 4 more entries, and 7 per level of depth-first growth below them
+        const uint32_t stack_cap = built ? (uint32_t)rtk::kTreeBacklog + 4u + 7u * tree.depth : 0u;
+        if (built && r->n_spheres < 32768u && tree.bytes() <= rtk::kClusterImageMax && stack_cap <= rtk::kTreeStackMax) {
+            if (tree.bytes() > r->cl_capacity) {
                 RT_CUDA(cudaStreamSynchronize(r->stream));
                 cudaFree(r->cl_blob); r->cl_blob = nullptr; r->cl_capacity = 0;
-                RT_CUDA(cudaMalloc(&r->cl_blob, cl.bytes()));
-                r->cl_capacity = cl.bytes();
+                RT_CUDA(cudaMalloc(&r->cl_blob, tree.bytes()));
+                r->cl_capacity = tree.bytes();
             }
-            std::vector<unsigned char> image(cl.bytes());
-            cl.pack(image.data());
+            std::vector<unsigned char> image(tree.bytes());
+            tree.pack(image.data());
             RT_CUDA(cudaMemcpyAsync(r->cl_blob, image.data(), image.size(), cudaMemcpyHostToDevice, r->stream));
             RT_CUDA(cudaStreamSynchronize(r->stream));   // `image` is about to go away
-            r->cl_n_top = cl.n_top;
-            r->cl_bytes = (uint32_t)cl.bytes();
-            r->cl_extra_r = cl.extra_r;
+            r->cl_n_nodes = tree.n_nodes;
+            r->cl_first_leaf = tree.first_leaf;
+            r->cl_bytes = (uint32_t)tree.bytes();
+            r->cl_stack_cap = stack_cap;
+            r->cl_n_entry = tree.n_entry;
+            r->cl_entry_r = tree.entry_r;
         }
     }
     p.cl_blob = r->cl_blob;
-    p.cl_n_top = r->cl_n_top;
+    p.cl_n_nodes = r->cl_n_nodes;
+    p.cl_first_leaf = r->cl_first_leaf;
     p.cl_bytes = r->cl_bytes;
-    p.cl_extra_r = r->cl_extra_r;
+    p.cl_stack_cap = r->cl_stack_cap;
+    p.cl_n_entry = r->cl_n_entry;
+    p.cl_entry_r = r->cl_entry_r;
     p.wf_queue[0] = r->wf_queue[0];
     p.wf_queue[1] = r->wf_queue[1];
     p.wf_counts = r->wf_counts;

@@ -373,17 +373,13 @@ RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m,
 }
 
 // ---------------------------------------------------------------------------------------------
-// Cluster level of the general broad phase (rt_cluster.h).  A cluster's bounding sphere has an ordinary record
+// Group level of the general broad phase (rt_tree.h).  A group's bounding sphere has an ordinary record
 // (Cc, k(Rc')); the ray's own share of the bound, m = 2^-7 |O|, enters through the threshold:
-// (Rc' + m)^2 <= Rc'^2 + 2 Rmax m + m^2, so the cluster is descended into when g >= thr - (2 Rmax m + m^2).
-// oo = dot(O, O); extra_r = Rmax, the largest cluster radius of the scene.
+// (Rc' + m)^2 <= Rc'^2 + 2 Rmax m + m^2, so the group is descended into when g >= thr - (2 Rmax m + m^2).
+// m = cluster_m(dot(O, O)); extra_r = Rmax, the largest bounding radius among the children of the node being visited.
 // ---------------------------------------------------------------------------------------------
-#ifndef RT_CLUSTER_SLOTS
-#define RT_CLUSTER_SLOTS 8 /* member slots per cluster: rtcl::kSlots (host build) = rtk::kClusterSlots (kernels) */
-#endif
-
-RT_DEV float cluster_thr(float thr, float oo, float extra_r) {
-    const float m = sqrtf(oo) * 0.00782012939453125f;   // 2^-7 (1 + 2^-10)
+RT_DEV float cluster_m(float oo) { return sqrtf(oo) * 0.00782012939453125f; }   // 2^-7 (1 + 2^-10) |O|
+RT_DEV float cluster_thr(float thr, float m, float extra_r) {
     const float extra = fmaf(m, m, (2.0f * extra_r) * m) * 1.0009765625f;
     return thr - extra;
 }

@@ -23,14 +23,14 @@ struct RtRenderer {
     float2* first_hit = nullptr;          // (t, sphere index) per texel, written by the primary pass
     float4* wf_queue[2] = {nullptr, nullptr};   // wavefront path queues (3 planes of n_texels float4 each), on first deep frame
     unsigned int* wf_counts = nullptr;
-    // clustered scene image for the bounce rays (rt_cluster.h): built lazily, on the first deep frame after rt_set_scene,
+    // tree image of the scene for the bounce rays (rt_tree.h): built lazily, on the first deep frame after rt_set_scene,
     // from the host copy of the sphere list kept for that purpose
     std::vector<GpuSphere> host_spheres;
     bool clusters_stale = true;
     unsigned char* cl_blob = nullptr;
     size_t cl_capacity = 0;
-    uint32_t cl_n_top = 0, cl_bytes = 0;
-    float cl_extra_r = 0.0f;
+    uint32_t cl_n_nodes = 0, cl_first_leaf = 0, cl_bytes = 0, cl_stack_cap = 0, cl_n_entry = 0;
+    float cl_entry_r = 0.0f;
     uint32_t n_spheres = 0;
     bool has_scene = false;
     unsigned int* tile_counter = nullptr;

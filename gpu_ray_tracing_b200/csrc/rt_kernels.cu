@@ -28,7 +28,6 @@ constexpr float kTMin = 0.001f;    // compute_shader.wgsl:266
 constexpr float kTMax = 3.4e35f;
 constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kUnroll = 4;         // spheres per broad-phase iteration
-static_assert(2 * kClusterSlots <= 32, "cluster_members keeps one candidate bit per (member, ray)");
 constexpr int kGeomPad = 8;        // geometry arrays are padded to a multiple of this ...
 constexpr int kGeomTail = 8;       // ... plus a tail the software prefetch may read (never computed)
 
@@ -1051,38 +1050,47 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 
 
 // ---------------------------------------------------------------------------------------------
-// Clustered traversal for incoherent rays (rt_cluster.h).  The scene image in shared memory is
-// [cluster records | member records | member -> sphere index | members per cluster].  A thread first runs its rays
-// against the CLUSTER records (7-FFMA2 test with the ray's lowered threshold, rtc::cluster_thr) and notes the
-// (cluster, ray pair) combinations that pass; the warp then drains the notes together, each lane scanning the
-// members of its own cluster with the ordinary broad test and putting the survivors through the reference quadratic.
-// The exact tests no longer come in index order, so the nearest hit is kept with rtc::nearest_update (ties to the
-// lower index); a NaN root makes the reference's result order dependent, and such a ray is retraced sequentially.
+// Tree traversal for incoherent rays (rt_tree.h).  The scene image in shared memory is
+// [child records, 9 slots per node | child links, 8 per node | largest child radius per node].  A thread traces one
+// FFMA2 pair of rays: it keeps a private stack of node numbers (a column of shared memory), pops a node, runs the
+// 7-FFMA2 test against its 8 child records branch-free (empty slots never pass) — with the ray's lowered threshold
+// (rtc::cluster_thr) for bounding spheres, with the ordinary one for the spheres under a leaf node — and pushes the
+// children either ray passes, or, under a leaf node, appends (sphere, ray) candidates to its list.  The warp drains the
+// candidate lists together, one exact test per lane and iteration.  The exact tests do not come in index order, so the
+// nearest hit is kept with rtc::nearest_update (ties to the lower index); a NaN root makes the reference's result
+// order dependent, and such a ray is retraced sequentially.
 // ---------------------------------------------------------------------------------------------
-struct ClusterView {
-    const float4* top;
-    const float4* mem;
-    const unsigned short* order;
-    const unsigned char* count;
-    int n_top_pad;
-    float extra_r;
+struct TreeView {
+    const float4* rec;
+    const unsigned short* link;
+    const float* node_r;
+    const float4* entry_rec;            // the entry list (rt_tree.h): records ...
+    const unsigned short* entry_node;   // ... and the nodes they stand for
+    int first_leaf, n_entry_pad, stack_cap;
+    float entry_r;
 };
 
-__device__ __forceinline__ ClusterView cluster_view(const void* blob, uint32_t n_top, float extra_r) {
-    const uint32_t n_top_pad = (n_top + 7u) / 8u * 8u;
+__device__ __forceinline__ TreeView tree_view(const void* blob, uint32_t n_nodes, uint32_t first_leaf, uint32_t n_entry,
+                                              float entry_r, uint32_t stack_cap) {
     const unsigned char* b = static_cast<const unsigned char*>(blob);
-    ClusterView cv;
-    cv.top = reinterpret_cast<const float4*>(b);
-    cv.mem = reinterpret_cast<const float4*>(b + (size_t)n_top_pad * 16u);
-    const size_t off_order = (size_t)n_top_pad * 16u + (size_t)n_top * kClusterStride * 16u;
-    cv.order = reinterpret_cast<const unsigned short*>(b + off_order);
-    cv.count = b + off_order + ((size_t)n_top * kClusterStride * 2u + 15u) / 16u * 16u;
-    cv.n_top_pad = (int)n_top_pad;
-    cv.extra_r = extra_r;
-    return cv;
+    TreeView tv;
+    tv.rec = reinterpret_cast<const float4*>(b);
+    const size_t off_link = (size_t)n_nodes * kTreeStride * 16u;
+    tv.link = reinterpret_cast<const unsigned short*>(b + off_link);
+    const size_t off_r = off_link + ((size_t)n_nodes * kTreeWide * 2u + 15u) / 16u * 16u;
+    tv.node_r = reinterpret_cast<const float*>(b + off_r);
+    const size_t off_entry = off_r + ((size_t)n_nodes * 4u + 15u) / 16u * 16u;
+    const uint32_t n_entry_pad = (n_entry + 3u) / 4u * 4u;
+    tv.entry_rec = reinterpret_cast<const float4*>(b + off_entry);
+    tv.entry_node = reinterpret_cast<const unsigned short*>(b + off_entry + (size_t)n_entry_pad * 16u);
+    tv.first_leaf = (int)first_leaf;
+    tv.n_entry_pad = (int)n_entry_pad;
+    tv.stack_cap = (int)stack_cap;
+    tv.entry_r = entry_r;
+    return tv;
 }
 
-// The reference loop itself (compute_shader.wgsl:164-180) for a ray whose clustered traversal met a NaN root.
+// The reference loop itself (compute_shader.wgsl:164-180) for a ray whose tree traversal met a NaN root.
 __device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ spheres, uint32_t n_spheres, float ox, float oy,
                                                   float oz, float dx, float dy, float dz, float a) {
     float bt = kTMax;
@@ -1098,126 +1106,121 @@ __device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ 
     return make_float2(bt, __int_as_float(bi));
 }
 
-// Members of cluster c against ray pair Q of the thread (rays 2Q and 2Q + 1).  The broad tests of all the member
-// slots run branch-free (padding slots never pass) and leave a bit per (member, ray) candidate; the candidates are
-// appended to the thread's list (s_cand column: member slot << 2 | ray) for drain_candidates.
-template <int Q>
-__device__ __forceinline__ void cluster_members(const ClusterView& cv, int c, const Lanes& L, unsigned short* __restrict__ s_cand,
-                                                int& n_cand) {
-    const int base = c * kClusterStride;
-    const float thr0 = L.alive[2 * Q] ? L.thr[2 * Q] : __int_as_float(0x7f800000);
-    const float thr1 = L.alive[2 * Q + 1] ? L.thr[2 * Q + 1] : __int_as_float(0x7f800000);
-    uint32_t cand = 0;
-#pragma unroll
-    for (int u = 0; u < kClusterSlots; ++u) {
-        const float2 g = broad_g2(cv.mem[base + u], L, Q);
-        cand |= (!(g.x < thr0) ? 1u : 0u) << (2 * u);
-        cand |= (!(g.y < thr1) ? 1u : 0u) << (2 * u + 1);
-    }
-    while (cand) {
-        const int bit = __ffs((int)cand) - 1;
-        cand &= cand - 1u;
-        s_cand[n_cand * kBlockThreads] = (unsigned short)(((base + (bit >> 1)) << 2) | (2 * Q + (bit & 1)));
-        ++n_cand;
-    }
-}
-
-// One exact test per lane and iteration: every lane works on its own (member, ray) candidate, so the reference
+// One exact test per lane and iteration: every lane works on its own (sphere, ray) candidate, so the reference
 // quadratic runs on full warps instead of on the one lane that happened to find a candidate.
-template <int NP>
-__device__ __forceinline__ void drain_candidates(const ClusterView& cv, const unsigned short* __restrict__ s_cand, int& n_cand,
+__device__ __forceinline__ void drain_candidates(const unsigned short* __restrict__ s_cand, int& n_cand,
                                                  const GpuSphere* __restrict__ spheres, Lanes& L, uint32_t& exact_tests,
                                                  uint32_t& nan_rays) {
     for (int e = 0; __any_sync(kFull, e < n_cand); ++e) {
         if (e < n_cand) {
             const int code = (int)s_cand[e * kBlockThreads];
-            const int idx = (int)cv.order[code >> 2], p = code & 3;
-            if (idx != 0xFFFF) {   // (a padding slot can only get here through a NaN threshold)
-                const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
-                // the ray is picked with selects: one copy of the quadratic for all the thread's rays
-                f3 o = origin_of(L, 0), d = rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
-                float a = L.a[0], bt = L.best_t[0];
-                int bi = L.best_i[0];
-#pragma unroll
-                for (int k = 1; k < 2 * NP; ++k) {
-                    if (p == k) {
-                        o = origin_of(L, k);
-                        d = rtc::mk(L.dx[k], L.dy[k], L.dz[k]);
-                        a = L.a[k];
-                        bt = L.best_t[k];
-                        bi = L.best_i[k];
-                    }
-                }
-                ++exact_tests;
-                if (!rtc::nearest_update(o, d, a, rtc::mk(gs.x, gs.y, gs.z), gs.w, kTMin, kTMax, idx, &bt, &bi)) nan_rays |= 1u << p;
-#pragma unroll
-                for (int k = 0; k < 2 * NP; ++k) {
-                    if (p == k) {
-                        L.best_t[k] = bt;
-                        L.best_i[k] = bi;
-                    }
-                }
+            const int idx = code & 0x7fff;
+            const bool second = (code >> 15) != 0;
+            const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
+            // the ray is picked with selects: one copy of the quadratic for both rays
+            const f3 o = second ? origin_of(L, 1) : origin_of(L, 0);
+            const f3 d = second ? rtc::mk(L.dx[1], L.dy[1], L.dz[1]) : rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
+            const float a = second ? L.a[1] : L.a[0];
+            float bt = second ? L.best_t[1] : L.best_t[0];
+            int bi = second ? L.best_i[1] : L.best_i[0];
+            ++exact_tests;
+            if (!rtc::nearest_update(o, d, a, rtc::mk(gs.x, gs.y, gs.z), gs.w, kTMin, kTMax, idx, &bt, &bi))
+                nan_rays |= second ? 2u : 1u;
+            if (second) {
+                L.best_t[1] = bt;
+                L.best_i[1] = bi;
+            } else {
+                L.best_t[0] = bt;
+                L.best_i[0] = bi;
             }
         }
     }
     n_cand = 0;
 }
 
-template <int NP>
-__device__ __forceinline__ void drain_cluster_notes(const ClusterView& cv, const unsigned short* __restrict__ s_note, int& n_notes,
-                                                    unsigned short* __restrict__ s_cand, int& n_cand,
-                                                    const GpuSphere* __restrict__ spheres, Lanes& L, uint32_t& exact_tests,
-                                                    uint32_t& nan_rays) {
-    for (int e = 0; __any_sync(kFull, e < n_notes); ++e) {
-        if (e < n_notes) {
-            const int note = (int)s_note[e * kBlockThreads];
-            if (NP > 1 && (note >> 15)) cluster_members<NP - 1>(cv, note & 0x7fff, L, s_cand, n_cand);
-            else cluster_members<0>(cv, note & 0x7fff, L, s_cand, n_cand);
-        }
-        // a note adds at most 2 * kClusterSlots candidates
-        if (__any_sync(kFull, n_cand > kWfCand - 2 * kClusterSlots)) drain_candidates<NP>(cv, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
-    }
-    n_notes = 0;
-}
-
-// Nearest hits of the thread's first 2 NP rays through the clusters.
-template <int NP>
-__device__ __forceinline__ void trace_clustered(const ClusterView& cv, unsigned short* __restrict__ s_note,
-                                                const GpuSphere* __restrict__ spheres, uint32_t n_spheres, Lanes& L,
-                                                uint32_t& exact_tests) {
-    unsigned short* s_cand = s_note + kWfDefer * kBlockThreads;   // [kWfCand][kBlockThreads], this thread's column
-    int n_cand = 0;
-    float thr2[2 * NP];
-#pragma unroll
-    for (int p = 0; p < 2 * NP; ++p) {
-        const f3 o = origin_of(L, p);
-        thr2[p] = rtc::cluster_thr(L.thr[p], rtc::dot(o, o), cv.extra_r);
-    }
+// Nearest hits of the thread's rays 0 and 1 through the tree.  s_stack / s_cand: this thread's columns.
+__device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* __restrict__ s_stack,
+                                           unsigned short* __restrict__ s_cand, const GpuSphere* __restrict__ spheres,
+                                           uint32_t n_spheres, Lanes& L, uint32_t& exact_tests) {
+    const float inf = __int_as_float(0x7f800000);
+    const float thr0 = L.alive[0] ? L.thr[0] : inf, thr1 = L.alive[1] ? L.thr[1] : inf;
+    const f3 o0 = origin_of(L, 0), o1 = origin_of(L, 1);
+    const float m0 = rtc::cluster_m(rtc::dot(o0, o0)), m1 = rtc::cluster_m(rtc::dot(o1, o1));
     uint32_t nan_rays = 0;
-    int n_notes = 0;
-#pragma unroll 1
-    for (int c0 = 0; c0 < cv.n_top_pad; c0 += 4) {
-        float4 rec[4];
+    int n_stack = 0, n_cand = 0;
+    auto traverse = [&]() {   // empties every lane's stack
+    while (__any_sync(kFull, n_stack > 0)) {
+        if (n_stack > 0) {
+            const int node = (int)s_stack[(--n_stack) * kBlockThreads];
+            const bool leaf = node >= tv.first_leaf;
+            float t0 = thr0, t1 = thr1;
+            if (!leaf) {
+                const float r = tv.node_r[node];
+                t0 = rtc::cluster_thr(thr0, m0, r);
+                t1 = rtc::cluster_thr(thr1, m1, r);
+            }
+            const float4* rec = tv.rec + node * kTreeStride;
+            uint32_t pass = 0;   // bit 2k: ray 0 passes child k, bit 2k + 1: ray 1
 #pragma unroll
-        for (int u = 0; u < 4; ++u) rec[u] = cv.top[c0 + u];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-#pragma unroll
-            for (int q = 0; q < NP; ++q) {
-                const float2 g = broad_g2(rec[u], L, q);
-                const bool pass = (L.alive[2 * q] && !(g.x < thr2[2 * q])) || (L.alive[2 * q + 1] && !(g.y < thr2[2 * q + 1]));
-                s_note[n_notes * kBlockThreads] = (unsigned short)((c0 + u) | (q << 15));   // slot n_notes is free; kept only if `pass`
-                n_notes += pass ? 1 : 0;
+            for (int k = 0; k < kTreeWide; ++k) {
+                const float2 g = broad_g2(rec[k], L, 0);
+                pass |= (!(g.x < t0) ? 1u : 0u) << (2 * k);
+                pass |= (!(g.y < t1) ? 1u : 0u) << (2 * k + 1);
+            }
+            const unsigned short* link = tv.link + node * kTreeWide;
+            if (leaf) {
+                while (pass) {
+                    const int bit = __ffs((int)pass) - 1;
+                    pass &= pass - 1u;
+                    const unsigned idx = link[bit >> 1];
+                    if (idx != 0xFFFFu) {   // (an empty slot can only get here through a NaN threshold)
+                        s_cand[n_cand * kBlockThreads] = (unsigned short)(idx | ((unsigned)(bit & 1) << 15));
+                        ++n_cand;
+                    }
+                }
+            } else {
+                pass = (pass | (pass >> 1)) & 0x5555u;   // either ray
+                while (pass) {
+                    const int bit = __ffs((int)pass) - 1;
+                    pass &= pass - 1u;
+                    const unsigned child = link[bit >> 1];
+                    if (child != 0xFFFFu) {
+                        s_stack[n_stack * kBlockThreads] = (unsigned short)child;
+                        ++n_stack;
+                    }
+                }
             }
         }
-        if (__any_sync(kFull, n_notes > kWfDefer - 4 * NP))
-            drain_cluster_notes<NP>(cv, s_note, n_notes, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+        // a leaf node adds at most 2 * kTreeWide candidates
+        if (__any_sync(kFull, n_cand > kWfCand - 2 * kTreeWide)) drain_candidates(s_cand, n_cand, spheres, L, exact_tests, nan_rays);
     }
-    drain_cluster_notes<NP>(cv, s_note, n_notes, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
-    drain_candidates<NP>(cv, s_cand, n_cand, spheres, L, exact_tests, nan_rays);
+    };
+    // the entry list, all lanes on the same record: the nodes either ray passes start the lane's stack
+    {
+        const float e0 = rtc::cluster_thr(thr0, m0, tv.entry_r), e1 = rtc::cluster_thr(thr1, m1, tv.entry_r);
+#pragma unroll 1
+        for (int c0 = 0; c0 < tv.n_entry_pad; c0 += 4) {
+            float4 rec[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) rec[u] = tv.entry_rec[c0 + u];
+            const uint2 nodes4 = *reinterpret_cast<const uint2*>(tv.entry_node + c0);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float2 g = broad_g2(rec[u], L, 0);
+                const bool pass = !(g.x < e0) || !(g.y < e1);
+                const unsigned node = ((u < 2 ? nodes4.x : nodes4.y) >> (16 * (u & 1))) & 0xFFFFu;
+                s_stack[n_stack * kBlockThreads] = (unsigned short)node;   // slot n_stack is free; kept only if `pass`
+                n_stack += (pass && node != 0xFFFFu) ? 1 : 0;
+            }
+            // the stack keeps room for 4 more entries and for the growth of the traversal below them (rt_api.cu)
+            if (__any_sync(kFull, n_stack > kTreeBacklog)) traverse();
+        }
+    }
+    traverse();
+    drain_candidates(s_cand, n_cand, spheres, L, exact_tests, nan_rays);
     if (nan_rays) {
 #pragma unroll
-        for (int p = 0; p < 2 * NP; ++p) {
+        for (int p = 0; p < 2; ++p) {
             if (nan_rays & (1u << p)) {
                 const float2 hit = retrace_sequential(spheres, n_spheres, L.ox[p], L.oy[p], L.oz[p], L.dx[p], L.dy[p], L.dz[p], L.a[p]);
                 L.best_t[p] = hit.x;
@@ -1236,7 +1239,7 @@ __device__ __forceinline__ void trace_clustered(const ClusterView& cv, unsigned 
 #define RT_WF_COMPLETE_BELOW 32u
 #endif
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
-                                          const ClusterView& cv, unsigned short* __restrict__ s_note,
+                                          const TreeView& tv, unsigned short* __restrict__ s_stack, unsigned short* __restrict__ s_cand,
                                           unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
                                           uint32_t& exact_tests_out, uint32_t& rays_out, uint32_t& rays_later_out) {
     const uint32_t n_batches = (count + 63u) / 64u;
@@ -1266,7 +1269,7 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
             }
         }
         for (uint32_t b = bounce;; ++b) {
-            trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
+            trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
                 if (!L.alive[p]) continue;
@@ -1304,10 +1307,10 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
     prim_flush(P, exact_tests, rays, lane);
 }
 
-// Traces queue P.wf_bounce through the clustered scene image (rt_cluster.h), which is copied into shared memory once
+// Traces queue P.wf_bounce through the tree image of the scene (rt_tree.h), which is copied into shared memory once
 // per CTA; every WARP then pulls batches of 64 rays (2 per thread, one FFMA2 pair) on its own — no block barrier in
-// the loop, so a warp with long note or candidate queues delays nobody.  Two rays per thread rather than four: the
-// drains run as long as the busiest lane's queue, and the queues of a thread grow with its rays.
+// the loop, so a warp with deep stacks or long candidate queues delays nobody.  Two rays per thread rather than four:
+// the traversal runs as long as the busiest lane's, and a thread's work grows with its rays.
 // kFinish: the instantiation the later bounces use (launch_update), which may finish a short queue in one launch
 // (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code.
 // Three CTAs per SM for the full-queue instantiation (77 registers, ~60 KB of shared memory for 1024 spheres); the
@@ -1317,7 +1320,8 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
     const uint32_t image_slots = (P.cl_bytes + 15u) / 16u;
-    unsigned short* s_note = reinterpret_cast<unsigned short*>(s_dyn + image_slots) + threadIdx.x;   // [kWfDefer + kWfCand][kBlockThreads]
+    unsigned short* s_stack = reinterpret_cast<unsigned short*>(s_dyn + image_slots) + threadIdx.x;   // [cl_stack_cap][kBlockThreads]
+    unsigned short* s_cand = s_stack + P.cl_stack_cap * kBlockThreads;                                // [kWfCand][kBlockThreads]
     const int lane = threadIdx.x & 31;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) {
@@ -1341,7 +1345,7 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
         bulk_copy_g2s((uint32_t)__cvta_generic_to_shared(s_dyn), P.cl_blob, P.cl_bytes, bar);
     }
     mbar_wait(bar, 0u);
-    const ClusterView cv = cluster_view(s_dyn, P.cl_n_top, P.cl_extra_r);
+    const TreeView tv = tree_view(s_dyn, P.cl_n_nodes, P.cl_first_leaf, P.cl_n_entry, P.cl_entry_r, P.cl_stack_cap);
     const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
     if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
         const uint32_t n_batches = (count + 63u) / 64u;
@@ -1353,11 +1357,11 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
             const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
             Lanes L;
             wf_load_rays<2>(P, qin, count, j0, L, rays);
-            trace_clustered<1>(cv, s_note, P.spheres, P.n_spheres, L, exact_tests);
+            trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
             wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
         }
     } else {
-        finish_paths(P, qin, count, cv, s_note, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+        finish_paths(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
     }
     wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
 }
@@ -1633,8 +1637,8 @@ static size_t prim_smem_bytes() {
 static size_t bounce_smem_bytes() {
     return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
 }
-static size_t clustered_smem_bytes(uint32_t image_bytes) {
-    return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(kWfDefer + kWfCand) * kBlockThreads * sizeof(unsigned short);
+static size_t clustered_smem_bytes(uint32_t image_bytes, uint32_t stack_cap) {
+    return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(stack_cap + kWfCand) * kBlockThreads * sizeof(unsigned short);
 }
 
 cudaError_t configure_kernels() {
@@ -1650,10 +1654,10 @@ cudaError_t configure_kernels() {
     e = cudaFuncSetAttribute(bounce_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(bounce_clustered_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax));
+                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(bounce_clustered_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax));
+                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
@@ -1714,12 +1718,12 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (p.cl_n_top == 0u) {
+                if (p.cl_n_nodes == 0u) {
                     bounce_streamed_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
                 } else if (b < finish_from) {
-                    bounce_clustered_kernel<false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes), stream>>>(p);
+                    bounce_clustered_kernel<false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
                 } else {
-                    bounce_clustered_kernel<true><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes), stream>>>(p);
+                    bounce_clustered_kernel<true><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
                 }
                 n_launch += 1;
             }

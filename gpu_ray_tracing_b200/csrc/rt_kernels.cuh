@@ -6,9 +6,6 @@
 
 #include "../../include/rt_abi.h"
 
-#ifndef RT_CLUSTER_SLOTS
-#define RT_CLUSTER_SLOTS 8 /* keep in step with rt_core.cuh */
-#endif
 
 namespace rtk {
 
@@ -28,12 +25,14 @@ constexpr int kPrimListCap = 512;   // records per cull pass of a warp: capacity
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
-constexpr int kClusterSlots = RT_CLUSTER_SLOTS;        // member slots per cluster (rtcl::kSlots)
-constexpr int kClusterStride = kClusterSlots + 1;      // record slots per cluster in the image (rtcl::kStride)
+constexpr int kTreeWide = 8;                           // children per node of the bounce rays' tree (rtt::kWide)
+constexpr int kTreeStride = kTreeWide + 1;             // record slots per node in the image (rtt::kStride)
+constexpr int kTreeBacklog = 16;                       // entry nodes a lane may stack up before the warp traverses
+constexpr uint32_t kTreeStackMax = 64;                 // deepest per-thread node stack the bounce kernel is configured for
 constexpr uint32_t kWfFinishFrom = 3;                   // first bounce whose launch may finish a short queue to the end
 constexpr int kWfChunk = 2048;      // wavefront bounce kernel: general records per stage (32 KB)
 constexpr size_t kClusterImageMax = (size_t)2 * (kWfChunk + 8) * 16;   // the bounce kernel's two record stages
-constexpr int kWfCand = 48;         // per-thread queue of (member, ray) candidates awaiting their exact tests (clustered traversal)
+constexpr int kWfCand = 32;         // per-thread queue of (member, ray) candidates awaiting their exact tests (clustered traversal)
 constexpr int kWfDefer = 24;        // per-thread queue of broad-phase groups awaiting their exact tests
 
 struct UpdateParams {
@@ -55,10 +54,10 @@ struct UpdateParams {
     uint32_t wf_bounce;         // bounce index this launch traces
     float2* first_hit;          // window texels x (t, bits(sphere index)): nearest hit of the primary ray found by
                                 // the primary pass; index -1 = miss, -2 = not traced (the update kernel scans it)
-    // clustered scene image for the bounce rays (rt_cluster.h), built by rt_set_scene; cl_n_top == 0: none
+    // tree image of the scene for the bounce rays (rt_tree.h), built after rt_set_scene; cl_n_nodes == 0: none
     const void* cl_blob;
-    uint32_t cl_n_top, cl_bytes;
-    float cl_extra_r;
+    uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry;
+    float cl_entry_r;
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };
 

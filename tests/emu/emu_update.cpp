@@ -13,7 +13,7 @@
 #endif
 
 #include "../../gpu_ray_tracing_b200/csrc/rt_core.cuh"
-#include "../../gpu_ray_tracing_b200/csrc/rt_cluster.h"
+#include "../../gpu_ray_tracing_b200/csrc/rt_tree.h"
 
 using rtc::f3;
 
@@ -32,8 +32,9 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     if (primary)
         for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);
     // clustered traversal of the bounce rays (rtk::trace_clustered): the wavefront path uses it behind a primary pass
-    rtcl::Clusters cl;
-    const bool clustered = primary && rtcl::build(spheres, count, cl) && cl.bytes() <= (size_t)2 * (2048 + 8) * 16;
+    rtt::Tree tree;
+    const bool clustered = primary && count < 32768u && rtt::build(spheres, count, tree) &&
+                           tree.bytes() <= (size_t)2 * (2048 + 8) * 16 && 16u + 4u + 7u * tree.depth <= 64u;
     uint64_t cluster_rays = 0, cluster_tests = 0, member_tests = 0, retraced = 0;
     uint64_t prim_rays = 0, untraced = 0, tile_pairs = 0, tile_dropped = 0;
     const uint32_t seed_bits_early = rtc::f2u(cam.random_seed * 4294967296.0f);
@@ -128,24 +129,38 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                         }
                     } else if (clustered && i >= 1) {
                         ++cluster_rays;
-                        const float thr2 = rtc::cluster_thr(b.thr, rtc::dot(r.o, r.o), cl.extra_r);
+                        const float m_ray = rtc::cluster_m(rtc::dot(r.o, r.o));
                         std::vector<uint8_t> tested(count, 0);
                         bool nan_root = false;
-                        for (uint32_t c = 0; c < cl.n_top; ++c) {
-                            const float* crec = &cl.top[(size_t)c * 4];
-                            ++cluster_tests;
-                            if (rtc::broad_g(crec[0], crec[1], crec[2], crec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < thr2)
-                                continue;
-                            for (uint32_t u = 0; u < cl.count[c]; ++u) {
-                                const float* mrec = &cl.mem[((size_t)c * rtcl::kStride + u) * 4];
-                                ++member_tests;
-                                if (rtc::broad_g(mrec[0], mrec[1], mrec[2], mrec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < b.thr)
+                        std::vector<uint16_t> stack;
+                        {   // the coherent scan of the entry list
+                            const float t_entry = rtc::cluster_thr(b.thr, m_ray, tree.entry_r);
+                            for (uint32_t e = 0; e < tree.n_entry; ++e) {
+                                const float* rec = &tree.entry_rec[(size_t)e * 4];
+                                ++cluster_tests;
+                                if (!(rtc::broad_g(rec[0], rec[1], rec[2], rec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < t_entry))
+                                    stack.push_back(tree.entry_node[e]);
+                            }
+                        }
+                        while (!stack.empty()) {
+                            const uint32_t node = stack.back();
+                            stack.pop_back();
+                            const bool leaf = node >= tree.first_leaf;
+                            const float t = leaf ? b.thr : rtc::cluster_thr(b.thr, m_ray, tree.node_r[node]);
+                            for (int k = 0; k < rtt::kWide; ++k) {
+                                const float* rec = &tree.rec[((size_t)node * rtt::kStride + k) * 4];
+                                const uint16_t link = tree.link[(size_t)node * rtt::kWide + k];
+                                ++(leaf ? member_tests : cluster_tests);
+                                if (rtc::broad_g(rec[0], rec[1], rec[2], rec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < t) continue;
+                                if (link == rtt::kNone) continue;
+                                if (!leaf) {
+                                    stack.push_back(link);
                                     continue;
-                                const uint32_t s = cl.order[(size_t)c * rtcl::kStride + u];
-                                const GpuSphere& sp = spheres[s];
+                                }
+                                const GpuSphere& sp = spheres[link];
                                 ++exact;
-                                tested[s] = 1;
-                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)s,
+                                tested[link] = 1;
+                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)link,
                                                          &best_t, &best_i))
                                     nan_root = true;
                             }

@@ -30,7 +30,7 @@ def build_emu():
     src = os.path.join(EMU_DIR, "emu_update.cpp")
     out = os.path.join(EMU_DIR, "libemu.so")
     deps = [src, os.path.join(ROOT, "gpu_ray_tracing_b200", "csrc", "rt_core.cuh"),
-            os.path.join(ROOT, "gpu_ray_tracing_b200", "csrc", "rt_cluster.h"),
+            os.path.join(ROOT, "gpu_ray_tracing_b200", "csrc", "rt_tree.h"),
             os.path.join(ROOT, "include", "rt_pinned_math.h"), os.path.join(ROOT, "include", "rt_abi.h")]
     if _newer(deps, out):
         subprocess.run([_CXX, "-std=c++17", "-O2", "-ffp-contract=off", "-fopenmp", "-fPIC", "-shared",
