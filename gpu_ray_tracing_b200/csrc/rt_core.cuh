@@ -198,6 +198,7 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
 // arithmetic: 7 FFMA per (ray, sphere).  Shared by the kernels and the CPU emulation in tests/emu.
 // ---------------------------------------------------------------------------------------------
 #define RT_KAPPA 1.52587890625e-05 /* 2^-16 */
+#define RT_BROAD_MAG 1073741824.0 /* 2^30: |C_i|, |r| window of the general records */
 
 struct BroadRay {
     float ux, uy, uz;     // d / |d|
@@ -225,9 +226,14 @@ RT_DEV float broad_g(float sx, float sy, float sz, float sk, float ux, float uy,
     return fmaf(h, h, -c);
 }
 
-// k = |C|^2 - r^2 - kappa (|C|^2 + r^2), evaluated in binary64 and rounded toward -infinity.
+// k = |C|^2 - r^2 - kappa (|C|^2 + r^2), evaluated in binary64 and rounded toward -infinity.  A sphere outside the
+// magnitude window (any of |C_i|, |r| beyond 2^30, or not finite) gets k = -infinity, which passes for every ray:
+// beyond the window the float test itself would overflow (c = +inf rejects a sphere whose reference discriminant
+// is NaN, i.e. a hit), and the reference's arithmetic is no longer covered by the kappa bound anyway.
 RT_DEV float broad_record_k(const GpuSphere& s) {
     const double cx = s.position.x, cy = s.position.y, cz = s.position.z, r = s.radius;
+    if (!(fabs(cx) <= RT_BROAD_MAG && fabs(cy) <= RT_BROAD_MAG && fabs(cz) <= RT_BROAD_MAG && fabs(r) <= RT_BROAD_MAG))
+        return -INFINITY;
     const double cc = cx * cx + cy * cy + cz * cz, rr = r * r;
     const double k = cc - rr - RT_KAPPA * (cc + rr);
     float f = (float)k;

@@ -209,9 +209,9 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     const double lim = 1073741824.0;   // 2^30, the magnitude window of the bound
     std::vector<uint32_t> bounded, always;
     for (uint32_t i = 0; i < n; ++i) {
-        const double m = std::max(std::max(std::fabs((double)s[i].position.x), std::fabs((double)s[i].position.y)),
-                                  std::max(std::fabs((double)s[i].position.z), std::fabs((double)s[i].radius)));
-        if (m <= lim) bounded.push_back(i);   // false for NaN
+        const bool in_window = std::fabs((double)s[i].position.x) <= lim && std::fabs((double)s[i].position.y) <= lim &&
+                               std::fabs((double)s[i].position.z) <= lim && std::fabs((double)s[i].radius) <= lim;
+        if (in_window) bounded.push_back(i);   // false for NaN
         else always.push_back(i);
     }
     if (!bounded.empty()) {

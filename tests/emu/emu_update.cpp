@@ -169,7 +169,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                             float root;
                             if (!tested[s] && rtc::sphere_root(r.o, r.d, a, rtc::mk(spheres[s].position), spheres[s].radius, 0.001f,
                                                                3.4e35f, &root))
-                                ++violations;   // the clusters skipped a sphere the reference hits
+                                ++violations;   // the tree skipped a sphere the reference hits
                         }
                         if (nan_root) {   // order matters once a root is NaN: the reference loop itself
                             ++retraced;

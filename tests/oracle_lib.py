@@ -133,3 +133,8 @@ def compare_images(a, b):
     return {"bit_identical": same_bits, "max_abs": max_abs,
             "pixels_over_1_255": int((dq > 1).sum()), "pixels_differing": int((dq > 0).sum()),
             "pixels": int(dq.size)}
+
+
+def nan_aware_equal(a, b):
+    return np.array_equal(a.view(np.uint32)[~np.isnan(a)], b.view(np.uint32)[~np.isnan(a)]) and \
+        np.array_equal(np.isnan(a), np.isnan(b))

@@ -154,3 +154,36 @@ def test_primary_records_are_conservative_by_construction():
             lib.emu_primary_record(C.byref(cam), sp[i:i + 1].ctypes.data_as(C.c_void_p), rec[i].ctypes.data_as(C.c_void_p))
         assert tuple(rec[0]) == (0.0, 0.0, 0.0, 1.0) and tuple(rec[1]) == (0.0, 0.0, 0.0, 1.0)
         assert rec[2][3] < 0.0 and abs(-rec[2][3] - np.sqrt(50.0 ** 2 - (1.0 + rho) ** 2)) < 0.02
+
+
+def test_degenerate_spheres_follow_the_reference_loop():
+    """NaN roots make sphere_list_hit order dependent; the tree traversal must notice and retrace such rays in index
+    order, and no bound may hide a sphere whose reference arithmetic goes non-finite."""
+    scene = scenes.degenerate_scene()
+    W, H = 64, 36
+    for depth in (1, 5):
+        cam = scenes.camera(W, H, max_depth=depth, spp=500, look_from=(9.0, 1.5, 2.0), fov=50.0)
+        cpu, rays = ol.oracle_update(cam, scene, W, H)
+        for variant in (0, 2):
+            emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=variant)
+            assert violations == 0 and rays == rays_e, (depth, variant, violations)
+            assert ol.nan_aware_equal(cpu, emu), (depth, variant)
+    cam = scenes.camera(W, H, max_depth=5, spp=500, look_from=(9.0, 1.5, 2.0), fov=50.0)
+    ol.emu_update(cam, scene, W, H, variant=0)
+    assert ol.EMU_STATS["cluster_rays"] > 0 and ol.EMU_STATS["retraced"] > 0
+
+
+def test_tree_culls_bounce_rays():
+    """The bounding-sphere tree: a bounce ray of the 1024-sphere scene tests a small part of the scene, no ray is
+    retraced, nothing is missed."""
+    W, H = 128, 72
+    scene = scenes.random_scene(1024)
+    cam = scenes.camera(W, H, max_depth=8, spp=500)
+    cpu, rays = ol.oracle_update(cam, scene, W, H)
+    emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=0)
+    st = dict(ol.EMU_STATS)
+    per_ray = (st["cluster_tests"] + st["member_tests"]) / st["cluster_rays"]
+    print("tree: %.1f record tests per bounce ray of %d spheres" % (per_ray, scene.count), st)
+    assert violations == 0 and rays == rays_e and st["retraced"] == 0
+    assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))
+    assert per_ray < 0.3 * scene.count

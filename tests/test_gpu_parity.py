@@ -265,3 +265,30 @@ def test_scripted_flythrough_frames():
             assert_parity(gpu, cpu, f"fly-through frame {f}")
             assert gpu[..., 3].max() == (1.0 if cam.camera_has_moved else gpu[..., 3].max())
         assert cpu[..., 3].max() == 2.0     # frames 5, 6: one moved frame then one idle frame
+
+
+@pytest.mark.parametrize("variant", [0, 2, 3])
+def test_degenerate_spheres_on_device(variant):
+    """NaN / infinite / out-of-window spheres next to ordinary ones: every kernel family must follow the reference
+    loop, including its order-dependent behaviour once a root is NaN (tree traversal: sequential retrace)."""
+    scene = scenes.degenerate_scene()
+    W, H = 64, 36
+    for depth in (1, 5):
+        cam = scenes.camera(W, H, max_depth=depth, spp=500, look_from=(9.0, 1.5, 2.0), fov=50.0)
+        cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+        gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H, variant)
+        assert rays_gpu == rays_cpu
+        assert ol.nan_aware_equal(cpu, gpu), (variant, depth)
+
+
+def test_tree_sizes_and_streamed_fallback():
+    """Bounce rays through trees of different depths (8 ... 3,000 spheres) and, past the shared-memory budget of the
+    tree image, through the streamed kernel; the counters of both paths agree with the oracle's ray count."""
+    W, H = 192, 108
+    for n in (8, 9, 64, 65, 500, 3000, 6000):
+        scene = scenes.random_scene(n)
+        cam = scenes.camera(W, H, max_depth=5, spp=500)
+        cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
+        gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
+        assert rays_gpu == rays_cpu, n
+        assert_parity(gpu, cpu, f"random {n} depth 5")
