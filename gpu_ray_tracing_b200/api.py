@@ -123,6 +123,11 @@ _SIGNATURES = {
     "rt_read_rgba8_async": (C.c_int, [_P, _P]),
     "rt_wavefront_counts": (C.c_int, [_P, _P, C.c_uint32, _P]),
     "rt_read_wait": (C.c_int, [_P]),
+    "rt_device_alloc": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(_P)]),
+    "rt_device_free": (C.c_int, [C.c_int, _P]),
+    "rt_ipc_export": (C.c_int, [C.c_int, _P, _P]),
+    "rt_ipc_open": (C.c_int, [C.c_int, _P, C.POINTER(_P)]),
+    "rt_ipc_close": (C.c_int, [C.c_int, _P]),
     "rt_rays_traced": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "rt_exact_tests": (C.c_int, [_P, C.POINTER(C.c_uint64)]),
     "rt_reset_counters": (C.c_int, [_P]),
@@ -226,6 +231,33 @@ def create_grid_spheres(n: int, seed: int = 4321) -> SphereCollection:
     buf = np.zeros(n, dtype=SPHERE_DTYPE)
     _check(lib().rt_create_grid_spheres(seed, n, _ptr(buf)))
     return SphereCollection(buf, n)
+
+
+def device_alloc(device: int, nbytes: int) -> int:
+    p = _P()
+    _check(lib().rt_device_alloc(device, nbytes, C.byref(p)))
+    return p.value
+
+
+def device_free(device: int, ptr: int) -> None:
+    _check(lib().rt_device_free(device, ptr))
+
+
+def ipc_export(device: int, ptr: int) -> bytes:
+    h = (C.c_uint8 * 64)()
+    _check(lib().rt_ipc_export(device, ptr, h))
+    return bytes(h)
+
+
+def ipc_open(device: int, handle: bytes) -> int:
+    h = (C.c_uint8 * 64).from_buffer_copy(handle)
+    p = _P()
+    _check(lib().rt_ipc_open(device, h, C.byref(p)))
+    return p.value
+
+
+def ipc_close(device: int, ptr: int) -> None:
+    _check(lib().rt_ipc_close(device, ptr))
 
 
 def orbit_camera(k: int, n: int, width: int, height: int, radius: float = 60.0, cam_height: float = 9.0,

@@ -333,7 +333,8 @@ int rt_read_rgba8_async(RtRenderer* r, uint8_t* host) {
     r->launches += 1;
     RT_CUDA(cudaEventRecord(r->ev_quantized[b], r->stream));
     RT_CUDA(cudaStreamWaitEvent(r->copy_stream, r->ev_quantized[b], 0));
-    RT_CUDA(cudaMemcpyAsync(host, dev, r->n_texels * sizeof(uchar4), cudaMemcpyDeviceToHost, r->copy_stream));
+    // cudaMemcpyDefault: the destination may be pinned host memory or device memory of this or a peer GPU
+    RT_CUDA(cudaMemcpyAsync(host, dev, r->n_texels * sizeof(uchar4), cudaMemcpyDefault, r->copy_stream));
     RT_CUDA(cudaEventRecord(r->ev_copied[b], r->copy_stream));
     r->async_reads += 1;
     return RT_OK;
@@ -342,6 +343,43 @@ int rt_read_rgba8_async(RtRenderer* r, uint8_t* host) {
 int rt_read_wait(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
     RT_CUDA(cudaStreamSynchronize(r->copy_stream));
+    return RT_OK;
+}
+
+// Device buffers other processes can write into: the gather target of a multi-process run (bench.py) lives in one
+// process and is mapped by the others through CUDA IPC, so that rt_read_rgba8_async can copy a finished frame
+// straight into it over NVLink.
+int rt_device_alloc(int device, uint64_t bytes, void** out) {
+    if (!out || bytes == 0) return fail(RT_ERR_INVALID_ARG, "null output or zero size");
+    RT_CUDA(cudaSetDevice(device));
+    RT_CUDA(cudaMalloc(out, (size_t)bytes));
+    return RT_OK;
+}
+int rt_device_free(int device, void* ptr) {
+    RT_CUDA(cudaSetDevice(device));
+    RT_CUDA(cudaFree(ptr));
+    return RT_OK;
+}
+int rt_ipc_export(int device, void* ptr, uint8_t handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+    if (!ptr || !handle) return fail(RT_ERR_INVALID_ARG, "null argument");
+    RT_CUDA(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    RT_CUDA(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(handle, &h, 64);
+    return RT_OK;
+}
+int rt_ipc_open(int device, const uint8_t handle[64], void** out) {
+    if (!handle || !out) return fail(RT_ERR_INVALID_ARG, "null argument");
+    RT_CUDA(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    RT_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return RT_OK;
+}
+int rt_ipc_close(int device, void* ptr) {
+    RT_CUDA(cudaSetDevice(device));
+    RT_CUDA(cudaIpcCloseMemHandle(ptr));
     return RT_OK;
 }
 

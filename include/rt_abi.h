@@ -164,6 +164,16 @@ RT_API int rt_read_rgba8(RtRenderer* r, uint8_t* host_rgba8);
  * first on the device. */
 RT_API int rt_read_rgba8_async(RtRenderer* r, uint8_t* host_rgba8);
 RT_API int rt_read_wait(RtRenderer* r);   /* every asynchronous read issued so far has landed */
+/* Device buffers that other processes can write into.  A multi-process run (one process per GPU) keeps its gather
+ * target in one process (rt_device_alloc + rt_ipc_export), the others map it (rt_ipc_open, peer access enabled
+ * lazily) and hand the mapped address to rt_read_rgba8_async, whose destination may be pinned host memory or device
+ * memory of this or a peer GPU: the finished frame then travels by one peer copy over NVLink, the analogue of the
+ * "final image is gathered by peer copy" step for frames sharded over processes. */
+RT_API int rt_device_alloc(int device, uint64_t bytes, void** ptr);
+RT_API int rt_device_free(int device, void* ptr);
+RT_API int rt_ipc_export(int device, void* ptr, uint8_t handle[64]);
+RT_API int rt_ipc_open(int device, const uint8_t handle[64], void** ptr);
+RT_API int rt_ipc_close(int device, void* ptr);
 
 /* Number of sphere_list_hit traversals (compute_shader.wgsl:266) executed since the last
  * rt_reset_counters: the "rays" of the Mrays/s metric. */
