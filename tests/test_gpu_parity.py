@@ -292,3 +292,31 @@ def test_tree_sizes_and_streamed_fallback():
         gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
         assert rays_gpu == rays_cpu, n
         assert_parity(gpu, cpu, f"random {n} depth 5")
+
+
+def test_async_read_into_device_memory():
+    """rt_read_rgba8_async with a DEVICE destination (what a peer process maps through CUDA IPC in bench.py --gpus N):
+    the copy lands in a buffer from rt_device_alloc and equals the blocking host read."""
+    import torch
+    W, H = 320, 180
+    scene, cam = scenes.default_scene(), scenes.camera(W, H, max_depth=3, spp=4)
+    nbytes = W * H * 4
+    dst = rt.device_alloc(0, 2 * nbytes)
+    try:
+        handle = rt.ipc_export(0, dst)
+        assert len(handle) == 64 and any(handle)
+        with rt.Renderer(W, H) as r:
+            r.set_scene(scene)
+            r.init()
+            r.update(cam)
+            r.read_rgba8_async_into(dst + nbytes)          # second slot of the buffer
+            want = r.read_rgba8()
+            r.read_wait()
+            # bring the device copy back through torch (same device, raw pointer wrapped by a pinned host read)
+            host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+            from cuda.bindings import runtime as cudart
+            err, = cudart.cudaMemcpy(host.data_ptr(), dst + nbytes, nbytes, cudart.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+            assert int(err) == 0
+            assert np.array_equal(host.numpy().reshape(H, W, 4), want)
+    finally:
+        rt.device_free(0, dst)
