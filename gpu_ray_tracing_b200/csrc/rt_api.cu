@@ -136,7 +136,7 @@ int rt_destroy(RtRenderer* r) {
     cudaFree(r->rgba8);
     cudaFree(r->spheres);
     cudaFree(r->geom);
-    cudaFree(r->prim);
+    cudaFree(r->prim_tree);
     cudaFree(r->first_hit);
     cudaFree(r->wf_queue[0]);
     cudaFree(r->wf_queue[1]);
@@ -163,19 +163,25 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
         RT_CUDA(cudaStreamSynchronize(r->stream));
         cudaFree(r->spheres); r->spheres = nullptr; r->sphere_capacity = 0;
         cudaFree(r->geom); r->geom = nullptr; r->geom_capacity = 0;
-        cudaFree(r->prim); r->prim = nullptr;
         RT_CUDA(cudaMalloc(&r->spheres, (size_t)cap_needed * sizeof(GpuSphere)));
         r->sphere_capacity = cap_needed;
         RT_CUDA(cudaMalloc(&r->geom, (size_t)pad_needed * sizeof(float4)));
-        RT_CUDA(cudaMalloc(&r->prim, (size_t)pad_needed * sizeof(float4)));
         r->geom_capacity = pad_needed;
     }
     if (buffer_len > 0)
         RT_CUDA(cudaMemcpyAsync(r->spheres, spheres, (size_t)buffer_len * sizeof(GpuSphere), cudaMemcpyHostToDevice, r->stream));
     r->n_spheres = count;
-    r->host_spheres.assign(spheres, spheres + count);   // for the lazily built clusters of the bounce rays
-    r->clusters_stale = true;
-    r->cl_n_nodes = 0;
+    // The tree of bounding spheres (rt_tree.h) is built on the host from a copy of the list, on the next update that
+    // needs it; an upload of the same bytes (the reference re-creates its buffers every frame, src/lib.rs:177-207)
+    // keeps the tree it has.
+    const bool same = r->host_spheres.size() == count &&
+                      (count == 0 || memcmp(r->host_spheres.data(), spheres, (size_t)count * sizeof(GpuSphere)) == 0);
+    if (!same) {
+        r->host_spheres.assign(spheres, spheres + count);
+        r->clusters_stale = true;
+        r->cl_n_nodes = 0;
+        r->cl_bytes = 0;
+    }
     RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
     r->launches += 1;
     // the source is borrowed for the call only (pageable memory: the copy above has been staged,
@@ -204,27 +210,22 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
     p.tile_counter = r->tile_counter;
     p.counters = r->counters;
-    p.prim = r->prim;
     p.first_hit = r->first_hit;
-    if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant == 4)) {
-        // first deep frame: path queues for the wavefront bounces (two queues x three float4 planes)
-        for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
-        RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
-    }
-    if (camera->max_depth > 1.0f && r->clusters_stale && r->wf_counts) {
-        // first deep frame of this scene: the tree of bounding spheres for the bounce rays (skipped when its image
-        // would not fit the bounce kernel's shared memory; that kernel then streams the plain records instead)
+    if (r->clusters_stale && (r->variant == 0 || r->variant == 4) && r->n_spheres > 0) {
+        // first update of this scene that can use the primary pass: the tree of bounding spheres, kept in global
+        // memory for the primary pass; the bounce kernel copies its image into shared memory when it fits there
         r->clusters_stale = false;
         rtt::Tree tree;
-        const bool built = rtt::build(r->host_spheres.data(), r->n_spheres, tree);
-        // per-thread node stack: the entry backlog, 4 more entries, and 7 per level of depth-first growth below them
-        const uint32_t stack_cap = built ? (uint32_t)rtk::kTreeBacklog + 4u + 7u * tree.depth : 0u;
-        if (built && r->n_spheres < 32768u && tree.bytes() <= rtk::kClusterImageMax && stack_cap <= rtk::kTreeStackMax) {
-            if (tree.bytes() > r->cl_capacity) {
+        if (rtt::build(r->host_spheres.data(), r->n_spheres, tree)) {
+            const size_t rec_bytes = ((size_t)tree.n_nodes * rtk::kTreeStride + tree.n_entry_pad) * sizeof(float4);
+            if (tree.bytes() > r->cl_capacity || rec_bytes > r->prim_tree_capacity) {
                 RT_CUDA(cudaStreamSynchronize(r->stream));
                 cudaFree(r->cl_blob); r->cl_blob = nullptr; r->cl_capacity = 0;
+                cudaFree(r->prim_tree); r->prim_tree = nullptr; r->prim_tree_capacity = 0;
                 RT_CUDA(cudaMalloc(&r->cl_blob, tree.bytes()));
                 r->cl_capacity = tree.bytes();
+                RT_CUDA(cudaMalloc(&r->prim_tree, rec_bytes));
+                r->prim_tree_capacity = rec_bytes;
             }
             std::vector<unsigned char> image(tree.bytes());
             tree.pack(image.data());
@@ -232,12 +233,17 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
             RT_CUDA(cudaStreamSynchronize(r->stream));   // `image` is about to go away
             r->cl_n_nodes = tree.n_nodes;
             r->cl_first_leaf = tree.first_leaf;
-            r->cl_bytes = (uint32_t)tree.bytes();
-            r->cl_stack_cap = stack_cap;
             r->cl_n_entry = tree.n_entry;
             r->cl_entry_r = tree.entry_r;
+            // per-thread node stack of the bounce kernel: the entry backlog, 4 more entries, and 7 per level of
+            // depth-first growth below them
+            r->cl_stack_cap = (uint32_t)rtk::kTreeBacklog + 4u + 7u * tree.depth;
+            const bool fits = r->n_spheres < 32768u && tree.n_nodes < 65536u && tree.bounce_bytes() <= rtk::kClusterImageMax &&
+                              r->cl_stack_cap <= rtk::kTreeStackMax;
+            r->cl_bytes = fits ? (uint32_t)tree.bounce_bytes() : 0u;
         }
     }
+    p.prim_tree = r->cl_n_nodes ? r->prim_tree : nullptr;
     p.cl_blob = r->cl_blob;
     p.cl_n_nodes = r->cl_n_nodes;
     p.cl_first_leaf = r->cl_first_leaf;
@@ -245,6 +251,11 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.cl_stack_cap = r->cl_stack_cap;
     p.cl_n_entry = r->cl_n_entry;
     p.cl_entry_r = r->cl_entry_r;
+    if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant == 4)) {
+        // first deep frame: path queues for the wavefront bounces (two queues x three float4 planes)
+        for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
+        RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
+    }
     p.wf_queue[0] = r->wf_queue[0];
     p.wf_queue[1] = r->wf_queue[1];
     p.wf_counts = r->wf_counts;

@@ -354,6 +354,25 @@ RT_DEV bool primary_candidate(float h) {
 // added to the left side — each several times the error it covers — so the tile test keeps every record that any
 // per-ray test of the tile keeps: the set of exact tests, and with it the result, is unchanged.
 // ---------------------------------------------------------------------------------------------
+// The camera's share of a group's bounding radius in the primary pass over the tree (rt_tree.h): every member's
+// inflated sphere (radius sqrt(r^2 + kappa S) + rho, S <= (|C| + |Oc| + r + rho)^2) must lie inside the group's, whose
+// stored radius covers the |C| and r terms; m_cam = 2^-7 (|Oc| + rho), rounded up, covers the rest twice over.
+RT_DEV float primary_m_cam(const SceneCamera& cam, double rho) {
+    const double cx = cam.center.x, cy = cam.center.y, cz = cam.center.z;
+    const double m = 0.0078125 * (sqrt(cx * cx + cy * cy + cz * cz) + rho) * (1.0 + 0.0009765625);
+    float f = (float)m;
+    if ((double)f < m) f = nextafterf(f, INFINITY);
+    return f;
+}
+// Record of a group of the tree for this frame: bounding sphere (centre, radius + m_cam) through primary_record.
+RT_DEV void primary_group_record(float cx, float cy, float cz, float radius, float m_cam, f3 o, double rho, float out[4]) {
+    GpuSphere g;
+    g.position.x = cx; g.position.y = cy; g.position.z = cz;
+    g.radius = radius + m_cam;
+    g.color[0] = 0.0f; g.color[1] = 0.0f; g.color[2] = 0.0f; g.color[3] = 0.0f;
+    primary_record(g, o, rho, out);
+}
+
 // Axis of a tile from the bounding box [lo, hi] of its rays' unit directions.
 RT_DEV f3 primary_tile_axis(f3 lo, f3 hi) {
     const f3 m = mk(0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z));

@@ -19,7 +19,8 @@ struct RtRenderer {
     uint32_t sphere_capacity = 0;
     float4* geom = nullptr;               // broad-phase records
     uint32_t geom_capacity = 0;
-    float4* prim = nullptr;               // per-frame common-origin records (same padded length as geom)
+    float4* prim_tree = nullptr;          // per-frame common-origin records of the tree's child slots
+    size_t prim_tree_capacity = 0;
     float2* first_hit = nullptr;          // (t, sphere index) per texel, written by the primary pass
     float4* wf_queue[2] = {nullptr, nullptr};   // wavefront path queues (3 planes of n_texels float4 each), on first deep frame
     unsigned int* wf_counts = nullptr;

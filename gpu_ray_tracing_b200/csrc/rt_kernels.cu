@@ -398,35 +398,40 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
 // ---------------------------------------------------------------------------------------------
 namespace {
 
-constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, then (best_t, best_i) for the fused epilogue
+constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, nearest hit (best_t, best_i)
 
 struct PrimLanes {
     float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
-    float best_t[kPrimRays];
-    int best_i[kPrimRays];
     uint32_t alive;   // bit p: ray p is traced here
 };
 
 __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
 
-// Exact tests (the reference quadratic, shrinking t_max) of sphere `idx` for the rays in `cand`.
-__device__ __forceinline__ void prim_exact(uint32_t cand, int idx, const float* __restrict__ s_d, const UpdateParams& P,
-                                           PrimLanes& L, uint32_t& exact_tests) {
+// Exact tests (the reference quadratic) of sphere `idx` for the rays in `cand`.  The tree hands the spheres over in
+// no particular order, so the nearest hit is kept with rtc::nearest_update (ties to the lower index); a ray that
+// meets a NaN root is handed to the sequential fallback (`untraced`), where the reference's order decides.
+__device__ __forceinline__ void prim_exact(uint32_t cand, int idx, float* __restrict__ s_d, const UpdateParams& P,
+                                           PrimLanes& L, uint32_t& untraced, uint32_t& exact_tests) {
     const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
     const f3 center = rtc::mk(g.x, g.y, g.z);
-#pragma unroll
-    for (int p = 0; p < kPrimRays; ++p) {
-        if (cand & (1u << p)) {
-            ++exact_tests;
-            const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-            const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
-            const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
-            float root;
-            if (rtc::sphere_root(origin, d, rtc::dot(d, d), center, g.w, kTMin, L.best_t[p], &root)) {
-                L.best_t[p] = root;
-                L.best_i[p] = idx;
-            }
+    // one rolled copy of the quadratic for all eight rays (ray state lives in the thread's shared-memory slots):
+    // the kernel's instruction footprint, not its instruction count, is what the profile shows to matter
+#pragma unroll 1
+    while (cand) {
+        const int p = __ffs((int)cand) - 1;
+        cand &= cand - 1u;
+        ++exact_tests;
+        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+        const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+        const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
+        float bt = dp[6 * kBlockThreads];
+        int bi = __float_as_int(dp[7 * kBlockThreads]);
+        if (!rtc::nearest_update(origin, d, rtc::dot(d, d), center, g.w, kTMin, kTMax, idx, &bt, &bi)) {
+            untraced |= 1u << p;
+            L.alive &= ~(1u << p);
         }
+        dp[6 * kBlockThreads] = bt;
+        dp[7 * kBlockThreads] = __int_as_float(bi);
     }
 }
 
@@ -451,25 +456,29 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
                 L.alive |= 1u << p;
             }
         }
-        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-        dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
-        dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
-    }
-#pragma unroll
-    for (int p = 0; p < kPrimRays; ++p) {
-        const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-        const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
+        // unit direction of the common-origin test (rtc::primary_arm), here in the rolled loop: parked in the slots
+        // of the nearest hit, which are initialised when the directions are picked up below
         float ux, uy, uz;
         const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
         if (!ok && (L.alive & (1u << p))) {
             untraced |= 1u << p;
             L.alive &= ~(1u << p);
         }
+        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+        dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
+        dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
+        dp[6 * kBlockThreads] = ux; dp[7 * kBlockThreads] = uy;
+        s_d[(kPrimRays * kPrimSlots + p) * kBlockThreads] = uz;
+    }
+#pragma unroll
+    for (int p = 0; p < kPrimRays; ++p) {
+        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+        const float ux = dp[6 * kBlockThreads], uy = dp[7 * kBlockThreads], uz = s_d[(kPrimRays * kPrimSlots + p) * kBlockThreads];
         const int q = p >> 1;
         if (p & 1) { L.ux[q].y = ux; L.uy[q].y = uy; L.uz[q].y = uz; }
         else       { L.ux[q].x = ux; L.uy[q].x = uy; L.uz[q].x = uz; }
-        L.best_t[p] = kTMax;
-        L.best_i[p] = -1;
+        dp[6 * kBlockThreads] = kTMax;
+        dp[7 * kBlockThreads] = __int_as_float(-1);
     }
 }
 
@@ -505,62 +514,110 @@ __device__ __forceinline__ void prim_tile_bound(const PrimLanes& L, f3& m, float
     chord = rtc::primary_tile_chord(e2);
 }
 
-// Two-level broad phase over `count` records at s_rec (global sphere index of slot 0 = index0).
-//   cull: the warp's lanes test 32 records at a time against the TILE (primary_tile_candidate) and compact the
-//         survivors' slots, in ascending order, into the warp's list (kPrimListCap records per pass);
-//   scan: every lane runs the per-ray sign test (3 FFMA per ray, as FFMA2 pairs) on the listed records only, the
-//         next one prefetched, and puts its candidates through the exact test.
-// A 32 x 8 pixel tile of a 4K frame keeps about 6 of 1024 records, so the scan that used to be the whole cost of the
-// pass is now a small part of it; index order, and with it the reference's tie and NaN behaviour, is preserved.
-__device__ __forceinline__ void prim_cull_scan(const float4* __restrict__ s_rec, int count, int index0,
-                                               unsigned short* __restrict__ s_list, f3 m, float chord,
-                                               const float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
-                                               uint32_t& exact_tests, int lane) {
+// The warp's tile against the tree of bounding spheres (rt_tree.h) with this frame's common-origin records
+// (P.prim_tree, one per child slot, written by prep_primary_tree_kernel).
+//   walk: the warp takes up to 4 nodes from its work stack, every lane tests ONE child record against the TILE
+//         (primary_tile_candidate); surviving nodes go back on the stack, surviving spheres (children of leaf nodes)
+//         into the warp's candidate list (ballot + popc compaction);
+//   scan: every lane runs the per-ray sign test (3 FFMA per ray, as FFMA2 pairs) on the listed records, the next one
+//         prefetched, and puts its candidates through the exact test.
+// A 32 x 8 pixel tile of a 4K frame ends up with about 6 of 1024 spheres after ~10 warp steps; the work grows with the
+// logarithm of the scene.  Records come straight from global memory (L1/L2): a tile touches a few hundred bytes.
+struct PrimTree {
+    const float4* rec;           // this frame's records, kTreeStride slots per node
+    const uint32_t* link;        // kTreeWide per node
+    const uint32_t* entry_node;  // the entry list (rt_tree.h): nodes ...
+    const float4* entry_rec;     // ... and this frame's records of them, contiguous (behind the child slots)
+    uint32_t first_leaf, n_entry;
+};
+
+__device__ __forceinline__ void prim_scan_list(const float4* __restrict__ s_rec, const uint32_t* __restrict__ s_idx, int n_list,
+                                               float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
+                                               uint32_t& untraced, uint32_t& exact_tests) {
+    if (n_list == 0) return;
+    float4 rec = s_rec[0];
 #pragma unroll 1
-    for (int base = 0; base < count; base += kPrimListCap) {
-        const int n = min(kPrimListCap, count - base);
-        int n_list = 0;
+    for (int e = 0; e < n_list; ++e) {
+        const float4 recn = s_rec[e + 1];   // (one readable slot past the list)
+        const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
+                     sw = make_float2(rec.w, rec.w);
+        float2 h[kPrimRays / 2];
+        int acc = -1;   // AND of the rays' sign bits
+#pragma unroll
+        for (int q = 0; q < kPrimRays / 2; ++q) {
+            h[q] = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
+            acc &= __float_as_int(h[q].x) & __float_as_int(h[q].y);
+        }
+        if (acc >= 0) {
+            uint32_t cand = 0;
+#pragma unroll
+            for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
+            cand &= L.alive;
+            if (cand) prim_exact(cand, (int)s_idx[e], s_d, P, L, untraced, exact_tests);
+        }
+        rec = recn;
+    }
+}
+
+__device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __restrict__ s_work, float4* __restrict__ s_rec,
+                                               uint32_t* __restrict__ s_idx, f3 m, float chord, float* __restrict__ s_d,
+                                               const UpdateParams& P, PrimLanes& L, uint32_t& untraced, uint32_t& exact_tests,
+                                               int lane) {
+    const unsigned lt = (1u << lane) - 1u;
+    int n_work = 0, n_list = 0;
+    // the entry list first: independent iterations, 32 records per step, instead of a walk down from the root whose
+    // every step waits for the one before
 #pragma unroll 1
-        for (int j0 = 0; j0 < n; j0 += 32) {
-            const int j = j0 + lane;
-            bool keep = false;
-            if (j < n) {
-                const float4 r = s_rec[base + j];
+    for (uint32_t e0 = 0; e0 < T.n_entry; e0 += 32u) {
+        const uint32_t e = e0 + (uint32_t)lane;
+        bool keep = false;
+        uint32_t node = 0;
+        if (e < T.n_entry) {
+            node = T.entry_node[e];
+            const float4 r = __ldg(T.entry_rec + e);
+            keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord);
+        }
+        const unsigned b = __ballot_sync(kFull, keep);
+        if (keep) s_work[n_work + __popc(b & lt)] = node;
+        n_work += __popc(b);
+    }
+    __syncwarp();
+    while (n_work > 0) {
+        // a nearly full stack is worked off one node at a time (at most 7 entries of growth per level below it)
+        const int take = n_work > kPrimWork - 64 ? 1 : min(n_work, 4);
+        n_work -= take;
+        const int g = lane >> 3, k = lane & 7;
+        bool keep = false, leaf = false;
+        uint32_t lk = 0xFFFFFFFFu;
+        float4 r = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        if (g < take) {
+            const uint32_t node = s_work[n_work + g];
+            lk = T.link[node * kTreeWide + k];
+            leaf = node >= T.first_leaf;
+            if (lk != 0xFFFFFFFFu) {
+                r = __ldg(T.rec + node * kTreeStride + k);
                 keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord);
             }
-            const unsigned b = __ballot_sync(kFull, keep);
-            if (keep) s_list[n_list + __popc(b & ((1u << lane) - 1u))] = (unsigned short)(base + j);
-            n_list += __popc(b);
         }
-        if (lane == 0) s_list[n_list] = (unsigned short)base;   // the prefetch of the last iteration reads one entry further
+        __syncwarp();   // the taken entries have been read before their slots are reused
+        const unsigned bi = __ballot_sync(kFull, keep && !leaf), bl = __ballot_sync(kFull, keep && leaf);
+        if (keep && !leaf) s_work[n_work + __popc(bi & lt)] = lk;
+        n_work += __popc(bi);
+        if (keep && leaf) {
+            const int j = n_list + __popc(bl & lt);
+            s_rec[j] = r;   // the sphere's record travels with it: the scan reads shared memory only
+            s_idx[j] = lk;
+        }
+        n_list += __popc(bl);
         __syncwarp();
-        int j = s_list[0];
-        float4 rec = s_rec[j];
-#pragma unroll 1
-        for (int e = 0; e < n_list; ++e) {
-            const int jn = s_list[e + 1];
-            const float4 recn = s_rec[jn];
-            const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
-                         sw = make_float2(rec.w, rec.w);
-            float2 h[kPrimRays / 2];
-            int acc = -1;   // AND of the rays' sign bits
-#pragma unroll
-            for (int q = 0; q < kPrimRays / 2; ++q) {
-                h[q] = __ffma2_rn(sx, L.ux[q], __ffma2_rn(sy, L.uy[q], __ffma2_rn(sz, L.uz[q], sw)));
-                acc &= __float_as_int(h[q].x) & __float_as_int(h[q].y);
-            }
-            if (acc >= 0) {
-                uint32_t cand = 0;
-#pragma unroll
-                for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
-                cand &= L.alive;
-                if (cand) prim_exact(cand, index0 + j, s_d, P, L, exact_tests);
-            }
-            j = jn;
-            rec = recn;
+        if (n_list > kPrimList - 32) {   // no room for another step's spheres: scan what is listed
+            prim_scan_list(s_rec, s_idx, n_list, s_d, P, L, untraced, exact_tests);
+            n_list = 0;
+            __syncwarp();
         }
-        __syncwarp();   // the list is rewritten by the next pass
     }
+    prim_scan_list(s_rec, s_idx, n_list, s_d, P, L, untraced, exact_tests);
+    __syncwarp();   // the lists are rewritten by the next tile
 }
 
 // kShade = false: write (t, index) per texel to P.first_hit; the update kernel shades and continues the paths.
@@ -577,18 +634,13 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         for (int p = 0; p < kPrimRays; ++p) {
             const int row = row0 + p;
             if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                const int code = (untraced & (1u << p)) ? -2 : L.best_i[p];
-                P.first_hit[(size_t)row * P.width + x] = make_float2(L.best_t[p], __int_as_float(code));
+                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+                const float code = (untraced & (1u << p)) ? __int_as_float(-2) : dp[7 * kBlockThreads];
+                P.first_hit[(size_t)row * P.width + x] = make_float2(dp[6 * kBlockThreads], code);
             }
         }
     } else {
-        // fused epilogue: park the hits next to the rays, then one rolled pass over the strip
-#pragma unroll
-        for (int p = 0; p < kPrimRays; ++p) {
-            float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-            dp[6 * kBlockThreads] = L.best_t[p];
-            dp[7 * kBlockThreads] = __int_as_float(L.best_i[p]);
-        }
+        // fused epilogue: one rolled pass over the strip (rays and their nearest hits are in the slots)
         const uint32_t sampling = L.alive | untraced;
 #pragma unroll 1
         for (int p = 0; p < kPrimRays; ++p) {
@@ -653,11 +705,7 @@ __device__ __forceinline__ void prim_flush(const UpdateParams& P, uint32_t exact
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
-// Scenes of any size: the records stream through two shared-memory stages of kPrimChunk records, filled
-// by 1-D bulk copies (cp.async.bulk, one elected thread) that signal an mbarrier per stage.  A CTA owns 8
-// warp tiles for one pass over the scene; chunk c + 2 is requested as soon as every warp has left chunk c,
-// so the copy of the next chunk always overlaps the scan of the current one.  Nearest-hit state stays in
-// registers across chunks: index order, and with it the reference's tie rule, is preserved.
+// Bulk copies into shared memory (cp.async.bulk + mbarrier), used by the bounce kernels below.
 // ---------------------------------------------------------------------------------------------
 namespace {
 
@@ -685,102 +733,60 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 
 }  // namespace
 
+// One kernel for any scene size: persistent CTAs, every WARP pulls 32 x 8 pixel tiles from an atomic counter on its
+// own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
+// finishes the texels.  Shared memory: the per-ray slots (64 KB) and each warp's work stack and candidate lists.
 template <bool kShade>
 __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
-    constexpr int kStage = kPrimChunk + kPrimTail;
-    __shared__ __align__(8) uint64_t s_bar[2];
-    __shared__ uint32_t s_block_tile;
-    float4* s_stage = s_dyn;                                                          // [2][kStage]
-    float* s_d = reinterpret_cast<float*>(s_dyn + 2 * kStage) + threadIdx.x;          // ray slots, this thread's column
-    unsigned short* s_list = reinterpret_cast<unsigned short*>(s_dyn + 2 * kStage + kPrimRays * kPrimSlots * kBlockThreads / 4) +
-                             (threadIdx.x >> 5) * (kPrimListCap + 8);                 // this warp's candidate list
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&s_bar[0]);
-    const uint32_t stage0 = (uint32_t)__cvta_generic_to_shared(s_stage);
-    if (threadIdx.x == 0) {
-        mbar_init(bar0, 1);
-        mbar_init(bar0 + 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
+    float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
+    // per warp: [kPrimList + 4] float4 records of the listed spheres, [kPrimList + 4] their indices, [kPrimWork] nodes
+    uint32_t* s_warp = reinterpret_cast<uint32_t*>(s_dyn) + kPrimRays * (kPrimSlots + 1) * kBlockThreads +
+                       (threadIdx.x >> 5) * (5 * (kPrimList + 4) + kPrimWork);
+    float4* s_rec = reinterpret_cast<float4*>(s_warp);
+    uint32_t* s_idx = s_warp + 4 * (kPrimList + 4);
+    uint32_t* s_work = s_idx + (kPrimList + 4);
+    const int lane = threadIdx.x & 31;
 
     const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
     const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
     const bool reset = P.cam.camera_has_moved > 0.5f;
-    const int n_pad = (int)((P.n_spheres + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll);
-    const int n_chunks = (n_pad + kPrimChunk - 1) / kPrimChunk;
     const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
     const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
-    const uint32_t n_block_tiles = (n_tiles + 7u) / 8u;
+    PrimTree T;
+    T.rec = P.prim_tree;
+    T.link = reinterpret_cast<const uint32_t*>(static_cast<const unsigned char*>(P.cl_blob) + (size_t)P.cl_n_nodes * kTreeStride * 16u);
+    T.first_leaf = P.cl_first_leaf;
+    T.n_entry = P.cl_n_entry;
+    {
+        const unsigned char* blob = static_cast<const unsigned char*>(P.cl_blob);
+        const size_t off_link = (size_t)P.cl_n_nodes * kTreeStride * 16u;
+        const size_t off_r = off_link + ((size_t)P.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
+        const size_t off_entry = off_r + ((size_t)P.cl_n_nodes * 4u + 15u) / 16u * 16u;
+        const uint32_t n_entry_pad = (P.cl_n_entry + 3u) / 4u * 4u;
+        const size_t off_entry_node = off_entry + (size_t)n_entry_pad * 16u;
+        T.entry_node = reinterpret_cast<const uint32_t*>(blob + off_entry_node);
+        T.entry_rec = P.prim_tree + (size_t)P.cl_n_nodes * kTreeStride;
+    }
     uint32_t exact_tests = 0, rays = 0;
-    uint32_t parity = 0;   // bit s: phase parity to wait for on stage s
 
-    auto request = [&](int c) {   // thread 0: chunk c -> stage c & 1
-        const int base = c * kPrimChunk;
-        const uint32_t bytes = (uint32_t)(min(kPrimChunk, n_pad - base) + kPrimTail) * (uint32_t)sizeof(float4);
-        const uint32_t bar = bar0 + 8u * (uint32_t)(c & 1);
-        mbar_expect_tx(bar, bytes);
-        bulk_copy_g2s(stage0 + (uint32_t)(c & 1) * (uint32_t)(kStage * sizeof(float4)), P.prim + base, bytes, bar);
-    };
-
-    if (n_chunks == 1) {
-        // The scene fits one stage: copied once per CTA, then every WARP pulls tiles on its own — no block barrier
-        // and no copy in the loop, so a warp on a crowded tile delays nobody.
-        if (threadIdx.x == 0) request(0);
-        mbar_wait(bar0, 0u);
-        for (;;) {
-            uint32_t tile = 0;
-            if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
-            tile = __shfl_sync(kFull, tile, 0);
-            if (tile >= n_tiles) break;
-            const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
-            const int row0 = (int)((tile / tiles_x) * kPrimTileH);
-            PrimLanes L;
-            uint32_t untraced;
-            prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
-            if (__any_sync(kFull, L.alive != 0u)) {
-                f3 m;
-                float chord;
-                prim_tile_bound(L, m, chord);
-                prim_cull_scan(s_stage, n_pad, 0, s_list, m, chord, s_d, P, L, exact_tests, lane);
-            }
-            prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
+    for (;;) {
+        uint32_t tile = 0;
+        if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
+        tile = __shfl_sync(kFull, tile, 0);
+        if (tile >= n_tiles) break;
+        const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
+        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+        PrimLanes L;
+        uint32_t untraced;
+        prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
+        if (__any_sync(kFull, L.alive != 0u)) {
+            f3 m;
+            float chord;
+            prim_tile_bound(L, m, chord);
+            prim_tree_walk(T, s_work, s_rec, s_idx, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
-    } else {
-        for (;;) {
-            __syncthreads();   // the previous tile is finished with s_block_tile and both stages
-            if (threadIdx.x == 0) s_block_tile = atomicAdd(P.tile_counter + 1, 1u);
-            __syncthreads();
-            const uint32_t bt = s_block_tile;
-            if (bt >= n_block_tiles) break;
-            if (threadIdx.x == 0) {
-                request(0);
-                request(1);
-            }
-            const uint32_t tile = bt * 8u + (uint32_t)warp;   // tiles past the end have every ray out of bounds
-            const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
-            const int row0 = (int)((tile / tiles_x) * kPrimTileH);
-            PrimLanes L;
-            uint32_t untraced;
-            prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
-            const bool warp_live = __any_sync(kFull, L.alive != 0u);
-            f3 m = rtc::mk(0.0f, 0.0f, 0.0f);
-            float chord = 0.0f;
-            if (warp_live) prim_tile_bound(L, m, chord);
-
-            for (int c = 0; c < n_chunks; ++c) {
-                const int st = c & 1, base = c * kPrimChunk;
-                mbar_wait(bar0 + 8u * (uint32_t)st, (parity >> st) & 1u);
-                parity ^= 1u << st;
-                if (warp_live)
-                    prim_cull_scan(s_stage + st * kStage, min(kPrimChunk, n_pad - base), base, s_list, m, chord, s_d, P, L,
-                                   exact_tests, lane);
-                __syncthreads();   // every warp has left stage st
-                if (threadIdx.x == 0 && c + 2 < n_chunks) request(c + 2);
-            }
-            prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
-        }
+        prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
     }
     prim_flush(P, exact_tests, rays, lane);
 }
@@ -1062,10 +1068,10 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 // ---------------------------------------------------------------------------------------------
 struct TreeView {
     const float4* rec;
-    const unsigned short* link;
+    const uint32_t* link;
     const float* node_r;
     const float4* entry_rec;            // the entry list (rt_tree.h): records ...
-    const unsigned short* entry_node;   // ... and the nodes they stand for
+    const uint32_t* entry_node;         // ... and the nodes they stand for
     int first_leaf, n_entry_pad, stack_cap;
     float entry_r;
 };
@@ -1076,13 +1082,13 @@ __device__ __forceinline__ TreeView tree_view(const void* blob, uint32_t n_nodes
     TreeView tv;
     tv.rec = reinterpret_cast<const float4*>(b);
     const size_t off_link = (size_t)n_nodes * kTreeStride * 16u;
-    tv.link = reinterpret_cast<const unsigned short*>(b + off_link);
-    const size_t off_r = off_link + ((size_t)n_nodes * kTreeWide * 2u + 15u) / 16u * 16u;
+    tv.link = reinterpret_cast<const uint32_t*>(b + off_link);
+    const size_t off_r = off_link + ((size_t)n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
     tv.node_r = reinterpret_cast<const float*>(b + off_r);
     const size_t off_entry = off_r + ((size_t)n_nodes * 4u + 15u) / 16u * 16u;
     const uint32_t n_entry_pad = (n_entry + 3u) / 4u * 4u;
     tv.entry_rec = reinterpret_cast<const float4*>(b + off_entry);
-    tv.entry_node = reinterpret_cast<const unsigned short*>(b + off_entry + (size_t)n_entry_pad * 16u);
+    tv.entry_node = reinterpret_cast<const uint32_t*>(b + off_entry + (size_t)n_entry_pad * 16u);
     tv.first_leaf = (int)first_leaf;
     tv.n_entry_pad = (int)n_entry_pad;
     tv.stack_cap = (int)stack_cap;
@@ -1167,13 +1173,13 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
                 pass |= (!(g.x < t0) ? 1u : 0u) << (2 * k);
                 pass |= (!(g.y < t1) ? 1u : 0u) << (2 * k + 1);
             }
-            const unsigned short* link = tv.link + node * kTreeWide;
+            const uint32_t* link = tv.link + node * kTreeWide;
             if (leaf) {
                 while (pass) {
                     const int bit = __ffs((int)pass) - 1;
                     pass &= pass - 1u;
                     const unsigned idx = link[bit >> 1];
-                    if (idx != 0xFFFFu) {   // (an empty slot can only get here through a NaN threshold)
+                    if (idx != 0xFFFFFFFFu) {   // (an empty slot can only get here through a NaN threshold)
                         s_cand[n_cand * kBlockThreads] = (unsigned short)(idx | ((unsigned)(bit & 1) << 15));
                         ++n_cand;
                     }
@@ -1184,7 +1190,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
                     const int bit = __ffs((int)pass) - 1;
                     pass &= pass - 1u;
                     const unsigned child = link[bit >> 1];
-                    if (child != 0xFFFFu) {
+                    if (child != 0xFFFFFFFFu) {
                         s_stack[n_stack * kBlockThreads] = (unsigned short)child;
                         ++n_stack;
                     }
@@ -1203,14 +1209,14 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
             float4 rec[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) rec[u] = tv.entry_rec[c0 + u];
-            const uint2 nodes4 = *reinterpret_cast<const uint2*>(tv.entry_node + c0);
+            const uint4 nodes4 = *reinterpret_cast<const uint4*>(tv.entry_node + c0);
+            const uint32_t node_of[4] = {nodes4.x, nodes4.y, nodes4.z, nodes4.w};
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const float2 g = broad_g2(rec[u], L, 0);
                 const bool pass = !(g.x < e0) || !(g.y < e1);
-                const unsigned node = ((u < 2 ? nodes4.x : nodes4.y) >> (16 * (u & 1))) & 0xFFFFu;
-                s_stack[n_stack * kBlockThreads] = (unsigned short)node;   // slot n_stack is free; kept only if `pass`
-                n_stack += (pass && node != 0xFFFFu) ? 1 : 0;
+                s_stack[n_stack * kBlockThreads] = (unsigned short)node_of[u];   // slot n_stack is free; kept only if `pass`
+                n_stack += (pass && node_of[u] != 0xFFFFFFFFu) ? 1 : 0;
             }
             // the stack keeps room for 4 more entries and for the growth of the traversal below them (rt_api.cu)
             if (__any_sync(kFull, n_stack > kTreeBacklog)) traverse();
@@ -1434,15 +1440,45 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_streamed_kernel(const
     wf_flush(P, bounce, exact_tests, rays, 0u, lane);
 }
 
-// Per-frame records of the primary pass (rtc::primary_record): one thread per slot.
-__global__ void prep_primary_kernel(const GpuSphere* __restrict__ spheres, float4* __restrict__ prim, uint32_t n,
-                                    uint32_t n_slots, float ox, float oy, float oz, double rho) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_slots) return;
+// Per-frame common-origin records of the tree (rt_tree.h): one thread per child slot.  A sphere under a leaf node gets
+// its own rtc::primary_record; a group gets the record of its bounding sphere, radius Rc' + m_cam (m_cam = 2^-7 (|Oc| +
+// rho): the camera's share of the members' kappa S inflation, so that every member's inflated sphere lies inside the
+// group's); children hanging under always-passing records stay always candidates; empty slots never are.
+__global__ void prep_primary_tree_kernel(const float4* __restrict__ tree_rec, const uint32_t* __restrict__ link,
+                                         const float* __restrict__ child_r, const GpuSphere* __restrict__ spheres,
+                                         const uint32_t* __restrict__ entry_slot, uint32_t n_entry,
+                                         float4* __restrict__ out, uint32_t n_nodes, uint32_t first_leaf, float ox, float oy,
+                                         float oz, double rho, float m_cam) {
+    // threads past the child slots write the entry list's records once more, contiguously, behind them
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_nodes * kTreeStride + n_entry) return;
+    uint32_t slot = t;
+    if (t >= n_nodes * kTreeStride) {
+        slot = entry_slot[t - n_nodes * kTreeStride];
+        if (slot == 0xFFFFFFFFu) {   // the root itself: always a candidate
+            out[t] = make_float4(0.0f, 0.0f, 0.0f, 1.0f);
+            return;
+        }
+    }
+    const uint32_t node = slot / kTreeStride, k = slot % kTreeStride;
     float r[4];
-    if (i < n) rtc::primary_record(spheres[i], rtc::mk(ox, oy, oz), rho, r);
-    else rtc::primary_record_pad(r);
-    prim[i] = make_float4(r[0], r[1], r[2], r[3]);
+    rtc::primary_record_pad(r);
+    if (k < (uint32_t)kTreeWide) {
+        const uint32_t lk = link[node * kTreeWide + k];
+        if (lk != 0xFFFFFFFFu) {
+            if (node >= first_leaf) {
+                rtc::primary_record(spheres[lk], rtc::mk(ox, oy, oz), rho, r);
+            } else {
+                const float4 b = tree_rec[slot];
+                if (b.w < -1.0e38f) {   // rtt::kAlways
+                    r[0] = 0.0f; r[1] = 0.0f; r[2] = 0.0f; r[3] = 1.0f;
+                } else {
+                    rtc::primary_group_record(b.x, b.y, b.z, child_r[node * kTreeWide + k], m_cam, rtc::mk(ox, oy, oz), rho, r);
+                }
+            }
+        }
+    }
+    out[t] = make_float4(r[0], r[1], r[2], r[3]);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1630,8 +1666,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // Launchers
 // ---------------------------------------------------------------------------------------------
 static size_t prim_smem_bytes() {
-    return (size_t)2 * (kPrimChunk + kPrimTail) * sizeof(float4) + (size_t)kPrimRays * kPrimSlots * kBlockThreads * sizeof(float) +
-           (size_t)(kBlockThreads / 32) * (kPrimListCap + 8) * sizeof(unsigned short);
+    return (size_t)kPrimRays * (kPrimSlots + 1) * kBlockThreads * sizeof(float) +
+           (size_t)(kBlockThreads / 32) * (5 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
 }
 
 static size_t bounce_smem_bytes() {
@@ -1664,7 +1700,7 @@ cudaError_t configure_kernels() {
 }
 
 bool primary_pass_applies(const UpdateParams& p) {
-    return p.prim != nullptr && p.first_hit != nullptr && p.n_spheres > 0 && rtc::primary_rho(p.cam) >= 0.0 &&
+    return p.prim_tree != nullptr && p.cl_n_nodes != 0u && p.first_hit != nullptr && p.n_spheres > 0 && rtc::primary_rho(p.cam) >= 0.0 &&
            rtc::f2u(p.cam.max_depth) > 0u;
 }
 
@@ -1686,7 +1722,7 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
     if (e != cudaSuccess) return e;
     const uint32_t resident = (uint32_t)sm_count * 2u;
     if (primary) {
-        e = launch_prep_primary(p.spheres, const_cast<float4*>(p.prim), p.n_spheres, p.cam, stream);
+        e = launch_prep_primary_tree(p, stream);
         if (e != cudaSuccess) return e;
         const uint32_t tiles = ((p.width + kPrimTileW - 1) / kPrimTileW) * ((p.row_count + kPrimTileH - 1) / kPrimTileH);
         uint32_t blocks = (tiles + 7) / 8;
@@ -1718,7 +1754,7 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (p.cl_n_nodes == 0u) {
+                if (p.cl_bytes == 0u) {   // the tree image does not fit the bounce kernel's shared memory
                     bounce_streamed_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
                 } else if (b < finish_from) {
                     bounce_clustered_kernel<false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
@@ -1744,10 +1780,22 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
     return cudaGetLastError();
 }
 
-cudaError_t launch_prep_primary(const GpuSphere* spheres, float4* prim, uint32_t n, const SceneCamera& cam, cudaStream_t stream) {
-    const uint32_t n_slots = (n + kPrimUnroll - 1) / kPrimUnroll * kPrimUnroll + kPrimTail;
-    prep_primary_kernel<<<(n_slots + 255) / 256, 256, 0, stream>>>(spheres, prim, n, n_slots, cam.center.x, cam.center.y,
-                                                                   cam.center.z, rtc::primary_rho(cam));
+cudaError_t launch_prep_primary_tree(const UpdateParams& p, cudaStream_t stream) {
+    const unsigned char* blob = static_cast<const unsigned char*>(p.cl_blob);
+    const size_t off_link = (size_t)p.cl_n_nodes * kTreeStride * 16u;
+    const size_t off_r = off_link + ((size_t)p.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
+    const size_t off_entry = off_r + ((size_t)p.cl_n_nodes * 4u + 15u) / 16u * 16u;
+    const uint32_t n_entry_pad = (p.cl_n_entry + 3u) / 4u * 4u;
+    const size_t off_child_r = off_entry + (size_t)n_entry_pad * 16u + ((size_t)n_entry_pad * 4u + 15u) / 16u * 16u;
+    const double rho = rtc::primary_rho(p.cam);
+    const float m_cam = rtc::primary_m_cam(p.cam, rho);
+    const size_t off_entry_slot = off_child_r + ((size_t)p.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
+    const uint32_t n_slots = p.cl_n_nodes * kTreeStride + p.cl_n_entry;
+    prep_primary_tree_kernel<<<(n_slots + 255) / 256, 256, 0, stream>>>(
+        reinterpret_cast<const float4*>(blob), reinterpret_cast<const uint32_t*>(blob + off_link),
+        reinterpret_cast<const float*>(blob + off_child_r), p.spheres, reinterpret_cast<const uint32_t*>(blob + off_entry_slot),
+        p.cl_n_entry, const_cast<float4*>(p.prim_tree), p.cl_n_nodes,
+        p.cl_first_leaf, p.cam.center.x, p.cam.center.y, p.cam.center.z, rho, m_cam);
     return cudaGetLastError();
 }
 

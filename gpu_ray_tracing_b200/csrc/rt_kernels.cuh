@@ -21,7 +21,8 @@ constexpr int kPrimTileW = 32;
 constexpr int kPrimTileH = 8;
 constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
-constexpr int kPrimListCap = 512;   // records per cull pass of a warp: capacity of its candidate list (2-byte slots)
+constexpr int kPrimWork = 256;      // per-warp stack of tree nodes awaiting their tile test
+constexpr int kPrimList = 96;       // per-warp list of spheres that passed the tile test, scanned when it fills
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
@@ -45,7 +46,8 @@ struct UpdateParams {
     uint32_t row_begin, row_count;  // window
     uint32_t tiles_x, n_tiles;  // warp tiles over the window
     unsigned int* tile_counter; // dynamic tile schedulers, zeroed before the launch: [0] update, [1] primary pass
-    const float4* prim;         // per-frame common-origin records (oc, -q), padded like geom; null = no primary pass
+    const float4* prim_tree;    // per-frame common-origin records (oc, -q) of the tree's child slots (cl_n_nodes * kTreeStride);
+                                // null = no primary pass
     // wavefront bounces (max_depth > 1 after a primary pass): compacted path queues, three float4 planes of
     // `wf_capacity` entries each: (o.xyz, d.x) (d.yz, factor.xy) (factor.z, bits(texel), bits(seed), bits(n))
     float4* wf_queue[2];
@@ -54,7 +56,8 @@ struct UpdateParams {
     uint32_t wf_bounce;         // bounce index this launch traces
     float2* first_hit;          // window texels x (t, bits(sphere index)): nearest hit of the primary ray found by
                                 // the primary pass; index -1 = miss, -2 = not traced (the update kernel scans it)
-    // tree image of the scene for the bounce rays (rt_tree.h), built after rt_set_scene; cl_n_nodes == 0: none
+    // tree image of the scene (rt_tree.h), built after rt_set_scene, in global memory; cl_n_nodes == 0: none.
+    // cl_bytes: the part the bounce kernel copies into shared memory, 0 when it does not fit (streamed bounce kernel)
     const void* cl_blob;
     uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry;
     float cl_entry_r;
@@ -68,7 +71,7 @@ cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cuda
 bool primary_pass_applies(const UpdateParams& p);
 // variant 4 = common-origin primary pass followed by the update kernel (chosen by variant 0 whenever the camera is
 // a pinhole, defocus_angle <= 0); p.prim / p.first_hit must be set.
-cudaError_t launch_prep_primary(const GpuSphere* spheres, float4* prim, uint32_t n, const SceneCamera& cam, cudaStream_t stream);
+cudaError_t launch_prep_primary_tree(const UpdateParams& p, cudaStream_t stream);
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream);
 cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream);
 cudaError_t configure_kernels();   // one-off cudaFuncSetAttribute calls

@@ -36,7 +36,7 @@ constexpr int kStride = kWide + 1;      // record slots per node in the image: t
 constexpr uint32_t kMaxEntry = 160;     // longest entry list (coherent scan) before the per-lane traversal takes over
 constexpr uint32_t kMaxAlways = 64;     // at most this many oversized spheres are pulled out of the tree
 constexpr double kMargin = 0.0078125;   // 2^-7
-constexpr uint16_t kNone = 0xFFFF;
+constexpr uint32_t kNone = 0xFFFFFFFFu;
 constexpr float kAlways = -3.0e38f;     // record constant of a child that every ray descends into
 constexpr float kNever = 3.0e38f;       // ... and of an empty slot
 
@@ -45,7 +45,9 @@ struct Tree {
     uint32_t first_leaf = 0;       // nodes [first_leaf, n_nodes) have spheres as children, the others have nodes
     uint32_t depth = 0;            // levels, root included
     std::vector<float> rec;        // n_nodes * kStride x (C.xyz, k)
-    std::vector<uint16_t> link;    // n_nodes * kWide: child node, or sphere index under a leaf node; kNone = empty
+    std::vector<uint32_t> link;    // n_nodes * kWide: child node, or sphere index under a leaf node; kNone = empty
+    std::vector<float> child_r;    // n_nodes * kWide: bounding radius Rc' of an internal node's child (0 elsewhere); the
+                                   // primary pass derives its per-frame records of the groups from it
     std::vector<float> node_r;     // n_nodes: largest bounding radius among the node's children (0 for leaf nodes)
     // Entry list: the nodes of the deepest level that still has at most kMaxEntry nodes (plus leaves above it), each
     // with the record its parent holds for it.  A warp scans this list coherently, all lanes on the same record, and
@@ -53,22 +55,29 @@ struct Tree {
     uint32_t n_entry = 0, n_entry_pad = 0;   // padded to a multiple of 4 with never-passing records
     float entry_r = 0.0f;                    // largest bounding radius among the entry records
     std::vector<float> entry_rec;            // n_entry_pad x (C.xyz, k)
-    std::vector<uint16_t> entry_node;        // n_entry_pad
+    std::vector<uint32_t> entry_node;        // n_entry_pad
+    std::vector<uint32_t> entry_slot;        // n_entry_pad: the child slot (node * kStride + k) the entry's record came from
 
-    // Device image: [rec | link | node_r], every part padded to 16 bytes.
+    // Device image: [rec | link | node_r | entry_rec | entry_node | child_r | entry_slot], every part padded to 16 bytes.  The
+    // bounce kernel copies the image up to child_r (bounce_bytes) into shared memory.
     static size_t pad16(size_t b) { return (b + 15) / 16 * 16; }
     size_t off_link() const { return (size_t)n_nodes * kStride * 16; }
-    size_t off_r() const { return off_link() + pad16((size_t)n_nodes * kWide * 2); }
+    size_t off_r() const { return off_link() + pad16((size_t)n_nodes * kWide * 4); }
     size_t off_entry_rec() const { return off_r() + pad16((size_t)n_nodes * 4); }
     size_t off_entry_node() const { return off_entry_rec() + (size_t)n_entry_pad * 16; }
-    size_t bytes() const { return off_entry_node() + pad16((size_t)n_entry_pad * 2); }
+    size_t off_child_r() const { return off_entry_node() + pad16((size_t)n_entry_pad * 4); }
+    size_t bounce_bytes() const { return off_child_r(); }
+    size_t off_entry_slot() const { return off_child_r() + pad16((size_t)n_nodes * kWide * 4); }
+    size_t bytes() const { return off_entry_slot() + pad16((size_t)n_entry_pad * 4); }
     void pack(unsigned char* blob) const {
         memset(blob, 0, bytes());
         memcpy(blob, rec.data(), rec.size() * 4);
-        memcpy(blob + off_link(), link.data(), link.size() * 2);
+        memcpy(blob + off_link(), link.data(), link.size() * 4);
         memcpy(blob + off_r(), node_r.data(), node_r.size() * 4);
         memcpy(blob + off_entry_rec(), entry_rec.data(), entry_rec.size() * 4);
-        memcpy(blob + off_entry_node(), entry_node.data(), entry_node.size() * 2);
+        memcpy(blob + off_entry_node(), entry_node.data(), entry_node.size() * 4);
+        memcpy(blob + off_child_r(), child_r.data(), child_r.size() * 4);
+        memcpy(blob + off_entry_slot(), entry_slot.data(), entry_slot.size() * 4);
     }
 };
 
@@ -112,6 +121,7 @@ struct Builder {
         std::vector<uint32_t> spheres;                // leaf: members, in index order
         std::vector<int> kids;                        // internal: child nodes (indices into `nodes`)
         std::vector<std::array<float, 4>> kid_rec;    // internal: one record per child
+        std::vector<float> kid_r;                     // internal: bounding radius per child (0 under always records)
         float rmax = 0.0f;
     };
     const GpuSphere* s;
@@ -163,6 +173,7 @@ struct Builder {
         for (auto& pt : parts) {
             float r;
             nd.kid_rec.push_back(bound_of(s, ids.data() + pt.first, pt.second - pt.first, &r));
+            nd.kid_r.push_back(r);
             nd.rmax = std::max(nd.rmax, r);
         }
         for (auto& pt : parts) nd.kids.push_back(make_subtree(pt.first, pt.second));   // (may reallocate `nodes`)
@@ -175,6 +186,7 @@ struct Builder {
         for (size_t lo = 0; lo < always.size(); lo += kWide) {
             nd.kids.push_back(make_leaf(always.data() + lo, std::min(always.size() - lo, (size_t)kWide)));
             nd.kid_rec.push_back({0.0f, 0.0f, 0.0f, kAlways});
+            nd.kid_r.push_back(0.0f);
         }
         nodes.push_back(std::move(nd));
         return (int)nodes.size() - 1;
@@ -202,10 +214,10 @@ inline double typical_leaf_radius(const GpuSphere* s, const std::vector<uint32_t
     return radii[radii.size() / 2];
 }
 
-// Builds the tree over spheres[0, n).  Returns false (out unusable) when n does not fit 16-bit links.
+// Builds the tree over spheres[0, n).  Returns false (out unusable) for an empty scene.
 inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     out = Tree();
-    if (n == 0 || n >= kNone) return false;
+    if (n == 0) return false;
     const double lim = 1073741824.0;   // 2^30, the magnitude window of the bound
     std::vector<uint32_t> bounded, always;
     for (uint32_t i = 0; i < n; ++i) {
@@ -241,10 +253,12 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     if (!bounded.empty()) {
         root.kids.push_back(b.make_subtree(0, bounded.size()));
         root.kid_rec.push_back({0.0f, 0.0f, 0.0f, kAlways});
+        root.kid_r.push_back(0.0f);
     }
     if (!always.empty()) {
         root.kids.push_back(b.make_always(always));
         root.kid_rec.push_back({0.0f, 0.0f, 0.0f, kAlways});
+        root.kid_r.push_back(0.0f);
     }
     b.nodes.push_back(std::move(root));
     const int root_i = (int)b.nodes.size() - 1;
@@ -259,7 +273,6 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     for (size_t q = 0; q < n_internal; ++q)
         for (int k : b.nodes[order[q]].kids)
             if (b.nodes[k].leaf) order.push_back(k);
-    if (order.size() >= kNone) return false;
     for (size_t q = 0; q < order.size(); ++q) number[order[q]] = (int)q;
     out.n_nodes = (uint32_t)order.size();
     out.first_leaf = n_internal;
@@ -268,6 +281,7 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     for (size_t j = 0; j < (size_t)out.n_nodes * kStride; ++j) out.rec[j * 4 + 3] = kNever;
     out.link.assign((size_t)out.n_nodes * kWide, kNone);
     out.node_r.assign(out.n_nodes, 0.0f);
+    out.child_r.assign((size_t)out.n_nodes * kWide, 0.0f);
     for (size_t q = 0; q < order.size(); ++q) {
         const Builder::Node& nd = b.nodes[order[q]];
         float* rec = &out.rec[q * kStride * 4];
@@ -276,20 +290,21 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
                 const GpuSphere& sp = s[nd.spheres[k]];
                 rec[k * 4 + 0] = sp.position.x; rec[k * 4 + 1] = sp.position.y; rec[k * 4 + 2] = sp.position.z;
                 rec[k * 4 + 3] = rtc::broad_record_k(sp);
-                out.link[q * kWide + k] = (uint16_t)nd.spheres[k];
+                out.link[q * kWide + k] = nd.spheres[k];
             }
         } else {
             for (size_t k = 0; k < nd.kids.size(); ++k) {
                 memcpy(rec + k * 4, nd.kid_rec[k].data(), 16);
-                out.link[q * kWide + k] = (uint16_t)number[nd.kids[k]];
+                out.link[q * kWide + k] = (uint32_t)number[nd.kids[k]];
+                out.child_r[q * kWide + k] = nd.kid_r[k];
             }
             out.node_r[q] = nd.rmax;
         }
     }
     // entry list: descend level by level while the frontier stays short
-    struct Entry { uint32_t node; std::array<float, 4> rec; float r; };
+    struct Entry { uint32_t node; std::array<float, 4> rec; float r; uint32_t slot; };
     std::vector<Entry> frontier;
-    frontier.push_back({0u, {0.0f, 0.0f, 0.0f, kAlways}, 0.0f});
+    frontier.push_back({0u, {0.0f, 0.0f, 0.0f, kAlways}, 0.0f, kNone});
     for (;;) {
         std::vector<Entry> next;
         bool any_internal = false;
@@ -300,12 +315,13 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
             }
             any_internal = true;
             for (int k = 0; k < kWide; ++k) {
-                const uint16_t child = out.link[(size_t)e.node * kWide + k];
+                const uint32_t child = out.link[(size_t)e.node * kWide + k];
                 if (child == kNone) continue;
                 Entry c;
                 c.node = child;
                 memcpy(c.rec.data(), &out.rec[((size_t)e.node * kStride + k) * 4], 16);
                 c.r = c.rec[3] == kAlways ? 0.0f : out.node_r[e.node];
+                c.slot = e.node * kStride + (uint32_t)k;
                 next.push_back(c);
             }
         }
@@ -316,10 +332,12 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     out.n_entry_pad = (out.n_entry + 3) / 4 * 4;
     out.entry_rec.assign((size_t)out.n_entry_pad * 4, 0.0f);
     out.entry_node.assign(out.n_entry_pad, kNone);
+    out.entry_slot.assign(out.n_entry_pad, kNone);
     for (uint32_t j = 0; j < out.n_entry_pad; ++j) out.entry_rec[(size_t)j * 4 + 3] = kNever;
     for (uint32_t j = 0; j < out.n_entry; ++j) {
         memcpy(&out.entry_rec[(size_t)j * 4], frontier[j].rec.data(), 16);
-        out.entry_node[j] = (uint16_t)frontier[j].node;
+        out.entry_node[j] = frontier[j].node;
+        out.entry_slot[j] = frontier[j].slot;
         out.entry_r = std::max(out.entry_r, frontier[j].r);
     }
     return true;

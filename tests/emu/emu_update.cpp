@@ -27,16 +27,37 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     for (uint32_t i = 0; i < count; ++i) gk[i] = rtc::broad_record_k(spheres[i]);
     // common-origin primary pass: same applicability rule as rtk::primary_pass_applies (variant 0 / 4)
     const double rho = rtc::primary_rho(cam);
-    const bool primary = (variant == 0 || variant == 4) && count > 0 && rho >= 0.0 && rtc::f2u(cam.max_depth) > 0u;
-    std::vector<float> prim(primary ? (size_t)count * 4 : 0);
-    if (primary)
-        for (uint32_t i = 0; i < count; ++i) rtc::primary_record(spheres[i], rtc::mk(cam.center), rho, &prim[(size_t)i * 4]);
-    // clustered traversal of the bounce rays (rtk::trace_clustered): the wavefront path uses it behind a primary pass
+    const bool primary_ok = (variant == 0 || variant == 4) && count > 0 && rho >= 0.0 && rtc::f2u(cam.max_depth) > 0u;
+    // the tree of bounding spheres (rt_tree.h): the primary pass walks it per pixel tile with this frame's records
+    // (rtk::prep_primary_tree_kernel), the bounce rays per ray (rtk::trace_tree) when its image fits shared memory
     rtt::Tree tree;
-    const bool clustered = primary && count < 32768u && rtt::build(spheres, count, tree) &&
-                           tree.bytes() <= (size_t)2 * (2048 + 8) * 16 && 16u + 4u + 7u * tree.depth <= 64u;
+    const bool primary = primary_ok && rtt::build(spheres, count, tree);
+    const bool clustered = primary && count < 32768u && tree.bounce_bytes() <= (size_t)2 * (2048 + 8) * 16 &&
+                           tree.n_nodes < 65536u && 16u + 4u + 7u * tree.depth <= 64u;
+    std::vector<float> ptree(primary ? (size_t)tree.n_nodes * rtt::kStride * 4 : 0);   // per child slot
+    std::vector<float> prim(primary ? (size_t)count * 4 : 0);                          // per sphere (= its leaf slot's record)
+    if (primary) {
+        const float m_cam = rtc::primary_m_cam(cam, rho);
+        for (uint32_t node = 0; node < tree.n_nodes; ++node)
+            for (int k = 0; k < rtt::kStride; ++k) {
+                float* out = &ptree[((size_t)node * rtt::kStride + k) * 4];
+                rtc::primary_record_pad(out);
+                if (k >= rtt::kWide) continue;
+                const uint32_t lk = tree.link[(size_t)node * rtt::kWide + k];
+                if (lk == rtt::kNone) continue;
+                const float* b = &tree.rec[((size_t)node * rtt::kStride + k) * 4];
+                if (node >= tree.first_leaf) {
+                    rtc::primary_record(spheres[lk], rtc::mk(cam.center), rho, out);
+                    memcpy(&prim[(size_t)lk * 4], out, 16);
+                } else if (b[3] < -1.0e38f) {
+                    out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = 1.0f;
+                } else {
+                    rtc::primary_group_record(b[0], b[1], b[2], tree.child_r[(size_t)node * rtt::kWide + k], m_cam, rtc::mk(cam.center), rho, out);
+                }
+            }
+    }
     uint64_t cluster_rays = 0, cluster_tests = 0, member_tests = 0, retraced = 0;
-    uint64_t prim_rays = 0, untraced = 0, tile_pairs = 0, tile_dropped = 0;
+    uint64_t prim_rays = 0, untraced = 0, tile_pairs = 0, tile_dropped = 0, tile_steps = 0;
     const uint32_t seed_bits_early = rtc::f2u(cam.random_seed * 4294967296.0f);
     // tile level of the primary pass (rtk::prim_tile_bound / prim_cull): per 32 x 8 pixel tile of the window, the
     // records that survive the tile test.  tile_cand[tile * count + s] != 0 <=> record s is scanned for that tile.
@@ -46,7 +67,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
         const uint32_t spp_e = rtc::f2u(cam.samples_per_pixel);
         const bool reset_e = cam.camera_has_moved > 0.5f;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : tile_pairs)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : tile_pairs, tile_steps)
 #endif
         for (int64_t tile = 0; tile < (int64_t)tiles_x * tiles_y; ++tile) {
             const uint32_t x0 = (uint32_t)(tile % tiles_x) * 32u, r0 = (uint32_t)(tile / tiles_x) * 8u;
@@ -72,11 +93,32 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
             float e2 = 0.0f;
             for (size_t k = 0; k < us.size(); k += 3) e2 = fmaxf(e2, rtc::primary_tile_e2(us[k], us[k + 1], us[k + 2], m));
             const float chord = rtc::primary_tile_chord(e2);
-            for (uint32_t sidx = 0; sidx < count; ++sidx) {
-                const float* rec = &prim[(size_t)sidx * 4];
-                const bool c = rtc::primary_tile_candidate(rec[0], rec[1], rec[2], rec[3], m, chord);
-                tile_cand[(size_t)tile * count + sidx] = c ? 1 : 0;
-                tile_pairs += c ? 1 : 0;
+            std::vector<uint32_t> work;   // the tile's walk: the entry list, then down the tree
+            for (uint32_t e = 0; e < tree.n_entry; ++e) {
+                const uint32_t slot = tree.entry_slot[e];
+                ++tile_steps;
+                if (slot != rtt::kNone) {
+                    const float* rec = &ptree[(size_t)slot * 4];
+                    if (!rtc::primary_tile_candidate(rec[0], rec[1], rec[2], rec[3], m, chord)) continue;
+                }
+                work.push_back(tree.entry_node[e]);
+            }
+            while (!work.empty()) {
+                const uint32_t node = work.back();
+                work.pop_back();
+                for (int k = 0; k < rtt::kWide; ++k) {
+                    const uint32_t lk = tree.link[(size_t)node * rtt::kWide + k];
+                    if (lk == rtt::kNone) continue;
+                    const float* rec = &ptree[((size_t)node * rtt::kStride + k) * 4];
+                    ++tile_steps;
+                    if (!rtc::primary_tile_candidate(rec[0], rec[1], rec[2], rec[3], m, chord)) continue;
+                    if (node >= tree.first_leaf) {
+                        tile_cand[(size_t)tile * count + lk] = 1;
+                        ++tile_pairs;
+                    } else {
+                        work.push_back(lk);
+                    }
+                }
             }
         }
     }
@@ -111,20 +153,30 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                     if (use_primary && rtc::primary_arm(r.d, a, &pux, &puy, &puz)) {
                         ++prim_rays;
                         const uint8_t* tc = &tile_cand[((size_t)(row / 8) * tiles_x + x / 32u) * count];
+                        bool nan_root = false;
                         for (uint32_t s = 0; s < count; ++s) {
                             const GpuSphere& sp = spheres[s];
                             const float* rec = &prim[(size_t)s * 4];
                             float root;
                             const bool ray_cand = rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz));
-                            if (ray_cand && !tc[s]) ++tile_dropped;   // expected 0: the tile test keeps what any ray test keeps
+                            if (ray_cand && !tc[s]) ++tile_dropped;   // expected 0: the tile level keeps what any ray test keeps
                             if (ray_cand && tc[s]) {
                                 ++exact;
-                                if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, best_t, &root)) {
+                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)s, &best_t, &best_i))
+                                    nan_root = true;
+                            } else if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root)) {
+                                ++violations;   // rejected a sphere the reference hits inside the original (tmin, tmax)
+                            }
+                        }
+                        if (nan_root) {   // the kernel hands such a ray to its sequential fallback
+                            best_t = 3.4e35f;
+                            best_i = -1;
+                            for (uint32_t s = 0; s < count; ++s) {
+                                float root;
+                                if (rtc::sphere_root(r.o, r.d, a, rtc::mk(spheres[s].position), spheres[s].radius, 0.001f, best_t, &root)) {
                                     best_t = root;
                                     best_i = (int)s;
                                 }
-                            } else if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root)) {
-                                ++violations;   // rejected a sphere the reference hits inside the original (tmin, tmax)
                             }
                         }
                     } else if (clustered && i >= 1) {
@@ -132,7 +184,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                         const float m_ray = rtc::cluster_m(rtc::dot(r.o, r.o));
                         std::vector<uint8_t> tested(count, 0);
                         bool nan_root = false;
-                        std::vector<uint16_t> stack;
+                        std::vector<uint32_t> stack;
                         {   // the coherent scan of the entry list
                             const float t_entry = rtc::cluster_thr(b.thr, m_ray, tree.entry_r);
                             for (uint32_t e = 0; e < tree.n_entry; ++e) {
@@ -149,7 +201,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                             const float t = leaf ? b.thr : rtc::cluster_thr(b.thr, m_ray, tree.node_r[node]);
                             for (int k = 0; k < rtt::kWide; ++k) {
                                 const float* rec = &tree.rec[((size_t)node * rtt::kStride + k) * 4];
-                                const uint16_t link = tree.link[(size_t)node * rtt::kWide + k];
+                                const uint32_t link = tree.link[(size_t)node * rtt::kWide + k];
                                 ++(leaf ? member_tests : cluster_tests);
                                 if (rtc::broad_g(rec[0], rec[1], rec[2], rec[3], b.ux, b.uy, b.uz, b.h0, b.mox, b.moy, b.moz) < t) continue;
                                 if (link == rtt::kNone) continue;
@@ -217,6 +269,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     if (stats) {
         stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced;
         stats[5] = tile_pairs; stats[6] = tile_dropped;
+        stats[11] = tile_steps;
         stats[7] = cluster_rays; stats[8] = cluster_tests; stats[9] = member_tests; stats[10] = retraced;
     }
 }
