@@ -413,22 +413,22 @@ def run_ours(args):
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": workload_config(world),
         "roofline": {"bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved_tf / peak_tf, "traffic": 74721792,
+                     "frac": achieved_tf / peak_tf, "traffic": 74364160,
                      "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
                      "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
                      "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
-                     "kernel": "primary_hits_kernel<true> (+ prep_primary_kernel, 3 us)",
-                     "ncu": {"source": "profiles/r1_primary_tiles_ncu.md (ncu --set full of this kernel on this workload)",
-                             "warp_instructions_per_launch": 319959677, "issue_slots_busy_pct": 50.8,
-                             "pipe_fma_pct": 21.3, "pipe_alu_pct": 27.1, "pipe_xu_pct": 18.8,
-                             "dram_bytes_read": 455168, "dram_bytes_written": 74266624},
+                     "kernel": "primary_hits_kernel<true> (+ prep_primary_tree_kernel, 3 us)",
+                     "ncu": {"source": "profiles/r1_primary_tree_ncu.md (ncu --set full of this kernel on this workload)",
+                             "warp_instructions_per_launch": 287235983, "issue_slots_busy_pct": 66.7,
+                             "pipe_fma_pct": 27.7, "pipe_alu_pct": 35.9, "pipe_xu_pct": 27.1, "stall_no_inst_pct": 5.5,
+                             "dram_bytes_read": 98560, "dram_bytes_written": 74265600},
                      "note": "achieved/frac count the reference's 18 flop per (ray, sphere) test over all N spheres (SURVEY.md "
-                             "8(d)).  The kernel reaches the same nearest hit without doing that work: one conservative test "
-                             "per (32x8 pixel tile, sphere) discards ~99 % of the pairs, the rays of the tile run a 3-FFMA "
-                             "sign test on the ~6 survivors and the reference quadratic on their candidates, so frac exceeds "
-                             "1.  What is left is per-ray scalar work that bit-exactness fixes (IEEE division / sqrt / the "
-                             "pinned sin-cos of get_ray and scatter): the kernel is issue-bound (ncu block), not FMA- or "
-                             "HBM-bound."},
+                             "8(d)).  The kernel reaches the same nearest hit without doing that work: each 32x8 pixel tile "
+                             "walks an 8-wide tree of bounding spheres with one conservative test per node, the rays of the "
+                             "tile run a 3-FFMA sign test on the ~6 surviving spheres and the reference quadratic on their "
+                             "candidates, so frac exceeds 1.  What is left is per-ray scalar work that bit-exactness fixes "
+                             "(IEEE division / sqrt / the pinned sin-cos of get_ray and scatter): the kernel is issue-bound "
+                             "(ncu block), not FMA- or HBM-bound."},
         "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_launch": hbm_bytes,
