@@ -9,7 +9,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librt_b200.so")
+# RT_B200_LIB: developer override, used by tools/ab_build.sh to time differently configured builds side by side
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "librt_b200.so")
 _SOURCES = ["rt_kernels.cu", "rt_kernels.cuh", "rt_core.cuh", "rt_api.cu", "rt_multi.cu", "rt_host.cpp",
             "rt_internal.h", "rt_internal_host.h", "build.sh"]
 

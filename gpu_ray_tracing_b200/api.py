@@ -122,6 +122,7 @@ _SIGNATURES = {
     "rt_read_rgba8": (C.c_int, [_P, _P]),
     "rt_read_rgba8_async": (C.c_int, [_P, _P]),
     "rt_wavefront_counts": (C.c_int, [_P, _P, C.c_uint32, _P]),
+    "rt_tree_info": (C.c_int, [_P, _P, _P, _P]),
     "rt_read_wait": (C.c_int, [_P]),
     "rt_device_alloc": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(_P)]),
     "rt_device_free": (C.c_int, [C.c_int, _P]),
@@ -394,6 +395,13 @@ class Renderer:
         n = C.c_uint32(0)
         _check(lib().rt_wavefront_counts(self._h, buf, 80, C.byref(n)))
         return [int(buf[i]) for i in range(n.value)]
+
+    def tree_info(self):
+        """(nodes, levels, bounce path) of the scene's tree: path 1 = shared-memory image, 2 = walked in global memory,
+        3 = plain records streamed, 0 = no tree yet."""
+        n, d, b = C.c_uint32(0), C.c_uint32(0), C.c_uint32(0)
+        _check(lib().rt_tree_info(self._h, C.byref(n), C.byref(d), C.byref(b)))
+        return n.value, d.value, b.value
 
     def reset_counters(self):
         _check(lib().rt_reset_counters(self._h))

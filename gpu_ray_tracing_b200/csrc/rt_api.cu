@@ -181,6 +181,7 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
         r->clusters_stale = true;
         r->cl_n_nodes = 0;
         r->cl_bytes = 0;
+        r->cl_global = 0;
     }
     RT_CUDA(rtk::launch_prep_geometry(r->spheres, r->geom, count, r->stream));
     r->launches += 1;
@@ -211,7 +212,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.tile_counter = r->tile_counter;
     p.counters = r->counters;
     p.first_hit = r->first_hit;
-    if (r->clusters_stale && (r->variant == 0 || r->variant == 4) && r->n_spheres > 0) {
+    if (r->clusters_stale && (r->variant == 0 || r->variant >= 4) && r->n_spheres > 0) {
         // first update of this scene that can use the primary pass: the tree of bounding spheres, kept in global
         // memory for the primary pass; the bounce kernel copies its image into shared memory when it fits there
         r->clusters_stale = false;
@@ -235,12 +236,15 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
             r->cl_first_leaf = tree.first_leaf;
             r->cl_n_entry = tree.n_entry;
             r->cl_entry_r = tree.entry_r;
+            r->cl_depth = tree.depth;
             // per-thread node stack of the bounce kernel: the entry backlog, 4 more entries, and 7 per level of
             // depth-first growth below them
             r->cl_stack_cap = (uint32_t)rtk::kTreeBacklog + 4u + 7u * tree.depth;
             const bool fits = r->n_spheres < 32768u && tree.n_nodes < 65536u && tree.bounce_bytes() <= rtk::kClusterImageMax &&
                               r->cl_stack_cap <= rtk::kTreeStackMax;
             r->cl_bytes = fits ? (uint32_t)tree.bounce_bytes() : 0u;
+            // too large for shared memory: the bounce kernel walks the tree where it lies (16-bit node numbers on its stack)
+            r->cl_global = (!fits && tree.n_nodes < 65536u && r->n_spheres < 0x80000000u && r->cl_stack_cap <= rtk::kTreeStackMax) ? 1u : 0u;
         }
     }
     p.prim_tree = r->cl_n_nodes ? r->prim_tree : nullptr;
@@ -248,10 +252,12 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.cl_n_nodes = r->cl_n_nodes;
     p.cl_first_leaf = r->cl_first_leaf;
     p.cl_bytes = r->cl_bytes;
+    p.cl_global = r->cl_bytes ? 0u : r->cl_global;
+    if (r->variant == 5) p.cl_bytes = p.cl_global = 0u;   // bounce rays through the streamed kernel whatever the scene size
     p.cl_stack_cap = r->cl_stack_cap;
     p.cl_n_entry = r->cl_n_entry;
     p.cl_entry_r = r->cl_entry_r;
-    if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant == 4)) {
+    if (camera->max_depth > 1.0f && !r->wf_counts && rtk::primary_pass_applies(p) && (r->variant == 0 || r->variant >= 4)) {
         // first deep frame: path queues for the wavefront bounces (two queues x three float4 planes)
         for (int q = 0; q < 2; ++q) RT_CUDA(cudaMalloc(&r->wf_queue[q], 3 * r->n_texels * sizeof(float4)));
         RT_CUDA(cudaMalloc(&r->wf_counts, rtk::kWfWords * sizeof(unsigned int)));
@@ -411,6 +417,15 @@ int rt_reset_counters(RtRenderer* r) {
     return RT_OK;
 }
 
+int rt_tree_info(RtRenderer* r, uint32_t* n_nodes, uint32_t* depth, uint32_t* bounce_path) {
+    RT_CHECK_HANDLE(r);
+    if (!n_nodes || !depth || !bounce_path) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *n_nodes = r->cl_n_nodes;
+    *depth = r->cl_n_nodes ? r->cl_depth : 0u;
+    *bounce_path = !r->cl_n_nodes ? 0u : r->variant == 5 ? 3u : r->cl_bytes ? 1u : r->cl_global ? 2u : 3u;
+    return RT_OK;
+}
+
 int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacity, uint32_t* n_out) {
     RT_CHECK_HANDLE(r);
     if (!counts || !n_out) return fail(RT_ERR_INVALID_ARG, "null argument");
@@ -470,7 +485,7 @@ int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height, uint32_t* row_be
 }
 int rt_set_kernel_variant(RtRenderer* r, int variant) {
     if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
-    if (variant < 0 || variant > 4) return fail(RT_ERR_INVALID_ARG, "variant %d not in 0..4", variant);
+    if (variant < 0 || variant > 5) return fail(RT_ERR_INVALID_ARG, "variant %d not in 0..5", variant);
     r->variant = variant;
     return RT_OK;
 }

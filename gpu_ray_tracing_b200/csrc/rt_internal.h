@@ -30,7 +30,7 @@ struct RtRenderer {
     bool clusters_stale = true;
     unsigned char* cl_blob = nullptr;
     size_t cl_capacity = 0;
-    uint32_t cl_n_nodes = 0, cl_first_leaf = 0, cl_bytes = 0, cl_stack_cap = 0, cl_n_entry = 0;
+    uint32_t cl_n_nodes = 0, cl_first_leaf = 0, cl_bytes = 0, cl_stack_cap = 0, cl_n_entry = 0, cl_global = 0, cl_depth = 0;
     float cl_entry_r = 0.0f;
     uint32_t n_spheres = 0;
     bool has_scene = false;

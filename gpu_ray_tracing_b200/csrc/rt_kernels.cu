@@ -15,6 +15,8 @@
 //                  (rtc::sphere_root), in sphere-index order with the shrinking t_max of
 //                  sphere_list_hit (compute_shader.wgsl:164-180).  Results are therefore
 //                  bit-identical to evaluating every sphere exactly.
+#include <type_traits>
+
 #include "rt_kernels.cuh"
 #include "rt_core.cuh"
 
@@ -399,6 +401,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
 namespace {
 
 constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, nearest hit (best_t, best_i)
+static_assert((kPrimList + 4) * 4 >= kPrimRays * 32, "prim_setup parks one float per ray and lane in the list area");
+static_assert(kPrimThreads % 32 == 0 && kPrimWork >= 160 + 64, "entry list (rtt::kMaxEntry) + growth");
 
 struct PrimLanes {
     float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
@@ -421,24 +425,25 @@ __device__ __forceinline__ void prim_exact(uint32_t cand, int idx, float* __rest
         const int p = __ffs((int)cand) - 1;
         cand &= cand - 1u;
         ++exact_tests;
-        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-        const f3 d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
-        const f3 origin = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
-        float bt = dp[6 * kBlockThreads];
-        int bi = __float_as_int(dp[7 * kBlockThreads]);
+        float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+        const f3 d = rtc::mk(dp[0], dp[kPrimThreads], dp[2 * kPrimThreads]);
+        const f3 origin = rtc::mk(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads]);
+        float bt = dp[6 * kPrimThreads];
+        int bi = __float_as_int(dp[7 * kPrimThreads]);
         if (!rtc::nearest_update(origin, d, rtc::dot(d, d), center, g.w, kTMin, kTMax, idx, &bt, &bi)) {
             untraced |= 1u << p;
             L.alive &= ~(1u << p);
         }
-        dp[6 * kBlockThreads] = bt;
-        dp[7 * kBlockThreads] = __int_as_float(bi);
+        dp[6 * kPrimThreads] = bt;
+        dp[7 * kPrimThreads] = __int_as_float(bi);
     }
 }
 
 // Primary rays of a strip (get_ray, compute_shader.wgsl:305-325): exact (d, o) parked in shared memory, unit
 // directions in registers.  `untraced` collects sampling rays outside primary_arm's window.
 __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
-                                           uint32_t seed_bits, uint32_t spp, bool reset, PrimLanes& L, uint32_t& untraced) {
+                                           float* __restrict__ s_tmp, uint32_t seed_bits, uint32_t spp, bool reset, PrimLanes& L,
+                                           uint32_t& untraced) {
     L.alive = 0;
     untraced = 0;
 #pragma unroll 1
@@ -464,21 +469,21 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
             untraced |= 1u << p;
             L.alive &= ~(1u << p);
         }
-        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-        dp[0] = d.x; dp[kBlockThreads] = d.y; dp[2 * kBlockThreads] = d.z;
-        dp[3 * kBlockThreads] = o.x; dp[4 * kBlockThreads] = o.y; dp[5 * kBlockThreads] = o.z;
-        dp[6 * kBlockThreads] = ux; dp[7 * kBlockThreads] = uy;
-        s_d[(kPrimRays * kPrimSlots + p) * kBlockThreads] = uz;
+        float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+        dp[0] = d.x; dp[kPrimThreads] = d.y; dp[2 * kPrimThreads] = d.z;
+        dp[3 * kPrimThreads] = o.x; dp[4 * kPrimThreads] = o.y; dp[5 * kPrimThreads] = o.z;
+        dp[6 * kPrimThreads] = ux; dp[7 * kPrimThreads] = uy;
+        s_tmp[p * 32] = uz;   // (the warp's list area is idle during set-up)
     }
 #pragma unroll
     for (int p = 0; p < kPrimRays; ++p) {
-        float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-        const float ux = dp[6 * kBlockThreads], uy = dp[7 * kBlockThreads], uz = s_d[(kPrimRays * kPrimSlots + p) * kBlockThreads];
+        float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+        const float ux = dp[6 * kPrimThreads], uy = dp[7 * kPrimThreads], uz = s_tmp[p * 32];
         const int q = p >> 1;
         if (p & 1) { L.ux[q].y = ux; L.uy[q].y = uy; L.uz[q].y = uz; }
         else       { L.ux[q].x = ux; L.uy[q].x = uy; L.uz[q].x = uz; }
-        dp[6 * kBlockThreads] = kTMax;
-        dp[7 * kBlockThreads] = __int_as_float(-1);
+        dp[6 * kPrimThreads] = kTMax;
+        dp[7 * kPrimThreads] = __int_as_float(-1);
     }
 }
 
@@ -634,9 +639,9 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         for (int p = 0; p < kPrimRays; ++p) {
             const int row = row0 + p;
             if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
-                const float code = (untraced & (1u << p)) ? __int_as_float(-2) : dp[7 * kBlockThreads];
-                P.first_hit[(size_t)row * P.width + x] = make_float2(dp[6 * kBlockThreads], code);
+                const float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+                const float code = (untraced & (1u << p)) ? __int_as_float(-2) : dp[7 * kPrimThreads];
+                P.first_hit[(size_t)row * P.width + x] = make_float2(dp[6 * kPrimThreads], code);
             }
         }
     } else {
@@ -655,12 +660,12 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 n = rtc::f2u(t.w);
             }
             if (sampling & (1u << p)) {
-                const float* dp = s_d + (p * kPrimSlots) * kBlockThreads;
+                const float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
                 rtc::Ray r;
-                r.d = rtc::mk(dp[0], dp[kBlockThreads], dp[2 * kBlockThreads]);
-                r.o = rtc::mk(dp[3 * kBlockThreads], dp[4 * kBlockThreads], dp[5 * kBlockThreads]);
-                float best_t = dp[6 * kBlockThreads];
-                int best_i = __float_as_int(dp[7 * kBlockThreads]);
+                r.d = rtc::mk(dp[0], dp[kPrimThreads], dp[2 * kPrimThreads]);
+                r.o = rtc::mk(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads]);
+                float best_t = dp[6 * kPrimThreads];
+                int best_i = __float_as_int(dp[7 * kPrimThreads]);
                 if (untraced & (1u << p)) {
                     // outside primary_arm's window: the reference loop itself (compute_shader.wgsl:164-180)
                     const float a = rtc::dot(r.d, r.d);
@@ -737,11 +742,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
 // finishes the texels.  Shared memory: the per-ray slots (64 KB) and each warp's work stack and candidate lists.
 template <bool kShade>
-__global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
+__global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
     // per warp: [kPrimList + 4] float4 records of the listed spheres, [kPrimList + 4] their indices, [kPrimWork] nodes
-    uint32_t* s_warp = reinterpret_cast<uint32_t*>(s_dyn) + kPrimRays * (kPrimSlots + 1) * kBlockThreads +
+    uint32_t* s_warp = reinterpret_cast<uint32_t*>(s_dyn) + kPrimRays * kPrimSlots * kPrimThreads +
                        (threadIdx.x >> 5) * (5 * (kPrimList + 4) + kPrimWork);
     float4* s_rec = reinterpret_cast<float4*>(s_warp);
     uint32_t* s_idx = s_warp + 4 * (kPrimList + 4);
@@ -779,7 +784,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) primary_hits_kernel(const __
         const int row0 = (int)((tile / tiles_x) * kPrimTileH);
         PrimLanes L;
         uint32_t untraced;
-        prim_setup(P, x, row0, s_d, seed_bits, spp, reset, L, untraced);
+        prim_setup(P, x, row0, s_d, reinterpret_cast<float*>(s_rec) + lane, seed_bits, spp, reset, L, untraced);
         if (__any_sync(kFull, L.alive != 0u)) {
             f3 m;
             float chord;
@@ -1114,14 +1119,16 @@ __device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ 
 
 // One exact test per lane and iteration: every lane works on its own (sphere, ray) candidate, so the reference
 // quadratic runs on full warps instead of on the one lane that happened to find a candidate.
-__device__ __forceinline__ void drain_candidates(const unsigned short* __restrict__ s_cand, int& n_cand,
+template <typename CandT>
+__device__ __forceinline__ void drain_candidates(const CandT* __restrict__ s_cand, int& n_cand,
                                                  const GpuSphere* __restrict__ spheres, Lanes& L, uint32_t& exact_tests,
                                                  uint32_t& nan_rays) {
     for (int e = 0; __any_sync(kFull, e < n_cand); ++e) {
         if (e < n_cand) {
-            const int code = (int)s_cand[e * kBlockThreads];
-            const int idx = code & 0x7fff;
-            const bool second = (code >> 15) != 0;
+            constexpr int kRayBit = (int)sizeof(CandT) * 8 - 1;   // top bit: the thread's second ray
+            const uint32_t code = (uint32_t)s_cand[e * kBlockThreads];
+            const int idx = (int)(code & ((1u << kRayBit) - 1u));
+            const bool second = (code >> kRayBit) != 0u;
             const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
             // the ray is picked with selects: one copy of the quadratic for both rays
             const f3 o = second ? origin_of(L, 1) : origin_of(L, 0);
@@ -1145,8 +1152,9 @@ __device__ __forceinline__ void drain_candidates(const unsigned short* __restric
 }
 
 // Nearest hits of the thread's rays 0 and 1 through the tree.  s_stack / s_cand: this thread's columns.
+template <typename CandT>
 __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* __restrict__ s_stack,
-                                           unsigned short* __restrict__ s_cand, const GpuSphere* __restrict__ spheres,
+                                           CandT* __restrict__ s_cand, const GpuSphere* __restrict__ spheres,
                                            uint32_t n_spheres, Lanes& L, uint32_t& exact_tests) {
     const float inf = __int_as_float(0x7f800000);
     const float thr0 = L.alive[0] ? L.thr[0] : inf, thr1 = L.alive[1] ? L.thr[1] : inf;
@@ -1180,7 +1188,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
                     pass &= pass - 1u;
                     const unsigned idx = link[bit >> 1];
                     if (idx != 0xFFFFFFFFu) {   // (an empty slot can only get here through a NaN threshold)
-                        s_cand[n_cand * kBlockThreads] = (unsigned short)(idx | ((unsigned)(bit & 1) << 15));
+                        s_cand[n_cand * kBlockThreads] = (CandT)(idx | ((unsigned)(bit & 1) << ((int)sizeof(CandT) * 8 - 1)));
                         ++n_cand;
                     }
                 }
@@ -1244,8 +1252,9 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 32u
 #endif
+template <typename CandT>
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
-                                          const TreeView& tv, unsigned short* __restrict__ s_stack, unsigned short* __restrict__ s_cand,
+                                          const TreeView& tv, unsigned short* __restrict__ s_stack, CandT* __restrict__ s_cand,
                                           unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
                                           uint32_t& exact_tests_out, uint32_t& rays_out, uint32_t& rays_later_out) {
     const uint32_t n_batches = (count + 63u) / 64u;
@@ -1321,13 +1330,18 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
 // (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code.
 // Three CTAs per SM for the full-queue instantiation (77 registers, ~60 KB of shared memory for 1024 spheres); the
 // finishing one would spill at that budget and runs when the machine is mostly idle anyway.
-template <bool kFinish>
+// kGlobal: the instantiation for scenes whose image does not fit shared memory (cl_bytes == 0): the same traversal
+// reads the tree where it lies in global memory (L1 / L2; the upper levels stay hot), and the candidate codes are
+// 32 bits wide, so the sphere count is not limited by the code's 15 index bits either.
+template <bool kFinish, bool kGlobal>
 __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
-    const uint32_t image_slots = (P.cl_bytes + 15u) / 16u;
-    unsigned short* s_stack = reinterpret_cast<unsigned short*>(s_dyn + image_slots) + threadIdx.x;   // [cl_stack_cap][kBlockThreads]
-    unsigned short* s_cand = s_stack + P.cl_stack_cap * kBlockThreads;                                // [kWfCand][kBlockThreads]
+    using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
+    const uint32_t image_slots = kGlobal ? 0u : (P.cl_bytes + 15u) / 16u;
+    // [kWfCand][kBlockThreads] candidate codes, then [cl_stack_cap][kBlockThreads] node numbers
+    CandT* s_cand = reinterpret_cast<CandT*>(s_dyn + image_slots) + threadIdx.x;
+    unsigned short* s_stack = reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads) + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) {
@@ -1346,12 +1360,15 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
     uint32_t exact_tests = 0, rays = 0, rays_later = 0;
     if (count == 0u) return;
 
-    if (threadIdx.x == 0) {
-        mbar_expect_tx(bar, P.cl_bytes);
-        bulk_copy_g2s((uint32_t)__cvta_generic_to_shared(s_dyn), P.cl_blob, P.cl_bytes, bar);
+    if constexpr (!kGlobal) {
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar, P.cl_bytes);
+            bulk_copy_g2s((uint32_t)__cvta_generic_to_shared(s_dyn), P.cl_blob, P.cl_bytes, bar);
+        }
+        mbar_wait(bar, 0u);
     }
-    mbar_wait(bar, 0u);
-    const TreeView tv = tree_view(s_dyn, P.cl_n_nodes, P.cl_first_leaf, P.cl_n_entry, P.cl_entry_r, P.cl_stack_cap);
+    const TreeView tv = tree_view(kGlobal ? P.cl_blob : (const void*)s_dyn, P.cl_n_nodes, P.cl_first_leaf, P.cl_n_entry, P.cl_entry_r,
+                                  P.cl_stack_cap);
     const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
     if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
         const uint32_t n_batches = (count + 63u) / 64u;
@@ -1666,8 +1683,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // Launchers
 // ---------------------------------------------------------------------------------------------
 static size_t prim_smem_bytes() {
-    return (size_t)kPrimRays * (kPrimSlots + 1) * kBlockThreads * sizeof(float) +
-           (size_t)(kBlockThreads / 32) * (5 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
+    return (size_t)kPrimRays * kPrimSlots * kPrimThreads * sizeof(float) +
+           (size_t)(kPrimThreads / 32) * (5 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
 }
 
 static size_t bounce_smem_bytes() {
@@ -1675,6 +1692,9 @@ static size_t bounce_smem_bytes() {
 }
 static size_t clustered_smem_bytes(uint32_t image_bytes, uint32_t stack_cap) {
     return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(stack_cap + kWfCand) * kBlockThreads * sizeof(unsigned short);
+}
+static size_t clustered_global_smem_bytes(uint32_t stack_cap) {   // tree in global memory, 32-bit candidate codes
+    return (size_t)kWfCand * kBlockThreads * sizeof(uint32_t) + (size_t)stack_cap * kBlockThreads * sizeof(unsigned short);
 }
 
 cudaError_t configure_kernels() {
@@ -1689,11 +1709,17 @@ cudaError_t configure_kernels() {
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(bounce_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)clustered_global_smem_bytes(kTreeStackMax));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(bounce_clustered_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)clustered_global_smem_bytes(kTreeStackMax));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
@@ -1707,9 +1733,9 @@ bool primary_pass_applies(const UpdateParams& p) {
 cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
     UpdateParams p = p_in;
     int n_launch = 0;
-    const bool primary = (variant == 0 || variant == 4) && primary_pass_applies(p);
+    const bool primary = (variant == 0 || variant >= 4) && primary_pass_applies(p);
     if (!primary) p.first_hit = nullptr;
-    if (variant == 4) variant = 0;
+    if (variant >= 4) variant = 0;
     if (variant == 0) variant = (p.n_spheres <= kResidentMaxSpheres) ? 2 : 3;
     if (variant == 2 && p.n_spheres > kResidentMaxSpheres) variant = 3;
     if (variant == 1) {
@@ -1725,11 +1751,12 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         e = launch_prep_primary_tree(p, stream);
         if (e != cudaSuccess) return e;
         const uint32_t tiles = ((p.width + kPrimTileW - 1) / kPrimTileW) * ((p.row_count + kPrimTileH - 1) / kPrimTileH);
-        uint32_t blocks = (tiles + 7) / 8;
-        if (blocks > resident) blocks = resident;
+        constexpr uint32_t warps = kPrimThreads / 32;
+        uint32_t blocks = (tiles + warps - 1) / warps;
+        if (blocks > (uint32_t)sm_count * kPrimCtas) blocks = (uint32_t)sm_count * kPrimCtas;
         const bool shade = rtc::f2u(p.cam.max_depth) == 1u;
-        if (shade) primary_hits_kernel<true><<<blocks, kBlockThreads, prim_smem_bytes(), stream>>>(p);
-        else primary_hits_kernel<false><<<blocks, kBlockThreads, prim_smem_bytes(), stream>>>(p);
+        if (shade) primary_hits_kernel<true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        else primary_hits_kernel<false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         n_launch += 2;
@@ -1754,12 +1781,16 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (p.cl_bytes == 0u) {   // the tree image does not fit the bounce kernel's shared memory
+                if (p.cl_bytes == 0u && p.cl_global != 0u) {   // the tree stays in global memory
+                    const size_t smem = clustered_global_smem_bytes(p.cl_stack_cap);
+                    if (b < finish_from) bounce_clustered_kernel<false, true><<<(uint32_t)sm_count * 3u, kBlockThreads, smem, stream>>>(p);
+                    else bounce_clustered_kernel<true, true><<<resident, kBlockThreads, smem, stream>>>(p);
+                } else if (p.cl_bytes == 0u) {   // no tree the bounce kernel can walk (node numbers beyond 16 bits)
                     bounce_streamed_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
                 } else if (b < finish_from) {
-                    bounce_clustered_kernel<false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
+                    bounce_clustered_kernel<false, false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
                 } else {
-                    bounce_clustered_kernel<true><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
+                    bounce_clustered_kernel<true, false><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
                 }
                 n_launch += 1;
             }

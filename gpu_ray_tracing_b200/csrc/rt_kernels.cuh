@@ -21,15 +21,31 @@ constexpr int kPrimTileW = 32;
 constexpr int kPrimTileH = 8;
 constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
 constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
-constexpr int kPrimWork = 256;      // per-warp stack of tree nodes awaiting their tile test
-constexpr int kPrimList = 96;       // per-warp list of spheres that passed the tile test, scanned when it fills
+#ifndef RT_PRIM_THREADS
+#define RT_PRIM_THREADS 352
+#endif
+#ifndef RT_PRIM_CTAS
+#define RT_PRIM_CTAS 2
+#endif
+#ifndef RT_PRIM_LIST
+#define RT_PRIM_LIST 64
+#endif
+#ifndef RT_PRIM_WORK
+#define RT_PRIM_WORK 224
+#endif
+// CTA shape of the primary pass: no block barrier anywhere, so the CTA is only a container of warps; 2 x 11 warps
+// per SM is what 88 registers and 10.2 KB of shared memory per warp (8 KB ray slots + lists) allow
+constexpr int kPrimThreads = RT_PRIM_THREADS;
+constexpr int kPrimCtas = RT_PRIM_CTAS;
+constexpr int kPrimWork = RT_PRIM_WORK;   // per-warp stack of tree nodes awaiting their tile test (entry list <= 160 + growth)
+constexpr int kPrimList = RT_PRIM_LIST;   // per-warp list of spheres that passed the tile test, scanned when it fills
 constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
 constexpr int kTreeWide = 8;                           // children per node of the bounce rays' tree (rtt::kWide)
 constexpr int kTreeStride = kTreeWide + 1;             // record slots per node in the image (rtt::kStride)
 constexpr int kTreeBacklog = 16;                       // entry nodes a lane may stack up before the warp traverses
-constexpr uint32_t kTreeStackMax = 64;                 // deepest per-thread node stack the bounce kernel is configured for
+constexpr uint32_t kTreeStackMax = 96;                 // deepest per-thread node stack the bounce kernel is configured for
 constexpr uint32_t kWfFinishFrom = 3;                   // first bounce whose launch may finish a short queue to the end
 constexpr int kWfChunk = 2048;      // wavefront bounce kernel: general records per stage (32 KB)
 constexpr size_t kClusterImageMax = (size_t)2 * (kWfChunk + 8) * 16;   // the bounce kernel's two record stages
@@ -59,7 +75,8 @@ struct UpdateParams {
     // tree image of the scene (rt_tree.h), built after rt_set_scene, in global memory; cl_n_nodes == 0: none.
     // cl_bytes: the part the bounce kernel copies into shared memory, 0 when it does not fit (streamed bounce kernel)
     const void* cl_blob;
-    uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry;
+    // cl_global: cl_bytes == 0 but the bounce kernel can walk the tree in global memory (node numbers fit 16 bits)
+    uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry, cl_global;
     float cl_entry_r;
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };

@@ -184,6 +184,11 @@ RT_API int rt_reset_counters(RtRenderer* r);
 /* Rays the wavefront traced per bounce in the last deep (max_depth > 1) update: counts[b] for b >= 1 (counts[0] is
  * unused: bounce 0 is the primary pass).  *n_out = entries written (0 before any deep frame). */
 RT_API int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacity, uint32_t* n_out);
+/* The scene's tree of bounding spheres as of the last update (zeros before the first one that built it): node count,
+ * levels, and how bounce rays (max_depth > 1) meet it — 0 = no tree, 1 = image copied into shared memory per CTA,
+ * 2 = walked where it lies in global memory (scenes past the shared-memory budget), 3 = not walked: plain records
+ * streamed (node numbers beyond 16 bits, or kernel variant 5). */
+RT_API int rt_tree_info(RtRenderer* r, uint32_t* n_nodes, uint32_t* depth, uint32_t* bounce_path);
 
 /* Device-side timing of the update kernels on the renderer's own stream (CUDA events). */
 RT_API int rt_timer_begin(RtRenderer* r);
@@ -205,7 +210,8 @@ RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
  * quadratic per sphere), 2 = tiled broad phase + exact narrow phase with the scene resident in shared
  * memory, 3 = the same streaming the scene through shared memory, 4 = common-origin primary pass
  * (primary rays of pinhole and defocus cameras, records streamed through shared memory) followed by 2 or 3
- * for the bounces.  0 picks 4 when it applies, else 2 or 3. */
+ * for the bounces, 5 = as 4 with the bounce rays forced through the streamed-record kernel (the path of scenes whose
+ * tree the bounce kernel cannot walk).  0 picks 4 when it applies, else 2 or 3. */
 RT_API int rt_set_kernel_variant(RtRenderer* r, int variant);
 
 /* ---------------------------------------------------------------------------------------

@@ -136,7 +136,10 @@ def test_large_scene_streamed():
     cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
     gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
     assert rays_cpu == rays_gpu
-    assert_parity(gpu, cpu, "grid 16384 depth 6")
+    assert_parity(gpu, cpu, "grid 16384 depth 6 (tree walked in global memory)")
+    gpu5, rays_gpu5, _ = gpu_update(scene, [cam], W, H, variant=5)
+    assert rays_cpu == rays_gpu5
+    assert_parity(gpu5, cpu, "grid 16384 depth 6 (streamed bounce kernel)")
     # 3000 spheres: three chunks with a ragged last one through the streamed primary pass, defocus camera
     scene = scenes.random_scene(3000)
     cam = scenes.camera(W, H, max_depth=3, spp=2)
@@ -282,16 +285,37 @@ def test_degenerate_spheres_on_device(variant):
 
 
 def test_tree_sizes_and_streamed_fallback():
-    """Bounce rays through trees of different depths (8 ... 3,000 spheres) and, past the shared-memory budget of the
-    tree image, through the streamed kernel; the counters of both paths agree with the oracle's ray count."""
+    """Bounce rays through trees of different depths (8 ... 3,000 spheres: image in shared memory; 6,000 and 40,000:
+    past that budget, walked in global memory with 32-bit candidate codes) and through the streamed-record kernel
+    (variant 5); the counters of every path agree with the oracle's ray count."""
     W, H = 192, 108
-    for n in (8, 9, 64, 65, 500, 3000, 6000):
-        scene = scenes.random_scene(n)
+    for n in (8, 9, 64, 65, 500, 3000, 6000, 40000):
+        scene = scenes.random_scene(n) if n < 10000 else scenes.grid_scene(n)
         cam = scenes.camera(W, H, max_depth=5, spp=500)
         cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
         gpu, rays_gpu, _ = gpu_update(scene, [cam], W, H)
         assert rays_gpu == rays_cpu, n
         assert_parity(gpu, cpu, f"random {n} depth 5")
+        if n in (500, 6000):
+            gpu5, rays_gpu5, _ = gpu_update(scene, [cam], W, H, variant=5)
+            assert rays_gpu5 == rays_cpu, n
+            assert_parity(gpu5, cpu, f"random {n} depth 5, streamed bounce kernel")
+
+
+def test_bounce_path_selection():
+    """Which traversal the bounce rays get (rt_tree_info): shared-memory image for small scenes, the tree walked in
+    global memory past that budget (config 5's 65,536 spheres included), streamed records only on request."""
+    W, H = 64, 36
+    for scene, variant, want in ((scenes.random_scene(1024), 0, 1), (scenes.random_scene(6000), 0, 2),
+                                 (scenes.grid_scene(65536), 0, 2), (scenes.random_scene(6000), 5, 3)):
+        with rt.Renderer(W, H) as r:
+            r.set_kernel_variant(variant)
+            r.set_scene(scene)
+            r.init()
+            assert r.tree_info() == (0, 0, 0)
+            r.update(scenes.camera(W, H, max_depth=3, spp=1))
+            nodes, depth, path = r.tree_info()
+            assert nodes > scene.count // 8 and depth >= 2 and path == want, (scene.count, variant, nodes, depth, path)
 
 
 def test_async_read_into_device_memory():
