@@ -124,6 +124,7 @@ _SIGNATURES = {
     "rt_wavefront_counts": (C.c_int, [_P, _P, C.c_uint32, _P]),
     "rt_tree_info": (C.c_int, [_P, _P, _P, _P]),
     "rt_read_wait": (C.c_int, [_P]),
+    "rt_set_rgba8_output": (C.c_int, [_P, C.c_int]),
     "rt_device_alloc": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(_P)]),
     "rt_device_free": (C.c_int, [C.c_int, _P]),
     "rt_ipc_export": (C.c_int, [C.c_int, _P, _P]),
@@ -395,6 +396,10 @@ class Renderer:
         n = C.c_uint32(0)
         _check(lib().rt_wavefront_counts(self._h, buf, 80, C.byref(n)))
         return [int(buf[i]) for i in range(n.value)]
+
+    def set_rgba8_output(self, enable: bool = True):
+        """Depth-1 updates also write the RGBA8 frame the next read_rgba8_async* call sends (no quantise kernel)."""
+        _check(lib().rt_set_rgba8_output(self._h, 1 if enable else 0))
 
     def tree_info(self):
         """(nodes, levels, bounce path) of the scene's tree: path 1 = shared-memory image, 2 = walked in global memory,

@@ -195,6 +195,7 @@ int rt_set_scene(RtRenderer* r, const GpuSphere* spheres, uint32_t buffer_len, u
 int rt_init(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
     RT_CUDA(cudaMemsetAsync(r->accum, 0, r->n_texels * sizeof(float4), r->stream));
+    r->rgba8_fresh = false;
     return RT_OK;
 }
 
@@ -267,9 +268,19 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.wf_counts = r->wf_counts;
     p.wf_capacity = (uint32_t)r->n_texels;
     p.wf_bounce = 0;
+    p.rgba8_out = nullptr;
+    r->rgba8_fresh = false;
+    if (r->rgba8_output && rtk::fused_shade_applies(p, r->variant)) {
+        // the slot the next rt_read_rgba8_async will send: its previous copy must have left it
+        if (!r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
+        const int b = (int)(r->async_reads & 1u);
+        if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
+        p.rgba8_out = reinterpret_cast<uint32_t*>(b ? r->rgba8_alt : r->rgba8);
+    }
     int launched = 0;
     RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched));
     r->launches += (uint64_t)launched;
+    r->rgba8_fresh = p.rgba8_out != nullptr;
     return RT_OK;
 }
 
@@ -308,6 +319,7 @@ int rt_read_accum(RtRenderer* r, float* host) {
 int rt_write_accum(RtRenderer* r, const float* host) {
     RT_CHECK_HANDLE(r);
     if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
+    r->rgba8_fresh = false;
     RT_CUDA(cudaMemcpyAsync(r->accum, host, r->n_texels * sizeof(float4), cudaMemcpyHostToDevice, r->stream));
     RT_CUDA(cudaStreamSynchronize(r->stream));
     return RT_OK;
@@ -345,15 +357,25 @@ int rt_read_rgba8_async(RtRenderer* r, uint8_t* host) {
     const int b = (int)(r->async_reads & 1u);
     uchar4* dev = b ? r->rgba8_alt : r->rgba8;
     // slot b was last used two reads ago: its copy must have left the buffer before it is overwritten
-    if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
-    RT_CUDA(rtk::launch_quantize(r->accum, dev, r->n_texels, r->stream));
-    r->launches += 1;
+    if (!r->rgba8_fresh) {   // (a fused update has already written slot b, after the same wait)
+        if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
+        RT_CUDA(rtk::launch_quantize(r->accum, dev, r->n_texels, r->stream));
+        r->launches += 1;
+    }
+    r->rgba8_fresh = false;
     RT_CUDA(cudaEventRecord(r->ev_quantized[b], r->stream));
     RT_CUDA(cudaStreamWaitEvent(r->copy_stream, r->ev_quantized[b], 0));
     // cudaMemcpyDefault: the destination may be pinned host memory or device memory of this or a peer GPU
     RT_CUDA(cudaMemcpyAsync(host, dev, r->n_texels * sizeof(uchar4), cudaMemcpyDefault, r->copy_stream));
     RT_CUDA(cudaEventRecord(r->ev_copied[b], r->copy_stream));
     r->async_reads += 1;
+    return RT_OK;
+}
+
+int rt_set_rgba8_output(RtRenderer* r, int enable) {
+    RT_CHECK_HANDLE(r);
+    r->rgba8_output = enable != 0;
+    r->rgba8_fresh = false;
     return RT_OK;
 }
 

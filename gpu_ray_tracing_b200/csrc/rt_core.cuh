@@ -34,10 +34,21 @@ RT_DEV f3 add(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 RT_DEV f3 sub(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
 RT_DEV f3 mul(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 RT_DEV f3 scale(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
-RT_DEV f3 divs(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+// The IEEE divisions (and the square root of normalize) expand to ~12 instructions each plus a slow-path call; the
+// kernels' instruction footprint is what limits them, so on the device the three-way division
+// and normalize exist ONCE, out of line, instead of once per call site.  Same operations, same results.
+#if defined(__CUDACC__) && !defined(RT_INLINE_DIVS)
+#define RT_DEV_SHARED static __host__ __device__ __noinline__
+#else
+#define RT_DEV_SHARED RT_DEV
+#endif
+RT_DEV_SHARED f3 divs(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
 RT_DEV f3 neg(f3 a) { return mk(-a.x, -a.y, -a.z); }
 RT_DEV float dot(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-RT_DEV f3 normalize(f3 a) { return divs(a, sqrtf(dot(a, a))); }
+RT_DEV_SHARED f3 normalize(f3 a) {
+    const float s = sqrtf(dot(a, a));
+    return mk(a.x / s, a.y / s, a.z / s);
+}
 
 // WGSL u32(f32): truncate, saturate, NaN -> 0
 RT_DEV uint32_t f2u(float f) {
@@ -316,7 +327,7 @@ RT_DEV void primary_record_pad(float out[4]) { out[0] = 0.0f; out[1] = 0.0f; out
 
 // Unit direction of a ray for the common-origin test.  Returns false (and u = 0) when |d|^2 is
 // outside [2^-40, 2^40] or not finite: such a ray has to be traced with the exact test only.
-RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz) {
+RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz, float* inv_len = nullptr) {
     const bool ok = (a >= 9.094947017729282e-13f) && (a <= 1099511627776.0f);
     if (!ok) {
         *ux = 0.0f; *uy = 0.0f; *uz = 0.0f;
@@ -324,6 +335,7 @@ RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz) {
     }
     const float inv = 1.0f / sqrtf(a);
     *ux = d.x * inv; *uy = d.y * inv; *uz = d.z * inv;
+    if (inv_len) *inv_len = inv;   // 1 / |d|
     return true;
 }
 
@@ -396,6 +408,23 @@ RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m,
     const float lhs = fmaf(sqrtf(n2), 3.814697265625e-06f, fmaf(R, k, fmaf(-q, ce, t)));
     return !(lhs < 0.0f);
 }
+
+// Nearest-first order and the "already beaten" cull of the primary pass.  From a sphere's common-origin record
+// (oc, -q): |oc| - R, R = sqrt(|oc|^2 - q^2) >= r + rho (primary_record), is a lower bound of the distance from any
+// origin on the defocus disk to the sphere's surface, so the reference's accepted root of a ray with direction d is at
+// least (|oc| - R) / |d| — in exact arithmetic.  The reference's float root (h - sqrt(h^2 - a c)) / a is below the
+// exact one by at most sqrt(delta) / a, delta <= 2^-22 h^2 the rounding of its discriminant, i.e. by 2^-11 |oc| / |d|
+// (its other roundings are of order 2^-22); primary_near takes 2^-9 |oc| and 2^-10 R off, four times that.  A sphere
+// with  primary_near * (smallest 1/|d| of the rays concerned) * (1 - 2^-12)  >  the nearest hit they all hold
+// cannot win for any of them (first root > best_t >= tmin: it loses or is rejected at tmax; the second root is larger
+// still) and is not tested.  Negative for a camera inside the inflated sphere and 0 for an always-record: never culled.
+RT_DEV float primary_near(float rx, float ry, float rz, float rw) {
+    const float q = -rw;
+    const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
+    const float R = sqrtf(fmaxf(fmaf(n2, 1.000003814697265625f, -((q * q) * 0.999996185302734375f)), 0.0f));
+    return fmaf(-R, 1.0009765625f, sqrtf(n2) * 0.998046875f);
+}
+RT_DEV float primary_near_scale(float inv_len_min) { return inv_len_min * 0.999755859375f; }
 
 // ---------------------------------------------------------------------------------------------
 // Group level of the general broad phase (rt_tree.h).  A group's bounding sphere has an ordinary record

@@ -40,6 +40,8 @@ struct RtRenderer {
     // asynchronous read-back (rt_read_rgba8_async): second RGBA8 buffer, copy stream, per-slot events
     cudaStream_t copy_stream = nullptr;
     uchar4* rgba8_alt = nullptr;
+    bool rgba8_output = false;   // rt_set_rgba8_output: fused updates also write the next async slot
+    bool rgba8_fresh = false;    // ... and the last update did, nothing has touched the accumulators since
     cudaEvent_t ev_quantized[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
     uint32_t async_reads = 0;
     uint64_t launches = 0;

@@ -398,15 +398,43 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
 // exactly what sphere_list_hit returns for the primary ray.  Shading and the texel update stay in
 // the update kernel, which skips its own first traversal when first_hit is present.
 // ---------------------------------------------------------------------------------------------
+// Linear RGBA8 of the running mean: q(x) = floor(clamp(x, 0, 1) * 255 + 0.5), alpha 255.
+__device__ __forceinline__ unsigned quant1(float v) {
+    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+    float q = floorf(v * 255.0f + 0.5f);
+    return (q == q) ? (unsigned)q : 0u;
+}
+__device__ __forceinline__ unsigned quant_texel(float4 t) {
+    return quant1(t.x) | (quant1(t.y) << 8) | (quant1(t.z) << 16) | 0xFF000000u;
+}
+
 namespace {
 
+// The reference loop itself (compute_shader.wgsl:164-180) for a ray whose tree traversal met a NaN root.
+__device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ spheres, uint32_t n_spheres, float ox, float oy,
+                                                  float oz, float dx, float dy, float dz, float a) {
+    float bt = kTMax;
+    int bi = -1;
+    for (uint32_t si = 0; si < n_spheres; ++si) {
+        const float4 g = __ldg(reinterpret_cast<const float4*>(spheres + si));
+        float root;
+        if (rtc::sphere_root(rtc::mk(ox, oy, oz), rtc::mk(dx, dy, dz), a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, bt, &root)) {
+            bt = root;
+            bi = (int)si;
+        }
+    }
+    return make_float2(bt, __int_as_float(bi));
+}
+
 constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, nearest hit (best_t, best_i)
-static_assert((kPrimList + 4) * 4 >= kPrimRays * 32, "prim_setup parks one float per ray and lane in the list area");
+static_assert((kPrimList + 4) * 6 >= kPrimRays * 32, "prim_setup parks one float per ray and lane in the list area");
 static_assert(kPrimThreads % 32 == 0 && kPrimWork >= 160 + 64, "entry list (rtt::kMaxEntry) + growth");
 
 struct PrimLanes {
     float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
     uint32_t alive;   // bit p: ray p is traced here
+    float bt_max;     // the farthest nearest-hit among the traced rays (kTMax while one of them has none)
+    float near_scale; // rtc::primary_near_scale of the smallest 1 / |d| among them
 };
 
 __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 1) ? v.y : v.x; }
@@ -437,6 +465,13 @@ __device__ __forceinline__ void prim_exact(uint32_t cand, int idx, float* __rest
         dp[6 * kPrimThreads] = bt;
         dp[7 * kPrimThreads] = __int_as_float(bi);
     }
+    if (!RT_PRIM_CULL) return;
+    // the strip's farthest nearest-hit, for the "already beaten" cull of the spheres still to come
+    float far = -kTMax;
+#pragma unroll
+    for (int p = 0; p < kPrimRays; ++p)
+        if (L.alive & (1u << p)) far = fmaxf(far, s_d[(p * kPrimSlots + 6) * kPrimThreads]);
+    L.bt_max = far;
 }
 
 // Primary rays of a strip (get_ray, compute_shader.wgsl:305-325): exact (d, o) parked in shared memory, unit
@@ -446,6 +481,7 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
                                            uint32_t& untraced) {
     L.alive = 0;
     untraced = 0;
+    float inv_min = __int_as_float(0x7f800000);
 #pragma unroll 1
     for (int p = 0; p < kPrimRays; ++p) {
         const int row = row0 + p;
@@ -463,12 +499,13 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
         }
         // unit direction of the common-origin test (rtc::primary_arm), here in the rolled loop: parked in the slots
         // of the nearest hit, which are initialised when the directions are picked up below
-        float ux, uy, uz;
-        const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz);
+        float ux, uy, uz, inv = __int_as_float(0x7f800000);
+        const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz, &inv);
         if (!ok && (L.alive & (1u << p))) {
             untraced |= 1u << p;
             L.alive &= ~(1u << p);
         }
+        if (L.alive & (1u << p)) inv_min = fminf(inv_min, inv);
         float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
         dp[0] = d.x; dp[kPrimThreads] = d.y; dp[2 * kPrimThreads] = d.z;
         dp[3 * kPrimThreads] = o.x; dp[4 * kPrimThreads] = o.y; dp[5 * kPrimThreads] = o.z;
@@ -485,6 +522,8 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
         dp[6 * kPrimThreads] = kTMax;
         dp[7 * kPrimThreads] = __int_as_float(-1);
     }
+    L.bt_max = kTMax;
+    L.near_scale = rtc::primary_near_scale(inv_min);   // (+inf without traced rays: nothing to cull for)
 }
 
 // Axis and chord bound of the warp's tile (rt_core.cuh, "Tile level"): bounding box of the traced rays' unit
@@ -536,13 +575,54 @@ struct PrimTree {
     uint32_t first_leaf, n_entry;
 };
 
-__device__ __forceinline__ void prim_scan_list(const float4* __restrict__ s_rec, const uint32_t* __restrict__ s_idx, int n_list,
-                                               float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
-                                               uint32_t& untraced, uint32_t& exact_tests) {
+// Nearest first: the warp sorts its listed spheres by rtc::primary_near (32 at a time, rank by counting), so that the
+// hits found early beat most of what follows (prim_scan_list).  Any order gives the same image.
+__device__ __forceinline__ void prim_sort_list(float4* __restrict__ s_rec, uint32_t* __restrict__ s_idx, float* __restrict__ s_near,
+                                               int n_list, int lane) {
+#pragma unroll 1
+    for (int c0 = 0; c0 < n_list; c0 += 32) {
+        const int m = min(32, n_list - c0);
+        if (m > 1) {
+            const bool mine = lane < m;
+            const float4 rec = mine ? s_rec[c0 + lane] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            const uint32_t idx = mine ? s_idx[c0 + lane] : 0u;
+            const float key = mine ? s_near[c0 + lane] : 0.0f;
+            int rank = 0;
+#pragma unroll 1
+            for (int j = 0; j < m; ++j) {
+                const float kj = __shfl_sync(kFull, key, j);
+                rank += (kj < key || (kj == key && j < lane)) ? 1 : 0;
+            }
+            __syncwarp();
+            if (mine) {
+                s_rec[c0 + rank] = rec;
+                s_idx[c0 + rank] = idx;
+                s_near[c0 + rank] = key;
+            }
+            __syncwarp();
+        }
+    }
+}
+
+__device__ __forceinline__ void prim_scan_list(float4* __restrict__ s_rec, uint32_t* __restrict__ s_idx, float* __restrict__ s_near,
+                                               int n_list, float* __restrict__ s_d, const UpdateParams& P, PrimLanes& L,
+                                               uint32_t& untraced, uint32_t& exact_tests, int lane) {
     if (n_list == 0) return;
+    const bool sorted = RT_PRIM_CULL && n_list >= RT_PRIM_SORT_MIN && n_list <= RT_PRIM_SORT_MAX;
+    if (sorted) prim_sort_list(s_rec, s_idx, s_near, n_list, lane);
     float4 rec = s_rec[0];
 #pragma unroll 1
     for (int e = 0; e < n_list; ++e) {
+        // already beaten for every ray of the strip (rt_core.cuh, primary_near); within a 32-entry run the bounds
+        // ascend, so once the whole warp says so the rest of the run is skipped as well
+        const bool beaten = RT_PRIM_CULL && s_near[e] * L.near_scale > L.bt_max;
+        if (sorted && __all_sync(kFull, beaten)) {
+            const int next = ((e >> 5) + 1) << 5;
+            if (next >= n_list) break;
+            e = next - 1;
+            rec = s_rec[next];
+            continue;
+        }
         const float4 recn = s_rec[e + 1];   // (one readable slot past the list)
         const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
                      sw = make_float2(rec.w, rec.w);
@@ -558,14 +638,14 @@ __device__ __forceinline__ void prim_scan_list(const float4* __restrict__ s_rec,
 #pragma unroll
             for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
             cand &= L.alive;
-            if (cand) prim_exact(cand, (int)s_idx[e], s_d, P, L, untraced, exact_tests);
+            if (cand && !beaten) prim_exact(cand, (int)s_idx[e], s_d, P, L, untraced, exact_tests);
         }
         rec = recn;
     }
 }
 
 __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __restrict__ s_work, float4* __restrict__ s_rec,
-                                               uint32_t* __restrict__ s_idx, f3 m, float chord, float* __restrict__ s_d,
+                                               uint32_t* __restrict__ s_idx, float* __restrict__ s_near, f3 m, float chord, float* __restrict__ s_d,
                                                const UpdateParams& P, PrimLanes& L, uint32_t& untraced, uint32_t& exact_tests,
                                                int lane) {
     const unsigned lt = (1u << lane) - 1u;
@@ -612,16 +692,17 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
             const int j = n_list + __popc(bl & lt);
             s_rec[j] = r;   // the sphere's record travels with it: the scan reads shared memory only
             s_idx[j] = lk;
+            if (RT_PRIM_CULL) s_near[j] = rtc::primary_near(r.x, r.y, r.z, r.w);
         }
         n_list += __popc(bl);
         __syncwarp();
         if (n_list > kPrimList - 32) {   // no room for another step's spheres: scan what is listed
-            prim_scan_list(s_rec, s_idx, n_list, s_d, P, L, untraced, exact_tests);
+            prim_scan_list(s_rec, s_idx, s_near, n_list, s_d, P, L, untraced, exact_tests, lane);
             n_list = 0;
             __syncwarp();
         }
     }
-    prim_scan_list(s_rec, s_idx, n_list, s_d, P, L, untraced, exact_tests);
+    prim_scan_list(s_rec, s_idx, s_near, n_list, s_d, P, L, untraced, exact_tests, lane);
     __syncwarp();   // the lists are rewritten by the next tile
 }
 
@@ -668,17 +749,10 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 int best_i = __float_as_int(dp[7 * kPrimThreads]);
                 if (untraced & (1u << p)) {
                     // outside primary_arm's window: the reference loop itself (compute_shader.wgsl:164-180)
-                    const float a = rtc::dot(r.d, r.d);
-                    best_t = kTMax;
-                    best_i = -1;
-                    for (uint32_t si = 0; si < P.n_spheres; ++si) {
-                        const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + si));
-                        float root;
-                        if (rtc::sphere_root(r.o, r.d, a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, best_t, &root)) {
-                            best_t = root;
-                            best_i = (int)si;
-                        }
-                    }
+                    const float2 hit = retrace_sequential(P.spheres, P.n_spheres, r.o.x, r.o.y, r.o.z, r.d.x, r.d.y, r.d.z,
+                                                          rtc::dot(r.d, r.d));
+                    best_t = hit.x;
+                    best_i = __float_as_int(hit.y);
                 }
                 ++rays;
                 f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
@@ -693,6 +767,8 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 n += 1u;
             }
             *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
+            // the frame's RGBA8 image in the same pass when asked for (rt_set_rgba8_output): 128 B contiguous per warp row
+            if (P.rgba8_out) P.rgba8_out[(size_t)row * P.width + x] = quant_texel(make_float4(mean.x, mean.y, mean.z, 0.0f));
         }
     }
 }
@@ -745,12 +821,14 @@ template <bool kShade>
 __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
-    // per warp: [kPrimList + 4] float4 records of the listed spheres, [kPrimList + 4] their indices, [kPrimWork] nodes
+    // per warp: [kPrimList + 4] float4 records of the listed spheres, [kPrimList + 4] their indices, as many
+    // nearest-distance bounds, [kPrimWork] nodes
     uint32_t* s_warp = reinterpret_cast<uint32_t*>(s_dyn) + kPrimRays * kPrimSlots * kPrimThreads +
-                       (threadIdx.x >> 5) * (5 * (kPrimList + 4) + kPrimWork);
+                       (threadIdx.x >> 5) * (6 * (kPrimList + 4) + kPrimWork);
     float4* s_rec = reinterpret_cast<float4*>(s_warp);
     uint32_t* s_idx = s_warp + 4 * (kPrimList + 4);
-    uint32_t* s_work = s_idx + (kPrimList + 4);
+    float* s_near = reinterpret_cast<float*>(s_idx + (kPrimList + 4));
+    uint32_t* s_work = s_idx + 2 * (kPrimList + 4);
     const int lane = threadIdx.x & 31;
 
     const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
@@ -789,7 +867,7 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
             f3 m;
             float chord;
             prim_tile_bound(L, m, chord);
-            prim_tree_walk(T, s_work, s_rec, s_idx, m, chord, s_d, P, L, untraced, exact_tests, lane);
+            prim_tree_walk(T, s_work, s_rec, s_idx, s_near, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
         prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
     }
@@ -1099,22 +1177,6 @@ __device__ __forceinline__ TreeView tree_view(const void* blob, uint32_t n_nodes
     tv.stack_cap = (int)stack_cap;
     tv.entry_r = entry_r;
     return tv;
-}
-
-// The reference loop itself (compute_shader.wgsl:164-180) for a ray whose tree traversal met a NaN root.
-__device__ __noinline__ float2 retrace_sequential(const GpuSphere* __restrict__ spheres, uint32_t n_spheres, float ox, float oy,
-                                                  float oz, float dx, float dy, float dz, float a) {
-    float bt = kTMax;
-    int bi = -1;
-    for (uint32_t si = 0; si < n_spheres; ++si) {
-        const float4 g = __ldg(reinterpret_cast<const float4*>(spheres + si));
-        float root;
-        if (rtc::sphere_root(rtc::mk(ox, oy, oz), rtc::mk(dx, dy, dz), a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, bt, &root)) {
-            bt = root;
-            bi = (int)si;
-        }
-    }
-    return make_float2(bt, __int_as_float(bi));
 }
 
 // One exact test per lane and iteration: every lane works on its own (sphere, ray) candidate, so the reference
@@ -1575,15 +1637,6 @@ __global__ void prep_geometry_kernel(const GpuSphere* __restrict__ spheres, floa
     geom[i] = make_float4(s.position.x, s.position.y, s.position.z, rtc::broad_record_k(s));
 }
 
-// Linear RGBA8 of the running mean: q(x) = floor(clamp(x, 0, 1) * 255 + 0.5), alpha 255.
-__device__ __forceinline__ unsigned quant1(float v) {
-    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
-    float q = floorf(v * 255.0f + 0.5f);
-    return (q == q) ? (unsigned)q : 0u;
-}
-__device__ __forceinline__ unsigned quant_texel(float4 t) {
-    return quant1(t.x) | (quant1(t.y) << 8) | (quant1(t.z) << 16) | 0xFF000000u;
-}
 __global__ void quantize_kernel(const float4* __restrict__ accum, uint32_t* __restrict__ rgba8, uint64_t n_texels) {
     // four texels per thread: 64 B in, one 16 B store out
     const uint64_t i4 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -1684,7 +1737,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 static size_t prim_smem_bytes() {
     return (size_t)kPrimRays * kPrimSlots * kPrimThreads * sizeof(float) +
-           (size_t)(kPrimThreads / 32) * (5 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
+           (size_t)(kPrimThreads / 32) * (6 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
 }
 
 static size_t bounce_smem_bytes() {
@@ -1723,6 +1776,10 @@ cudaError_t configure_kernels() {
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
+}
+
+bool fused_shade_applies(const UpdateParams& p, int variant) {
+    return (variant == 0 || variant >= 4) && primary_pass_applies(p) && rtc::f2u(p.cam.max_depth) == 1u;
 }
 
 bool primary_pass_applies(const UpdateParams& p) {

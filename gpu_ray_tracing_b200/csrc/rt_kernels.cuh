@@ -28,7 +28,16 @@ constexpr int kPrimTail = 8;        // readable slots after the padded record ar
 #define RT_PRIM_CTAS 2
 #endif
 #ifndef RT_PRIM_LIST
-#define RT_PRIM_LIST 64
+#define RT_PRIM_LIST 48
+#endif
+#ifndef RT_PRIM_SORT_MIN
+#define RT_PRIM_SORT_MIN 2
+#endif
+#ifndef RT_PRIM_CULL
+#define RT_PRIM_CULL 1
+#endif
+#ifndef RT_PRIM_SORT_MAX
+#define RT_PRIM_SORT_MAX 16
 #endif
 #ifndef RT_PRIM_WORK
 #define RT_PRIM_WORK 224
@@ -78,6 +87,7 @@ struct UpdateParams {
     // cl_global: cl_bytes == 0 but the bounce kernel can walk the tree in global memory (node numbers fit 16 bits)
     uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry, cl_global;
     float cl_entry_r;
+    uint32_t* rgba8_out;            // non-null: the fused shading pass (max_depth 1) also stores the texel's RGBA8 here
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };
 
@@ -86,6 +96,8 @@ struct UpdateParams {
 //          3 = tiled broad phase streaming sphere chunks through shared memory.
 cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream, int* launches = nullptr);
 bool primary_pass_applies(const UpdateParams& p);
+// max_depth == 1 behind a primary pass: primary_hits_kernel<true> finishes the texels (and honours p.rgba8_out)
+bool fused_shade_applies(const UpdateParams& p, int variant);
 // variant 4 = common-origin primary pass followed by the update kernel (chosen by variant 0 whenever the camera is
 // a pinhole, defocus_angle <= 0); p.prim / p.first_hit must be set.
 cudaError_t launch_prep_primary_tree(const UpdateParams& p, cudaStream_t stream);

@@ -164,6 +164,10 @@ RT_API int rt_read_rgba8(RtRenderer* r, uint8_t* host_rgba8);
  * first on the device. */
 RT_API int rt_read_rgba8_async(RtRenderer* r, uint8_t* host_rgba8);
 RT_API int rt_read_wait(RtRenderer* r);   /* every asynchronous read issued so far has landed */
+/* enable != 0: updates whose shading is finished inside the primary pass (max_depth == 1) also store the frame's RGBA8
+ * image, into the buffer the next rt_read_rgba8_async sends, so that read needs no quantise pass of its own (one kernel
+ * less per frame, 166 MB less HBM traffic at 4K).  Other updates and reads behave as before.  Off by default. */
+RT_API int rt_set_rgba8_output(RtRenderer* r, int enable);
 /* Device buffers that other processes can write into.  A multi-process run (one process per GPU) keeps its gather
  * target in one process (rt_device_alloc + rt_ipc_export), the others map it (rt_ipc_open, peer access enabled
  * lazily) and hand the mapped address to rt_read_rgba8_async, whose destination may be pinned host memory or device

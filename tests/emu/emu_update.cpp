@@ -7,6 +7,8 @@
 // Built with -ffp-contract=off; fmaf() is the IEEE fused operation, as FFMA is on the GPU.
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
+#include <utility>
 #include <vector>
 #ifdef _OPENMP
 #include <omp.h>
@@ -63,6 +65,8 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
     // records that survive the tile test.  tile_cand[tile * count + s] != 0 <=> record s is scanned for that tile.
     const uint32_t tiles_x = (width + 31u) / 32u, tiles_y = (row_count + 7u) / 8u;
     std::vector<uint8_t> tile_cand(primary ? (size_t)tiles_x * tiles_y * count : 0);
+    // ... and the same records as the warp scans them: nearest first by rtc::primary_near (rtk::prim_sort_list)
+    std::vector<std::vector<std::pair<float, uint32_t>>> tile_list(primary ? (size_t)tiles_x * tiles_y : 0);
     if (primary) {
         const uint32_t spp_e = rtc::f2u(cam.samples_per_pixel);
         const bool reset_e = cam.camera_has_moved > 0.5f;
@@ -114,24 +118,29 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                     if (!rtc::primary_tile_candidate(rec[0], rec[1], rec[2], rec[3], m, chord)) continue;
                     if (node >= tree.first_leaf) {
                         tile_cand[(size_t)tile * count + lk] = 1;
+                        tile_list[(size_t)tile].push_back({rtc::primary_near(rec[0], rec[1], rec[2], rec[3]), lk});
                         ++tile_pairs;
                     } else {
                         work.push_back(lk);
                     }
                 }
             }
+            std::stable_sort(tile_list[(size_t)tile].begin(), tile_list[(size_t)tile].end(),
+                             [](const std::pair<float, uint32_t>& x, const std::pair<float, uint32_t>& y) { return x.first < y.first; });
         }
     }
     const uint32_t seed_bits = rtc::f2u(cam.random_seed * 4294967296.0f);
     const uint32_t spp = rtc::f2u(cam.samples_per_pixel);
     const uint32_t max_depth = rtc::f2u(cam.max_depth);
     const bool reset = cam.camera_has_moved > 0.5f;
-    uint64_t rays = 0, exact = 0, violations = 0;
+    uint64_t rays = 0, exact = 0, violations = 0, beaten = 0;
 #ifdef _OPENMP
-#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, prim_rays, untraced, tile_dropped, cluster_rays, cluster_tests, member_tests, retraced)
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : rays, exact, violations, beaten, prim_rays, untraced, tile_dropped, cluster_rays, cluster_tests, member_tests, retraced)
 #endif
     for (int64_t row = 0; row < (int64_t)row_count; ++row) {
         const int y_abs = (int)(row_begin + row);
+        std::vector<uint32_t> stamp(primary ? count : 0, 0u);   // [s] == ray number: s went through (or was culled before) the exact test
+        uint32_t ray_no = 0;
         for (uint32_t x = 0; x < width; ++x) {
             float* texel = accum + ((size_t)row * width + x) * 4;
             f3 mean = rtc::mk(texel[0], texel[1], texel[2]);
@@ -148,25 +157,49 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                     const rtc::BroadRay b = rtc::broad_arm(r.o, r.d, a);
                     float best_t = 3.4e35f;
                     int best_i = -1;
-                    float pux, puy, puz;
+                    float pux, puy, puz, inv_len = 0.0f;
                     const bool use_primary = primary && i == 0;
-                    if (use_primary && rtc::primary_arm(r.d, a, &pux, &puy, &puz)) {
+                    if (use_primary && rtc::primary_arm(r.d, a, &pux, &puy, &puz, &inv_len)) {
                         ++prim_rays;
-                        const uint8_t* tc = &tile_cand[((size_t)(row / 8) * tiles_x + x / 32u) * count];
+                        ++ray_no;
+                        const size_t tile = (size_t)(row / 8) * tiles_x + x / 32u;
+                        const uint8_t* tc = &tile_cand[tile * count];
+                        // the kernel culls with the smallest 1/|d| and the farthest hit of a strip of 8 rays; this ray's own
+                        // values cull at least as much, so the audit below covers every cull the kernel can make
+                        const float near_scale = rtc::primary_near_scale(inv_len);
                         bool nan_root = false;
+                        for (const std::pair<float, uint32_t>& item : tile_list[tile]) {   // nearest first
+                            const uint32_t s = item.second;
+                            const GpuSphere& sp = spheres[s];
+                            const float* rec = &prim[(size_t)s * 4];
+                            if (!rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz))) continue;
+                            stamp[s] = ray_no;
+                            if (item.first * near_scale > best_t) {   // already beaten (rtk::prim_scan_list)
+                                ++beaten;
+                                float root;
+                                if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root) &&
+                                    !(root > best_t))
+                                    ++violations;   // ... but the reference's root is not beyond the hit held (NaN included)
+                                continue;
+                            }
+                            ++exact;
+                            float root;
+                            if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root) &&
+                                root < item.first * near_scale)
+                                ++violations;   // the bound primary_near rests on fails for a root the reference accepts
+                                                // (a NaN root belongs to an always-record, whose bound is 0: never culled)
+                            if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)s, &best_t, &best_i))
+                                nan_root = true;
+                        }
                         for (uint32_t s = 0; s < count; ++s) {
+                            if (stamp[s] == ray_no) continue;
                             const GpuSphere& sp = spheres[s];
                             const float* rec = &prim[(size_t)s * 4];
                             float root;
                             const bool ray_cand = rtc::primary_candidate(rtc::primary_h(rec[0], rec[1], rec[2], rec[3], pux, puy, puz));
                             if (ray_cand && !tc[s]) ++tile_dropped;   // expected 0: the tile level keeps what any ray test keeps
-                            if (ray_cand && tc[s]) {
-                                ++exact;
-                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)s, &best_t, &best_i))
-                                    nan_root = true;
-                            } else if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root)) {
+                            if (rtc::sphere_root(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, &root))
                                 ++violations;   // rejected a sphere the reference hits inside the original (tmin, tmax)
-                            }
                         }
                         if (nan_root) {   // the kernel hands such a ray to its sequential fallback
                             best_t = 3.4e35f;
@@ -267,6 +300,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
         }
     }
     if (stats) {
+        stats[12] = beaten;
         stats[0] = rays; stats[1] = exact; stats[2] = violations; stats[3] = prim_rays; stats[4] = untraced;
         stats[5] = tile_pairs; stats[6] = tile_dropped;
         stats[11] = tile_steps;

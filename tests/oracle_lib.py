@@ -107,11 +107,11 @@ def emu_update(camera, scene, width, height, accum=None, row_begin=0, row_count=
         row_count = height - row_begin
     if accum is None:
         accum = np.zeros((row_count, width, 4), dtype=np.float32)
-    stats = np.zeros(12, dtype=np.uint64)
+    stats = np.zeros(13, dtype=np.uint64)
     emu().emu_update(C.byref(camera), _p(scene.spheres), scene.count, width, height, row_begin, row_count,
                      _p(accum), _p(stats), variant)
     EMU_STATS.update(primary_rays=int(stats[3]), untraced=int(stats[4]), tile_pairs=int(stats[5]), tile_dropped=int(stats[6]),
-                     cluster_rays=int(stats[7]), cluster_tests=int(stats[8]), member_tests=int(stats[9]), retraced=int(stats[10]), tile_steps=int(stats[11]))
+                     cluster_rays=int(stats[7]), cluster_tests=int(stats[8]), member_tests=int(stats[9]), retraced=int(stats[10]), tile_steps=int(stats[11]), beaten=int(stats[12]))
     return accum, int(stats[0]), int(stats[1]), int(stats[2])
 
 

@@ -318,6 +318,43 @@ def test_bounce_path_selection():
             assert nodes > scene.count // 8 and depth >= 2 and path == want, (scene.count, variant, nodes, depth, path)
 
 
+def test_fused_rgba8_output():
+    """rt_set_rgba8_output: depth-1 updates write the RGBA8 frame themselves; asynchronous reads of progressive frames,
+    of a deep frame in between (quantise kernel again) and after rt_init equal the blocking read every time, and the
+    fused frames cost no extra kernel."""
+    import torch
+    W, H = 250, 131
+    scene = scenes.random_scene(300)
+    host = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        r.set_rgba8_output(True)
+        seq = [(1, 1), (1, 0), (1, 0), (4, 1), (1, 1), (1, 0)]     # (max_depth, camera_has_moved)
+        for i, (depth, moved) in enumerate(seq):
+            cam = scenes.camera(W, H, max_depth=depth, spp=8, random_seed=(i + 1) / 16.0, moved=moved)
+            before = r.kernel_launches()
+            r.update(cam)
+            r.read_rgba8_async_into(host[i & 1].data_ptr())
+            used = r.kernel_launches() - before
+            r.read_wait()
+            want = r.read_rgba8()
+            assert np.array_equal(host[i & 1].numpy(), want), (i, depth)
+            if depth == 1:
+                assert used == 2, used      # per-frame records + primary pass, no quantise kernel
+        r.init()
+        r.read_rgba8_async_into(host[0].data_ptr())
+        r.read_wait()
+        assert not host[0].numpy()[..., :3].any() and (host[0].numpy()[..., 3] == 255).all()
+        # against the oracle's quantisation of its own image
+        cam = scenes.camera(W, H, max_depth=1, spp=1)
+        r.update(cam)
+        r.read_rgba8_async_into(host[1].data_ptr())
+        r.read_wait()
+        cpu, _ = ol.oracle_update(cam, scene, W, H)
+        assert np.array_equal(host[1].numpy(), ol.quantize(cpu))
+
+
 def test_async_read_into_device_memory():
     """rt_read_rgba8_async with a DEVICE destination (what a peer process maps through CUDA IPC in bench.py --gpus N):
     the copy lands in a buffer from rt_device_alloc and equals the blocking host read."""
