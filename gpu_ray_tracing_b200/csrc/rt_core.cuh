@@ -34,18 +34,20 @@ RT_DEV f3 add(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 RT_DEV f3 sub(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
 RT_DEV f3 mul(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 RT_DEV f3 scale(float s, f3 a) { return mk(s * a.x, s * a.y, s * a.z); }
-// The IEEE divisions (and the square root of normalize) expand to ~12 instructions each plus a slow-path call; the
-// kernels' instruction footprint is what limits them, so on the device the three-way division
-// and normalize exist ONCE, out of line, instead of once per call site.  Same operations, same results.
+RT_DEV f3 divs(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+RT_DEV f3 neg(f3 a) { return mk(-a.x, -a.y, -a.z); }
+RT_DEV float dot(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+RT_DEV f3 normalize(f3 a) { return divs(a, sqrtf(dot(a, a))); }
+// An IEEE square root and three IEEE divisions expand to ~45 instructions plus slow-path calls, and the kernels'
+// instruction footprint is what limits them: the metal and dielectric branches of scatter,
+// which a minority of the rays take, share ONE out-of-line copy on the device.  (Every ray's own divisions — sky
+// colour, running mean, outward normal — stay inline: there the call costs more than the footprint.)
 #if defined(__CUDACC__) && !defined(RT_INLINE_DIVS)
 #define RT_DEV_SHARED static __host__ __device__ __noinline__
 #else
 #define RT_DEV_SHARED RT_DEV
 #endif
-RT_DEV_SHARED f3 divs(f3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
-RT_DEV f3 neg(f3 a) { return mk(-a.x, -a.y, -a.z); }
-RT_DEV float dot(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-RT_DEV_SHARED f3 normalize(f3 a) {
+RT_DEV_SHARED f3 normalize_shared(f3 a) {
     const float s = sqrtf(dot(a, a));
     return mk(a.x / s, a.y / s, a.z / s);
 }
@@ -166,8 +168,8 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
     } else if (w <= 1.0f) {
         // metal_scatter, compute_shader.wgsl:95-100; reflect(e1,e2) = e1 - 2 dot(e2,e1) e2
         f3 refl = sub(d, scale(2.0f * dot(n, d), n));
-        f3 reflected = add(normalize(refl), scale(w, random_unit_vector(bounce_seed)));
-        out.d = normalize(reflected);
+        f3 reflected = add(normalize_shared(refl), scale(w, random_unit_vector(bounce_seed)));
+        out.d = normalize_shared(reflected);
         *factor = mul(*factor, albedo);
         *ray = out;
         return dot(reflected, n) > 0.0f;
@@ -175,7 +177,7 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
         // dielectric_scatter + reflectance, compute_shader.wgsl:102-141
         float ior = sp.color[0];
         float ratio = front ? (1.0f / ior) : ior;
-        f3 ud = normalize(d);
+        f3 ud = normalize_shared(d);
         float cos_theta = fminf(dot(neg(ud), n), 1.0f);
         float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
         bool cannot_refract = ratio * sin_theta > 1.0f;
@@ -196,7 +198,7 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
                 dir = sub(scale(ratio, ud), scale(ratio * dn + sqrtf(k), n));
             }
         }
-        out.d = normalize(dir);
+        out.d = normalize_shared(dir);
         // attenuation = vec3(1.0): color_factor *= 1.0 is exact, skipped
         *ray = out;
         return true;
@@ -398,14 +400,17 @@ RT_DEV float primary_tile_e2(float ux, float uy, float uz, f3 m) {
 // e2max: the largest primary_tile_e2 over the tile's traced rays.  Returns the chord bound k.
 RT_DEV float primary_tile_chord(float e2max) { return sqrtf(e2max) * 1.0009765625f + 3.814697265625e-06f; }
 // A NaN anywhere (degenerate axis) and k >= 1 (a tile wider than 60 degrees) keep the record.
-RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m, float k) {
-    if (!(k < 1.0f)) return true;
+// *near_out (optional): primary_near of the record (below), from the same |oc| and R.
+RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m, float k, float* near_out = nullptr) {
     const float q = -rw;
     const float t = fmaf(rx, m.x, fmaf(ry, m.y, rz * m.z));
     const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
     const float R = sqrtf(fmaxf(fmaf(n2, 1.000003814697265625f, -((q * q) * 0.999996185302734375f)), 0.0f));
+    const float len = sqrtf(n2);
+    if (near_out) *near_out = fmaf(-R, 1.0009765625f, len * 0.998046875f);
+    if (!(k < 1.0f)) return true;
     const float ce = fmaf(-0.5f * k, k, 1.0f);
-    const float lhs = fmaf(sqrtf(n2), 3.814697265625e-06f, fmaf(R, k, fmaf(-q, ce, t)));
+    const float lhs = fmaf(len, 3.814697265625e-06f, fmaf(R, k, fmaf(-q, ce, t)));
     return !(lhs < 0.0f);
 }
 

@@ -675,13 +675,14 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
         bool keep = false, leaf = false;
         uint32_t lk = 0xFFFFFFFFu;
         float4 r = make_float4(0.0f, 0.0f, 0.0f, -1.0f);
+        float near = 0.0f;   // rtc::primary_near of the child's record
         if (g < take) {
             const uint32_t node = s_work[n_work + g];
             lk = T.link[node * kTreeWide + k];
             leaf = node >= T.first_leaf;
             if (lk != 0xFFFFFFFFu) {
                 r = __ldg(T.rec + node * kTreeStride + k);
-                keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord);
+                keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord, &near);
             }
         }
         __syncwarp();   // the taken entries have been read before their slots are reused
@@ -692,7 +693,7 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
             const int j = n_list + __popc(bl & lt);
             s_rec[j] = r;   // the sphere's record travels with it: the scan reads shared memory only
             s_idx[j] = lk;
-            if (RT_PRIM_CULL) s_near[j] = rtc::primary_near(r.x, r.y, r.z, r.w);
+            if (RT_PRIM_CULL) s_near[j] = near;
         }
         n_list += __popc(bl);
         __syncwarp();
