@@ -352,8 +352,13 @@ def run_ours(args):
     # per step: sphere buffer uploaded from pinned host memory (the reference re-creates its buffers
     # from host memory every frame, src/lib.rs:151-207), the 176-byte camera uniform rides in the
     # kernel parameters, and the frame comes back as RGBA8 into pinned host memory.
-    host_spheres = torch.from_numpy(scene.spheres.view(np.uint8).copy()).pin_memory()
-    host_images = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    # pinned frames are allocated from a thread bound to the GPU's own NUMA node when the box says which that is:
+    # a read-back that crosses the socket interconnect runs at ~39 GB/s instead of ~54 (seen between otherwise equal boxes)
+    with numa_local(local_rank) as numa_note:
+        host_spheres = torch.from_numpy(scene.spheres.view(np.uint8).copy()).pin_memory()
+        host_images = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
+        for t in host_images:
+            t.zero_()          # first touch on this node
     K_e2e = max(3, min(K, 50))
 
     def e2e_step(i):
@@ -418,29 +423,31 @@ def run_ours(args):
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": workload_config(world),
         "roofline": {"bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved_tf / peak_tf, "traffic": 74364160,
+                     "frac": achieved_tf / peak_tf, "traffic": 75208704,
                      "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
                      "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
                      "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
                      "kernel": "primary_hits_kernel<true> (+ prep_primary_tree_kernel, 3 us)",
-                     "ncu": {"source": "profiles/r1_primary_tree_ncu.md (ncu --set full of this kernel on this workload)",
-                             "warp_instructions_per_launch": 287235983, "issue_slots_busy_pct": 66.7,
-                             "pipe_fma_pct": 27.7, "pipe_alu_pct": 35.9, "pipe_xu_pct": 27.1, "stall_no_inst_pct": 5.5,
-                             "dram_bytes_read": 98560, "dram_bytes_written": 74265600},
+                     "ncu": {"source": "profiles/r1_primary_cull_ncu.md (ncu --set full of this kernel on this workload)",
+                             "warp_instructions_per_launch": 247215710, "issue_slots_busy_pct": 76.0,
+                             "pipe_fma_pct": 33.5, "pipe_alu_pct": 39.2, "pipe_xu_pct": 29.5, "stall_no_inst_pct": 8.7,
+                             "dram_bytes_read": 94464, "dram_bytes_written": 75114240},
                      "note": "achieved/frac count the reference's 18 flop per (ray, sphere) test over all N spheres (SURVEY.md "
                              "8(d)).  The kernel reaches the same nearest hit without doing that work: each 32x8 pixel tile "
                              "walks an 8-wide tree of bounding spheres with one conservative test per node, the rays of the "
-                             "tile run a 3-FFMA sign test on the ~6 surviving spheres and the reference quadratic on their "
-                             "candidates, so frac exceeds 1.  What is left is per-ray scalar work that bit-exactness fixes "
+                             "tile run a 3-FFMA sign test on the ~6 surviving spheres, nearest first, and the reference quadratic on "
+                             "their candidates until every ray of a strip holds a nearer hit (2.1 exact tests per ray), so frac "
+                             "exceeds 1.  What is left is per-ray scalar work that bit-exactness fixes "
                              "(IEEE division / sqrt / the pinned sin-cos of get_ray and scatter): the kernel is issue-bound "
                              "(ncu block), not FMA- or HBM-bound."},
         "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_launch": hbm_bytes,
-                "note": "one float4 accumulator store per pixel (camera_has_moved = 1: no read); ncu sees 74 MB of it reach DRAM inside the launch, the rest is still in the 126 MB L2"},
+                "note": "one float4 accumulator store per pixel (camera_has_moved = 1: no read); ncu sees 75 MB of it reach DRAM inside the launch, the rest is still in the 126 MB L2"},
         "cpu_baseline": cpu,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(scene.spheres) * 32 + 176),
                 "d2h_bytes_per_step": W * H * 4, "steps": K_e2e,
+                "pinned_host_memory": str(numa_note),
                 "call": "rt_set_scene + rt_update + rt_read_rgba8_async per frame (two pinned host frames, read-back of "
                         "frame i overlaps the kernel of frame i+1), rt_read_wait before the clock stops",
                 "blocking_read_value": e2e_sync_value, "checksum": checksum},
@@ -451,6 +458,46 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+class numa_local:
+    """Binds the calling thread to the CPUs next to GPU `index` (sysfs local_cpulist of its PCI function) for the
+    duration of the block, so that host memory allocated and first touched inside lands on that NUMA node.
+    Says what it did; does nothing when sysfs or the affinity call are not available."""
+
+    def __init__(self, index):
+        self.index, self.saved, self.note = index, None, "unchanged"
+
+    def __enter__(self):
+        try:
+            import torch
+            pr = torch.cuda.get_device_properties(self.index)
+            bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+            base = f"/sys/bus/pci/devices/{bdf}/"
+            node = open(base + "numa_node").read().strip()
+            cpus = set()
+            for part in open(base + "local_cpulist").read().strip().split(","):
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+            allowed = os.sched_getaffinity(0)
+            use = cpus & allowed
+            if use and use != allowed:
+                self.saved = allowed
+                os.sched_setaffinity(0, use)
+                self.note = f"bound to {len(use)} CPUs of NUMA node {node} ({bdf})"
+            else:
+                self.note = f"NUMA node {node}: {'no local CPU in the cpuset' if not use else 'cpuset already local'}"
+        except Exception as e:   # no sysfs, no permission: allocate where we are
+            self.note = f"unavailable ({type(e).__name__})"
+        return self
+
+    def __exit__(self, *exc):
+        if self.saved is not None:
+            os.sched_setaffinity(0, self.saved)
+        return False
+
+    def __str__(self):
+        return self.note
 
 
 def main():

@@ -272,8 +272,8 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     r->rgba8_fresh = false;
     if (r->rgba8_output && rtk::fused_shade_applies(p, r->variant)) {
         // the slot the next rt_read_rgba8_async will send: its previous copy must have left it
-        if (!r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
         const int b = (int)(r->async_reads & 1u);
+        if (b && !r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
         if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
         p.rgba8_out = reinterpret_cast<uint32_t*>(b ? r->rgba8_alt : r->rgba8);
     }
@@ -327,6 +327,8 @@ int rt_write_accum(RtRenderer* r, const float* host) {
 
 int rt_quantize(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
+    // a fused update (rt_set_rgba8_output) may have written this very buffer already: slot 0 of the asynchronous reads
+    if (r->rgba8_fresh && (r->async_reads & 1u) == 0u) return RT_OK;
     RT_CUDA(rtk::launch_quantize(r->accum, r->rgba8, r->n_texels, r->stream));
     r->launches += 1;
     return RT_OK;

@@ -90,6 +90,8 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
             cudaGetLastError();
         }
     }
+    // the gather sends RGBA8 blocks: depth-1 updates write them in the shading pass (no quantise kernel per shard)
+    for (RtRenderer* s : m->shards) rt_set_rgba8_output(s, 1);
     cudaError_t e = cudaSetDevice(devices[0]);
     if (e == cudaSuccess) e = cudaMalloc(&m->full_rgba8, (size_t)width * height * sizeof(uchar4));
     if (e != cudaSuccess) { rt_multi_destroy(m); return fail_cuda(e, "rt_multi_create"); }

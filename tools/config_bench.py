@@ -68,6 +68,7 @@ def config5(n_dev, reps):
         for r in renderers:
             r.set_scene(scene)
             r.init()
+            r.set_rgba8_output(True)     # the frame that is read back comes out of the shading pass
         best = 1e9
         for rep in range(reps + 1):
             poses = range(POSES) if rep else range(2 * n_dev)     # short warm-up
