@@ -442,9 +442,8 @@ __device__ __forceinline__ float ray_half(const float2& v, int p) { return (p & 
 // Exact tests (the reference quadratic) of sphere `idx` for the rays in `cand`.  The tree hands the spheres over in
 // no particular order, so the nearest hit is kept with rtc::nearest_update (ties to the lower index); a ray that
 // meets a NaN root is handed to the sequential fallback (`untraced`), where the reference's order decides.
-__device__ __forceinline__ void prim_exact(uint32_t cand, int idx, float* __restrict__ s_d, const UpdateParams& P,
-                                           PrimLanes& L, uint32_t& untraced, uint32_t& exact_tests) {
-    const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));   // centre, radius as uploaded
+__device__ __forceinline__ void prim_exact(uint32_t cand, int idx, const float4 g /* centre, radius as uploaded */,
+                                           float* __restrict__ s_d, PrimLanes& L, uint32_t& untraced, uint32_t& exact_tests) {
     const f3 center = rtc::mk(g.x, g.y, g.z);
     // one rolled copy of the quadratic for all eight rays (ray state lives in the thread's shared-memory slots):
     // the kernel's instruction footprint, not its instruction count, is what the profile shows to matter
@@ -624,6 +623,10 @@ __device__ __forceinline__ void prim_scan_list(float4* __restrict__ s_rec, uint3
             continue;
         }
         const float4 recn = s_rec[e + 1];   // (one readable slot past the list)
+        // the sphere as uploaded (exact test operand): a broadcast load issued ahead of the sign tests, which cover its
+        // latency in scenes past L1 (65,536 spheres are 2 MB)
+        const uint32_t idx = s_idx[e];
+        const float4 sph = __ldg(reinterpret_cast<const float4*>(P.spheres + idx));
         const float2 sx = make_float2(rec.x, rec.x), sy = make_float2(rec.y, rec.y), sz = make_float2(rec.z, rec.z),
                      sw = make_float2(rec.w, rec.w);
         float2 h[kPrimRays / 2];
@@ -638,7 +641,7 @@ __device__ __forceinline__ void prim_scan_list(float4* __restrict__ s_rec, uint3
 #pragma unroll
             for (int p = 0; p < kPrimRays; ++p) cand |= rtc::primary_candidate(ray_half(h[p >> 1], p)) ? (1u << p) : 0u;
             cand &= L.alive;
-            if (cand && !beaten) prim_exact(cand, (int)s_idx[e], s_d, P, L, untraced, exact_tests);
+            if (cand && !beaten) prim_exact(cand, (int)idx, sph, s_d, L, untraced, exact_tests);
         }
         rec = recn;
     }
@@ -817,7 +820,8 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 
 // One kernel for any scene size: persistent CTAs, every WARP pulls 32 x 8 pixel tiles from an atomic counter on its
 // own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
-// finishes the texels.  Shared memory: the per-ray slots (64 KB) and each warp's work stack and candidate lists.
+// finishes the texels.  Shared memory per warp: the per-ray slots (8 KB) and the warp's work stack and candidate
+// lists (2.1 KB); 2 CTAs of 11 warps per SM (rt_kernels.cuh).
 template <bool kShade>
 __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];

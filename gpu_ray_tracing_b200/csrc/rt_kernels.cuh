@@ -19,8 +19,6 @@ constexpr uint32_t kResidentMaxSpheres = 4096;  // 64 KB of shared memory per CT
 constexpr int kPrimRays = 8;
 constexpr int kPrimTileW = 32;
 constexpr int kPrimTileH = 8;
-constexpr int kPrimUnroll = 8;      // records per broad-phase iteration
-constexpr int kPrimTail = 8;        // readable slots after the padded record array (software prefetch)
 #ifndef RT_PRIM_THREADS
 #define RT_PRIM_THREADS 352
 #endif
@@ -48,7 +46,6 @@ constexpr int kPrimThreads = RT_PRIM_THREADS;
 constexpr int kPrimCtas = RT_PRIM_CTAS;
 constexpr int kPrimWork = RT_PRIM_WORK;   // per-warp stack of tree nodes awaiting their tile test (entry list <= 160 + growth)
 constexpr int kPrimList = RT_PRIM_LIST;   // per-warp list of spheres that passed the tile test, scanned when it fills
-constexpr int kPrimChunk = 1024;    // streamed primary pass: records per shared-memory stage (16 KB)
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
 constexpr int kTreeWide = 8;                           // children per node of the bounce rays' tree (rtt::kWide)
