@@ -681,12 +681,11 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
         float near = 0.0f;   // rtc::primary_near of the child's record
         if (g < take) {
             const uint32_t node = s_work[n_work + g];
-            lk = T.link[node * kTreeWide + k];
+            // link and record are fetched side by side (an empty slot holds a readable never-record), not one after the other
+            lk = __ldg(T.link + node * kTreeWide + k);
+            r = __ldg(T.rec + node * kTreeStride + k);
             leaf = node >= T.first_leaf;
-            if (lk != 0xFFFFFFFFu) {
-                r = __ldg(T.rec + node * kTreeStride + k);
-                keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord, &near);
-            }
+            keep = rtc::primary_tile_candidate(r.x, r.y, r.z, r.w, m, chord, &near) && lk != 0xFFFFFFFFu;
         }
         __syncwarp();   // the taken entries have been read before their slots are reused
         const unsigned bi = __ballot_sync(kFull, keep && !leaf), bl = __ballot_sync(kFull, keep && leaf);
