@@ -1316,7 +1316,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
 // costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
 #ifndef RT_WF_COMPLETE_BELOW
-#define RT_WF_COMPLETE_BELOW 32u
+#define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
 #endif
 template <typename CandT>
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
