@@ -458,4 +458,33 @@ RT_DEV bool nearest_update(f3 o, f3 d, float a, f3 center, float radius, float t
     return true;
 }
 
+// The same for rays that start inside the scene (bounce rays): their candidates come from a LINE test, so half of them
+// lie behind the origin, and the reference spends a square root and two divisions on each to reject both roots.
+// With h = oc.d < 0 and c = |oc|^2 - r^2 > 0 as the reference computes them, and a finite discriminant, that outcome
+// is certain without them: fl(a c) >= 0, so disc <= fl(h^2) and sq = fl(sqrt(disc)) <= fl(sqrt(fl(h^2))) = |h| (square
+// root and rounding are monotone), hence h + sq <= 0: the second root is <= 0 < tmin and the first is no larger.
+// (h^2 = inf gives sq = inf and a root >= tmax, rejected as well; only a NaN discriminant, which the reference ACCEPTS
+// with a NaN root, must take the full path — it fails `disc == disc` below.)  Same results, bit for bit.
+RT_DEV bool nearest_update_from_inside(f3 o, f3 d, float a, f3 center, float radius, float tmin, float tmax0, int idx,
+                                       float* best_t, int* best_i) {
+    f3 oc = sub(center, o);
+    float h = dot(oc, d);
+    float c = dot(oc, oc) - radius * radius;
+    float disc = h * h - a * c;
+    if (disc < 0.0f) return true;
+    if (h < 0.0f && c > 0.0f && disc == disc && tmin >= 0.0f) return true;
+    float sq = sqrtf(disc);
+    float root = (h - sq) / a;
+    if (root <= tmin || tmax0 <= root) {
+        root = (h + sq) / a;
+        if (root <= tmin || tmax0 <= root) return true;
+    }
+    if (root != root) return false;
+    if (root < *best_t || (root == *best_t && idx < *best_i)) {
+        *best_t = root;
+        *best_i = idx;
+    }
+    return true;
+}
+
 }  // namespace rtc

@@ -1203,7 +1203,7 @@ __device__ __forceinline__ void drain_candidates(const CandT* __restrict__ s_can
             float bt = second ? L.best_t[1] : L.best_t[0];
             int bi = second ? L.best_i[1] : L.best_i[0];
             ++exact_tests;
-            if (!rtc::nearest_update(o, d, a, rtc::mk(gs.x, gs.y, gs.z), gs.w, kTMin, kTMax, idx, &bt, &bi))
+            if (!rtc::nearest_update_from_inside(o, d, a, rtc::mk(gs.x, gs.y, gs.z), gs.w, kTMin, kTMax, idx, &bt, &bi))
                 nan_rays |= second ? 2u : 1u;
             if (second) {
                 L.best_t[1] = bt;

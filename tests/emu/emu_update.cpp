@@ -245,7 +245,7 @@ void emu_update(const SceneCamera* cam_p, const GpuSphere* spheres, uint32_t cou
                                 const GpuSphere& sp = spheres[link];
                                 ++exact;
                                 tested[link] = 1;
-                                if (!rtc::nearest_update(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)link,
+                                if (!rtc::nearest_update_from_inside(r.o, r.d, a, rtc::mk(sp.position), sp.radius, 0.001f, 3.4e35f, (int)link,
                                                          &best_t, &best_i))
                                     nan_root = true;
                             }
