@@ -407,7 +407,7 @@ RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m,
     const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
     const float R = sqrtf(fmaxf(fmaf(n2, 1.000003814697265625f, -((q * q) * 0.999996185302734375f)), 0.0f));
     const float len = sqrtf(n2);
-    if (near_out) *near_out = fmaf(-R, 1.0009765625f, len * 0.998046875f);
+    if (near_out) *near_out = fmaf(-R, 1.0009765625f, len * 0.99609375f);
     if (!(k < 1.0f)) return true;
     const float ce = fmaf(-0.5f * k, k, 1.0f);
     const float lhs = fmaf(len, 3.814697265625e-06f, fmaf(R, k, fmaf(-q, ce, t)));
@@ -418,8 +418,10 @@ RT_DEV bool primary_tile_candidate(float rx, float ry, float rz, float rw, f3 m,
 // (oc, -q): |oc| - R, R = sqrt(|oc|^2 - q^2) >= r + rho (primary_record), is a lower bound of the distance from any
 // origin on the defocus disk to the sphere's surface, so the reference's accepted root of a ray with direction d is at
 // least (|oc| - R) / |d| — in exact arithmetic.  The reference's float root (h - sqrt(h^2 - a c)) / a is below the
-// exact one by at most sqrt(delta) / a, delta <= 2^-22 h^2 the rounding of its discriminant, i.e. by 2^-11 |oc| / |d|
-// (its other roundings are of order 2^-22); primary_near takes 2^-9 |oc| and 2^-10 R off, four times that.  A sphere
+// exact one by at most sqrt(delta) / a, delta the rounding of its discriminant: h, a and c each carry a few 2^-24 of
+// |oc||d|, |d|^2 and |oc|^2 + r^2, so delta <= 2^-20 |oc|^2 |d|^2 and the root falls short by at most
+// 2^-10 |oc| / |d| (its other roundings are of order 2^-22); primary_near takes 2^-8 |oc| and 2^-10 R off, four times
+// that.  A sphere
 // with  primary_near * (smallest 1/|d| of the rays concerned) * (1 - 2^-12)  >  the nearest hit they all hold
 // cannot win for any of them (first root > best_t >= tmin: it loses or is rejected at tmax; the second root is larger
 // still) and is not tested.  Negative for a camera inside the inflated sphere and 0 for an always-record: never culled.
@@ -427,7 +429,7 @@ RT_DEV float primary_near(float rx, float ry, float rz, float rw) {
     const float q = -rw;
     const float n2 = fmaf(rx, rx, fmaf(ry, ry, rz * rz));
     const float R = sqrtf(fmaxf(fmaf(n2, 1.000003814697265625f, -((q * q) * 0.999996185302734375f)), 0.0f));
-    return fmaf(-R, 1.0009765625f, sqrtf(n2) * 0.998046875f);
+    return fmaf(-R, 1.0009765625f, sqrtf(n2) * 0.99609375f);
 }
 RT_DEV float primary_near_scale(float inv_len_min) { return inv_len_min * 0.999755859375f; }
 

@@ -74,6 +74,42 @@ def test_broad_phase_is_conservative_on_adversarial_geometry():
             assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32))
 
 
+def test_nearest_first_cull_on_grazing_chains():
+    """The "already beaten" cull of the primary pass (rtc::primary_near): chains of overlapping spheres strung along
+    the view direction, near and 10,000 units away, seen through narrow fields of view so that most hits are grazing
+    ones — where the reference's own root is least accurate.  The emulation checks the bound against every root the
+    reference accepts and every skipped pair against the final hit: 0 violations, image bit-identical, and the cull
+    does remove tests."""
+    rng = np.random.default_rng(77)
+    culled = 0
+    for dist, radius, fov in ((30.0, 1.0, 8.0), (800.0, 6.0, 2.0), (10000.0, 40.0, 1.0), (10000.0, 3.0, 0.1)):
+        n = 160
+        sp = np.zeros(n, dtype=rt.SPHERE_DTYPE)
+        t = np.sort(rng.uniform(0.3, 1.7, n)) * dist
+        axis = np.array([1.0, 0.1, -0.4]) / np.linalg.norm([1.0, 0.1, -0.4])
+        side = rng.normal(0.0, 0.9 * radius, (n, 3))
+        sp["position"] = (t[:, None] * axis[None, :] + side).astype(np.float32)
+        sp["radius"] = (radius * rng.uniform(0.5, 1.5, n)).astype(np.float32)
+        sp["color"] = rng.uniform(0.1, 1, (n, 4)).astype(np.float32)
+        sp["color"][:, 3] = rng.choice([-2.0, 0.2, 2.0], n)
+        sp["color"][sp["color"][:, 3] == 2.0, 0] = 1.5
+        scene = rt.SphereCollection(sp, n)
+        W, H = 64, 32
+        for defocus in (0.0, 0.6):
+            s = rt.CameraSettings.default()
+            s.max_depth, s.samples_per_pixel, s.camera_has_moved = 1, 1, 1
+            s.look_from = rt.RtVec3(0.0, 0.0, 0.0)
+            s.look_at = rt.RtVec3(*(float(v) for v in axis * dist))
+            s.field_of_view, s.defocus_angle, s.focus_distance = fov, defocus, dist
+            cam = rt.SceneCamera.from_settings(s, W, H, 0.25)
+            cpu, rays = ol.oracle_update(cam, scene, W, H)
+            emu, rays_e, exact, violations = ol.emu_update(cam, scene, W, H, variant=0)
+            assert violations == 0 and rays == rays_e, (dist, defocus, violations)
+            assert np.array_equal(cpu.view(np.uint32), emu.view(np.uint32)), (dist, defocus)
+            culled += ol.EMU_STATS["beaten"]
+    assert culled > 0
+
+
 def test_randomised_scenes_and_cameras_audit():
     """Seeded random scenes (log-uniform radii over 5 decades, clustered and overlapping spheres) seen by random
     cameras — pinhole and wide defocus disks, inside clusters, far away, huge and tiny fields of view: neither broad
