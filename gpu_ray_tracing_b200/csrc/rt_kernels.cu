@@ -709,15 +709,111 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
     __syncwarp();   // the lists are rewritten by the next tile
 }
 
-// kShade = false: write (t, index) per texel to P.first_hit; the update kernel shades and continues the paths.
-// kShade = true (max_depth == 1): the whole `update` for the texel is finished here — scatter once for the
-//          attenuation and the outgoing direction, sky colour, running mean, store (compute_shader.wgsl:267-296,
-//          356-363) — and no second kernel runs.
-template <bool kShade>
+// Running mean and texel store for a finished path (compute_shader.wgsl:356-363).
+__device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t texel_index, uint32_t n, f3 color, bool reset) {
+    float4* texel = &P.accum[texel_index];
+    f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
+    if (!reset) {
+        const float4 t = *texel;
+        mean = rtc::mk(t.x, t.y, t.z);
+    }
+    mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+    *texel = make_float4(mean.x, mean.y, mean.z, (float)(n + 1u));
+}
+
+// Warp-aggregated append of one path per pushing lane.  Every lane of the warp must call this.
+__device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_bounce, bool push, f3 o, f3 d, f3 factor,
+                                          uint32_t texel_index, uint32_t bseed, uint32_t n, int lane) {
+    const unsigned m = __ballot_sync(kFull, push);
+    if (m == 0u) return;
+    const int leader = __ffs((int)m) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&P.wf_counts[next_bounce], (unsigned)__popc(m));
+    base = __shfl_sync(kFull, base, leader);
+    if (push) {
+        const uint32_t j = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+        float4* q = P.wf_queue[next_bounce & 1u];
+        q[j] = make_float4(o.x, o.y, o.z, d.x);
+        q[(size_t)P.wf_capacity + j] = make_float4(d.y, d.z, factor.x, factor.y);
+        q[2 * (size_t)P.wf_capacity + j] =
+            make_float4(factor.z, __uint_as_float(texel_index), __uint_as_float(bseed), __uint_as_float(n));
+    }
+}
+
+// What happens to a traced ray (compute_shader.wgsl:267-296): returns true when the path continues (then o, d,
+// factor are the scattered ray), false when the texel has been finished.
+__device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
+                                            f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
+                                            bool reset) {
+    if (best_i < 0) {
+        finalize_texel(P, texel_index, n, rtc::sky_times(factor, d), reset);
+        return false;
+    }
+    const GpuSphere sp = load_sphere(P.spheres, best_i);
+    rtc::Ray r;
+    r.o = o;
+    r.d = d;
+    const bool ok = rtc::scatter(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
+    if (!ok) {
+        finalize_texel(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
+        return false;
+    }
+    if (last) {
+        finalize_texel(P, texel_index, n, rtc::sky_times(factor, r.d), reset);
+        return false;
+    }
+    o = r.o;
+    d = r.d;
+    return true;
+}
+
+// kMode = kPrimHits:  write (t, index) per texel to P.first_hit; the update kernel shades and continues the paths
+//         (in-kernel bounce loop, max_depth > kWfMaxDepth).
+// kMode = kPrimShade (max_depth == 1): the whole `update` for the texel is finished here — scatter once for the
+//         attenuation and the outgoing direction, sky colour, running mean, store (compute_shader.wgsl:267-296,
+//         356-363) — and no second kernel runs.
+// kMode = kPrimQueue (wavefront, 1 < max_depth <= kWfMaxDepth): the first hit is resolved here as well — texel finished
+//         (miss, absorbed) or the scattered path appended to queue 1 (resolve_hit + push_path, what shade_first_kernel
+//         did from P.first_hit in a pass of its own: 8 B written and read back per texel, every ray generated twice).
+constexpr int kPrimHits = 0, kPrimShade = 1, kPrimQueue = 2;
+template <int kMode>
 __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
                                             const PrimLanes& L, uint32_t untraced, uint32_t seed_bits, bool reset,
                                             uint32_t& rays) {
-    if constexpr (!kShade) {
+    if constexpr (kMode == kPrimQueue) {
+        const uint32_t sampling = L.alive | untraced;
+        const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+        const int lane = threadIdx.x & 31;
+#pragma unroll 1
+        for (int p = 0; p < kPrimRays; ++p) {   // every lane takes every turn: push_path is a warp-wide append
+            const int row = row0 + p;
+            bool push = false;
+            f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = rtc::mk(1.0f, 1.0f, 1.0f);
+            uint32_t bseed = 0, n = 0, texel_index = 0;
+            if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
+                texel_index = (uint32_t)row * P.width + (uint32_t)x;
+                if (!reset) n = rtc::f2u(P.accum[texel_index].w);
+                if (sampling & (1u << p)) {
+                    const float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+                    d = rtc::mk(dp[0], dp[kPrimThreads], dp[2 * kPrimThreads]);
+                    o = rtc::mk(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads]);
+                    float best_t = dp[6 * kPrimThreads];
+                    int best_i = __float_as_int(dp[7 * kPrimThreads]);
+                    if (untraced & (1u << p)) {   // outside primary_arm's window: the reference loop itself
+                        const float2 hit = retrace_sequential(P.spheres, P.n_spheres, o.x, o.y, o.z, d.x, d.y, d.z, rtc::dot(d, d));
+                        best_t = hit.x;
+                        best_i = __float_as_int(hit.y);
+                    }
+                    ++rays;
+                    bseed = 2u + n + seed_bits;   // hash seed of bounce 0 (compute_shader.wgsl:353, 268)
+                    push = resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+                } else if (reset) {
+                    P.accum[texel_index] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // reset rule with nothing to sample
+                }
+            }
+            push_path(P, 1u, push, o, d, factor, texel_index, bseed, n, lane);
+        }
+    } else if constexpr (kMode == kPrimHits) {
         // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
 #pragma unroll
         for (int p = 0; p < kPrimRays; ++p) {
@@ -821,7 +917,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
 // finishes the texels.  Shared memory per warp: the per-ray slots (8 KB) and the warp's work stack and candidate
 // lists (2.1 KB); 2 CTAs of 11 warps per SM (rt_kernels.cuh).
-template <bool kShade>
+template <int kMode>
 __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
@@ -873,7 +969,7 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
             prim_tile_bound(L, m, chord);
             prim_tree_walk(T, s_work, s_rec, s_idx, s_near, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
-        prim_finish<kShade>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
+        prim_finish<kMode>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
     }
     prim_flush(P, exact_tests, rays, lane);
 }
@@ -890,64 +986,6 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
 // index, so the result is the reference's.
 // ---------------------------------------------------------------------------------------------
 namespace {
-
-// Running mean and texel store for a finished path (compute_shader.wgsl:356-363).
-__device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t texel_index, uint32_t n, f3 color, bool reset) {
-    float4* texel = &P.accum[texel_index];
-    f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
-    if (!reset) {
-        const float4 t = *texel;
-        mean = rtc::mk(t.x, t.y, t.z);
-    }
-    mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
-    *texel = make_float4(mean.x, mean.y, mean.z, (float)(n + 1u));
-}
-
-// Warp-aggregated append of one path per pushing lane.  Every lane of the warp must call this.
-__device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_bounce, bool push, f3 o, f3 d, f3 factor,
-                                          uint32_t texel_index, uint32_t bseed, uint32_t n, int lane) {
-    const unsigned m = __ballot_sync(kFull, push);
-    if (m == 0u) return;
-    const int leader = __ffs((int)m) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&P.wf_counts[next_bounce], (unsigned)__popc(m));
-    base = __shfl_sync(kFull, base, leader);
-    if (push) {
-        const uint32_t j = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
-        float4* q = P.wf_queue[next_bounce & 1u];
-        q[j] = make_float4(o.x, o.y, o.z, d.x);
-        q[(size_t)P.wf_capacity + j] = make_float4(d.y, d.z, factor.x, factor.y);
-        q[2 * (size_t)P.wf_capacity + j] =
-            make_float4(factor.z, __uint_as_float(texel_index), __uint_as_float(bseed), __uint_as_float(n));
-    }
-}
-
-// What happens to a traced ray (compute_shader.wgsl:267-296): returns true when the path continues (then o, d,
-// factor are the scattered ray), false when the texel has been finished.
-__device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
-                                            f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
-                                            bool reset) {
-    if (best_i < 0) {
-        finalize_texel(P, texel_index, n, rtc::sky_times(factor, d), reset);
-        return false;
-    }
-    const GpuSphere sp = load_sphere(P.spheres, best_i);
-    rtc::Ray r;
-    r.o = o;
-    r.d = d;
-    const bool ok = rtc::scatter(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
-    if (!ok) {
-        finalize_texel(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
-        return false;
-    }
-    if (last) {
-        finalize_texel(P, texel_index, n, rtc::sky_times(factor, r.d), reset);
-        return false;
-    }
-    o = r.o;
-    d = r.d;
-    return true;
-}
 
 // narrow_phase with the broad test re-evaluated by the same packed operations as the scan (half the instructions
 // of the scalar form; the values are identical, each half of an FFMA2 being the IEEE fused operation).
@@ -1038,7 +1076,8 @@ __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__
 
 }  // namespace
 
-// One thread per texel: the `update` bookkeeping around the primary hit found by primary_hits_kernel<false>.
+// One thread per texel: the `update` bookkeeping around the primary hit found by primary_hits_kernel<kPrimHits>.
+// Superseded by primary_hits_kernel<kPrimQueue>; kept as the A/B arm (-DRT_WF_SEPARATE_SHADE=1).
 __global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant__ UpdateParams P) {
     const uint64_t n_texels = (uint64_t)P.width * P.row_count;
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1315,6 +1354,9 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 // remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
 // costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
+#ifndef RT_WF_SEPARATE_SHADE
+#define RT_WF_SEPARATE_SHADE 1
+#endif
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
 #endif
@@ -1758,10 +1800,13 @@ cudaError_t configure_kernels() {
     cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimHits>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimShade>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)prim_smem_bytes());
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimQueue>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)prim_smem_bytes());
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(bounce_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
@@ -1815,9 +1860,16 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         constexpr uint32_t warps = kPrimThreads / 32;
         uint32_t blocks = (tiles + warps - 1) / warps;
         if (blocks > (uint32_t)sm_count * kPrimCtas) blocks = (uint32_t)sm_count * kPrimCtas;
-        const bool shade = rtc::f2u(p.cam.max_depth) == 1u;
-        if (shade) primary_hits_kernel<true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
-        else primary_hits_kernel<false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        const uint32_t depth = rtc::f2u(p.cam.max_depth);
+        const bool shade = depth == 1u;
+        const bool wavefront = !shade && p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth;
+        if (wavefront) {   // queue lengths, batch tickets and per-bounce counters of this frame
+            e = cudaMemsetAsync(p.wf_counts, 0, kWfWords * sizeof(unsigned int), stream);
+            if (e != cudaSuccess) return e;
+        }
+        if (shade) primary_hits_kernel<kPrimShade><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        else if (wavefront && !RT_WF_SEPARATE_SHADE) primary_hits_kernel<kPrimQueue><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        else primary_hits_kernel<kPrimHits><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         n_launch += 2;
@@ -1825,14 +1877,13 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             if (launches) *launches = n_launch;
             return cudaSuccess;
         }
-        const uint32_t depth = rtc::f2u(p.cam.max_depth);
-        if (p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth) {
-            // wavefront: shade the primary hits, then one launch per bounce over the compacted survivors
-            e = cudaMemsetAsync(p.wf_counts, 0, kWfWords * sizeof(unsigned int), stream);
-            if (e != cudaSuccess) return e;
+        if (wavefront) {
+            // the primary pass has resolved the first hits and queued the survivors (kPrimQueue): one launch per bounce
             const uint64_t n_texels = (uint64_t)p.width * p.row_count;
-            shade_first_kernel<<<(unsigned)((n_texels + 255) / 256), 256, 0, stream>>>(p);
-            n_launch += 1;
+            if (RT_WF_SEPARATE_SHADE) {   // A/B arm: first hits resolved from P.first_hit by a pass of their own
+                shade_first_kernel<<<(unsigned)((n_texels + 255) / 256), 256, 0, stream>>>(p);
+                n_launch += 1;
+            }
             // First bounce launched with the finishing code compiled in: not before the queue can be short enough to
             // use it, assuming it shrinks by no more than a fifth per bounce (texels * 0.8^b < 8 * the short-queue
             // threshold).  A scene that sheds paths faster only delays the switch by a few cheap launches.
