@@ -784,34 +784,71 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         const uint32_t sampling = L.alive | untraced;
         const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
         const int lane = threadIdx.x & 31;
+        // pass A: resolve every ray's first hit; a continuing path parks its scattered ray in the ray's own slots
+        // (d, o; n in the best_t slot, the sphere index stays: the factor after one hit is that sphere's attenuation)
+        uint32_t pmask = 0;
 #pragma unroll 1
-        for (int p = 0; p < kPrimRays; ++p) {   // every lane takes every turn: push_path is a warp-wide append
+        for (int p = 0; p < kPrimRays; ++p) {
             const int row = row0 + p;
-            bool push = false;
-            f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = rtc::mk(1.0f, 1.0f, 1.0f);
-            uint32_t bseed = 0, n = 0, texel_index = 0;
-            if ((uint32_t)x < P.width && (uint32_t)row < P.row_count) {
-                texel_index = (uint32_t)row * P.width + (uint32_t)x;
-                if (!reset) n = rtc::f2u(P.accum[texel_index].w);
-                if (sampling & (1u << p)) {
-                    const float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
-                    d = rtc::mk(dp[0], dp[kPrimThreads], dp[2 * kPrimThreads]);
-                    o = rtc::mk(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads]);
-                    float best_t = dp[6 * kPrimThreads];
-                    int best_i = __float_as_int(dp[7 * kPrimThreads]);
-                    if (untraced & (1u << p)) {   // outside primary_arm's window: the reference loop itself
-                        const float2 hit = retrace_sequential(P.spheres, P.n_spheres, o.x, o.y, o.z, d.x, d.y, d.z, rtc::dot(d, d));
-                        best_t = hit.x;
-                        best_i = __float_as_int(hit.y);
-                    }
-                    ++rays;
-                    bseed = 2u + n + seed_bits;   // hash seed of bounce 0 (compute_shader.wgsl:353, 268)
-                    push = resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
-                } else if (reset) {
-                    P.accum[texel_index] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // reset rule with nothing to sample
+            if (!((uint32_t)x < P.width && (uint32_t)row < P.row_count)) continue;
+            const uint32_t texel_index = (uint32_t)row * P.width + (uint32_t)x;
+            uint32_t n = 0;
+            if (!reset) n = rtc::f2u(P.accum[texel_index].w);
+            if (sampling & (1u << p)) {
+                float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+                f3 d = rtc::mk(dp[0], dp[kPrimThreads], dp[2 * kPrimThreads]);
+                f3 o = rtc::mk(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads]);
+                float best_t = dp[6 * kPrimThreads];
+                int best_i = __float_as_int(dp[7 * kPrimThreads]);
+                if (untraced & (1u << p)) {   // outside primary_arm's window: the reference loop itself
+                    const float2 hit = retrace_sequential(P.spheres, P.n_spheres, o.x, o.y, o.z, d.x, d.y, d.z, rtc::dot(d, d));
+                    best_t = hit.x;
+                    best_i = __float_as_int(hit.y);
+                    dp[7 * kPrimThreads] = hit.y;
                 }
+                ++rays;
+                f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
+                const uint32_t bseed = 2u + n + seed_bits;   // hash seed of bounce 0 (compute_shader.wgsl:353, 268)
+                if (resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset)) {
+                    dp[0] = d.x; dp[kPrimThreads] = d.y; dp[2 * kPrimThreads] = d.z;
+                    dp[3 * kPrimThreads] = o.x; dp[4 * kPrimThreads] = o.y; dp[5 * kPrimThreads] = o.z;
+                    dp[6 * kPrimThreads] = __uint_as_float(n);
+                    pmask |= 1u << p;
+                }
+            } else if (reset) {
+                P.accum[texel_index] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // reset rule with nothing to sample
             }
-            push_path(P, 1u, push, o, d, factor, texel_index, bseed, n, lane);
+        }
+        // pass B: ONE reservation per tile, the tile's surviving paths appended row by row — a 64-ray batch of the first
+        // bounce is then a 32 x 2 pixel block of one tile (appending row by row with a reservation each interleaves
+        // the tiles of different warps in the queue and costs the bounce launches 3 %)
+        uint32_t total = (uint32_t)__popc(pmask);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(kFull, total, o);
+        if (total == 0u) return;
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&P.wf_counts[1], total);
+        base = __shfl_sync(kFull, base, 0);
+        float4* q = P.wf_queue[1];
+#pragma unroll 1
+        for (int p = 0; p < kPrimRays; ++p) {
+            const bool mine = (pmask >> p) & 1u;
+            const unsigned m = __ballot_sync(kFull, mine);
+            if (mine) {
+                const float* dp = s_d + (p * kPrimSlots) * kPrimThreads;
+                const uint32_t j = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+                const uint32_t n = __float_as_uint(dp[6 * kPrimThreads]);
+                const float4 col = __ldg(reinterpret_cast<const float4*>(P.spheres + __float_as_int(dp[7 * kPrimThreads])) + 1);
+                // attenuation of the one hit so far (rtc::scatter): albedo for lambertian and metal, 1 for a dielectric
+                const bool glass = !(col.w <= 1.0f);   // (the else-branch of scatter, NaN included)
+                const f3 factor = rtc::mk(glass ? 1.0f : col.x, glass ? 1.0f : col.y, glass ? 1.0f : col.z);
+                const uint32_t texel_index = (uint32_t)(row0 + p) * P.width + (uint32_t)x;
+                q[j] = make_float4(dp[3 * kPrimThreads], dp[4 * kPrimThreads], dp[5 * kPrimThreads], dp[0]);
+                q[(size_t)P.wf_capacity + j] = make_float4(dp[kPrimThreads], dp[2 * kPrimThreads], factor.x, factor.y);
+                q[2 * (size_t)P.wf_capacity + j] = make_float4(factor.z, __uint_as_float(texel_index),
+                                                                __uint_as_float(2u + n + seed_bits), __uint_as_float(n));
+            }
+            base += (uint32_t)__popc(m);
         }
     } else if constexpr (kMode == kPrimHits) {
         // one (t, index) per texel: 8-byte stores, 256 B contiguous per warp row
@@ -1355,7 +1392,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
 // costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
 #ifndef RT_WF_SEPARATE_SHADE
-#define RT_WF_SEPARATE_SHADE 1
+#define RT_WF_SEPARATE_SHADE 0
 #endif
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
