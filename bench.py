@@ -345,7 +345,7 @@ def run_ours(args):
         deep_ms = r.timer_end() / n_deep
         deep_rays = r.rays_traced() / n_deep
         deep = {"max_depth": 30, "ms_per_frame": deep_ms, "rays_per_frame": deep_rays, "mrays_s": deep_rays / deep_ms / 1e3,
-                "note": "primary pass + shade_first_kernel + 29 wavefront bounce launches over compacted path queues"}
+                "note": "primary pass (first hits resolved and survivors queued in the same kernel) + 29 wavefront bounce launches over compacted path queues"}
         r.init()
 
     # ---- end to end through the C ABI with HOST buffers ----------------------------------------
