@@ -1218,6 +1218,94 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 }
 
 
+// The same for a 64-ray batch of the tree kernel (2 rays per thread: queue entries j0 and j0 + 1), with ONE reservation
+// per batch and the survivors appended in their queue order.  (Two appends per batch, one per p, put the even entries'
+// survivors before the odd ones — a perfect unshuffle per bounce, so the rays of an FFMA2 pair drift 2^k entries apart —
+// and let other warps' appends fall between.)  Ray 0's outcome waits in `s_park`, 12 words of the thread's idle candidate
+// column (its OWN column: a wider view of the area would land in other warps' cells, which are in use), while the
+// rolled loop resolves ray 1.
+template <typename CandT>
+__device__ __forceinline__ void park_word(CandT* s_cand, int k, uint32_t v) {
+    if constexpr (sizeof(CandT) == 4) {
+        s_cand[k * kBlockThreads] = v;
+    } else {
+        s_cand[(2 * k) * kBlockThreads] = (CandT)(v & 0xffffu);
+        s_cand[(2 * k + 1) * kBlockThreads] = (CandT)(v >> 16);
+    }
+}
+template <typename CandT>
+__device__ __forceinline__ uint32_t parked_word(const CandT* s_cand, int k) {
+    if constexpr (sizeof(CandT) == 4) return s_cand[k * kBlockThreads];
+    else return (uint32_t)s_cand[(2 * k) * kBlockThreads] | ((uint32_t)s_cand[(2 * k + 1) * kBlockThreads] << 16);
+}
+template <typename CandT>
+__device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
+                                                 const Lanes& L, uint32_t bounce, bool last, bool reset, int lane,
+                                                 CandT* s_park) {
+    static_assert(kWfCand * sizeof(CandT) >= 12 * sizeof(uint32_t), "12 parked words per thread");
+    bool push = false, push0 = false;
+    f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
+    uint32_t texel_index = 0, bseed = 0, n = 0;
+    __syncwarp();
+#pragma unroll 1
+    for (int p = 0; p < 2; ++p) {
+        const uint32_t j = j0 + (uint32_t)p;
+        push = false;
+        if (j < count) {
+            const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+            factor = rtc::mk(B.z, B.w, C.x);
+            texel_index = __float_as_uint(C.y);
+            bseed = __float_as_uint(C.z);
+            n = __float_as_uint(C.w);
+            const bool second = p != 0;   // picked with selects: no dynamic register indexing
+            o = second ? origin_of(L, 1) : origin_of(L, 0);
+            d = second ? rtc::mk(L.dx[1], L.dy[1], L.dz[1]) : rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
+            const float best_t = second ? L.best_t[1] : L.best_t[0];
+            const int best_i = second ? L.best_i[1] : L.best_i[0];
+            push = resolve_hit(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+        }
+        if (p == 0) {
+            push0 = push;
+            if (push) {
+                park_word(s_park, 0, __float_as_uint(o.x)); park_word(s_park, 1, __float_as_uint(o.y));
+                park_word(s_park, 2, __float_as_uint(o.z)); park_word(s_park, 3, __float_as_uint(d.x));
+                park_word(s_park, 4, __float_as_uint(d.y)); park_word(s_park, 5, __float_as_uint(d.z));
+                park_word(s_park, 6, __float_as_uint(factor.x)); park_word(s_park, 7, __float_as_uint(factor.y));
+                park_word(s_park, 8, __float_as_uint(factor.z)); park_word(s_park, 9, texel_index);
+                park_word(s_park, 10, bseed); park_word(s_park, 11, n);
+            }
+        }
+    }
+    const unsigned m0 = __ballot_sync(kFull, push0), m1 = __ballot_sync(kFull, push);
+    const uint32_t total = (uint32_t)(__popc(m0) + __popc(m1));
+    if (total != 0u) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&P.wf_counts[bounce + 1u], total);
+        base = __shfl_sync(kFull, base, 0);
+        const unsigned lt = (1u << lane) - 1u;
+        const uint32_t rank0 = base + (uint32_t)(__popc(m0 & lt) + __popc(m1 & lt));
+        float4* q = P.wf_queue[(bounce + 1u) & 1u];
+        if (push0) {
+            q[rank0] = make_float4(__uint_as_float(parked_word(s_park, 0)), __uint_as_float(parked_word(s_park, 1)),
+                                   __uint_as_float(parked_word(s_park, 2)), __uint_as_float(parked_word(s_park, 3)));
+            q[(size_t)P.wf_capacity + rank0] =
+                make_float4(__uint_as_float(parked_word(s_park, 4)), __uint_as_float(parked_word(s_park, 5)),
+                            __uint_as_float(parked_word(s_park, 6)), __uint_as_float(parked_word(s_park, 7)));
+            q[2 * (size_t)P.wf_capacity + rank0] =
+                make_float4(__uint_as_float(parked_word(s_park, 8)), __uint_as_float(parked_word(s_park, 9)),
+                            __uint_as_float(parked_word(s_park, 10)), __uint_as_float(parked_word(s_park, 11)));
+        }
+        if (push) {
+            const uint32_t j = rank0 + (push0 ? 1u : 0u);
+            q[j] = make_float4(o.x, o.y, o.z, d.x);
+            q[(size_t)P.wf_capacity + j] = make_float4(d.y, d.z, factor.x, factor.y);
+            q[2 * (size_t)P.wf_capacity + j] =
+                make_float4(factor.z, __uint_as_float(texel_index), __uint_as_float(bseed), __uint_as_float(n));
+        }
+    }
+    __syncwarp();   // the parked words are candidate codes again from the next batch on
+}
+
 // ---------------------------------------------------------------------------------------------
 // Tree traversal for incoherent rays (rt_tree.h).  The scene image in shared memory is
 // [child records, 9 slots per node | child links, 8 per node | largest child radius per node].  A thread traces one
@@ -1391,6 +1479,9 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 // remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
 // costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
+#ifndef RT_WF_BATCH_APPEND
+#define RT_WF_BATCH_APPEND 1
+#endif
 #ifndef RT_WF_SEPARATE_SHADE
 #define RT_WF_SEPARATE_SHADE 0
 #endif
@@ -1486,6 +1577,7 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
     const uint32_t image_slots = kGlobal ? 0u : (P.cl_bytes + 15u) / 16u;
     // [kWfCand][kBlockThreads] candidate codes, then [cl_stack_cap][kBlockThreads] node numbers
     CandT* s_cand = reinterpret_cast<CandT*>(s_dyn + image_slots) + threadIdx.x;
+
     unsigned short* s_stack = reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads) + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
@@ -1526,7 +1618,11 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
             Lanes L;
             wf_load_rays<2>(P, qin, count, j0, L, rays);
             trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+#if RT_WF_BATCH_APPEND
+            wf_resolve_batch(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
+#else
             wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
+#endif
         }
     } else {
         finish_paths(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
