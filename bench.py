@@ -427,7 +427,7 @@ def run_ours(args):
                      "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
                      "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
                      "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
-                     "kernel": "primary_hits_kernel<true> (+ prep_primary_tree_kernel, 3 us)",
+                     "kernel": "primary_hits_kernel<kPrimShade> (+ prep_primary_tree_kernel, 3 us)",
                      "ncu": {"source": "profiles/r1_primary_cull_ncu.md (ncu --set full of this kernel on this workload)",
                              "warp_instructions_per_launch": 247215710, "issue_slots_busy_pct": 76.0,
                              "pipe_fma_pct": 33.5, "pipe_alu_pct": 39.2, "pipe_xu_pct": 29.5, "stall_no_inst_pct": 8.7,
