@@ -92,6 +92,7 @@ SPHERE_DTYPE = np.dtype([("position", "<f4", 3), ("radius", "<f4"), ("color", "<
 assert SPHERE_DTYPE.itemsize == 32 and C.sizeof(GpuSphere) == 32 and C.sizeof(SceneCamera) == 176
 
 RT_OK = 0
+RT_PRECISION_EXACT, RT_PRECISION_FAST = 0, 1
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_NO_SCENE, RT_ERR_OUT_OF_MEMORY, RT_ERR_STATE = -1, -2, -3, -4, -5, -6
 
 
@@ -125,6 +126,12 @@ _SIGNATURES = {
     "rt_tree_info": (C.c_int, [_P, _P, _P, _P]),
     "rt_read_wait": (C.c_int, [_P]),
     "rt_set_rgba8_output": (C.c_int, [_P, C.c_int]),
+    "rt_set_rgba8_target": (C.c_int, [_P, _P]),
+    "rt_stream_signal": (C.c_int, [_P, _P, C.c_uint32]),
+    "rt_stream_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "rt_stream_wait_timed_out": (C.c_int, [_P, C.POINTER(C.c_uint32)]),
+    "rt_set_precision": (C.c_int, [_P, C.c_int]),
+    "rt_tree_build_ms": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "rt_device_alloc": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(_P)]),
     "rt_device_free": (C.c_int, [C.c_int, _P]),
     "rt_ipc_export": (C.c_int, [C.c_int, _P, _P]),
@@ -400,6 +407,31 @@ class Renderer:
     def set_rgba8_output(self, enable: bool = True):
         """Depth-1 updates also write the RGBA8 frame the next read_rgba8_async* call sends (no quantise kernel)."""
         _check(lib().rt_set_rgba8_output(self._h, 1 if enable else 0))
+
+    def set_rgba8_target(self, device_ptr):
+        """Fused gather: depth-1 updates store the window's RGBA8 texels at device_ptr (this GPU's memory or a peer's);
+        None switches it off."""
+        _check(lib().rt_set_rgba8_target(self._h, C.c_void_p(device_ptr or 0)))
+
+    def stream_signal(self, device_flag: int, value: int):
+        _check(lib().rt_stream_signal(self._h, C.c_void_p(device_flag), value))
+
+    def stream_wait(self, device_flags: int, n: int, value: int, timeout_ms: int = 2000):
+        _check(lib().rt_stream_wait(self._h, C.c_void_p(device_flags), n, value, timeout_ms))
+
+    def stream_wait_timed_out(self) -> int:
+        v = C.c_uint32(0)
+        _check(lib().rt_stream_wait_timed_out(self._h, C.byref(v)))
+        return v.value
+
+    def set_precision(self, precision: int):
+        """RT_PRECISION_EXACT (default, bit-identical to the oracle) or RT_PRECISION_FAST (MUFU + FMA per-ray arithmetic)."""
+        _check(lib().rt_set_precision(self._h, precision))
+
+    def tree_build_ms(self) -> float:
+        v = C.c_double(0)
+        _check(lib().rt_tree_build_ms(self._h, C.byref(v)))
+        return v.value
 
     def tree_info(self):
         """(nodes, levels, bounce path) of the scene's tree: path 1 = shared-memory image, 2 = walked in global memory,

@@ -8,6 +8,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -98,6 +99,8 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     if (e == cudaSuccess) e = cudaMalloc(&r->first_hit, r->n_texels * sizeof(float2));
     if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, 2 * sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMalloc(&r->counters, 2 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&r->wait_status, sizeof(unsigned int));
+    if (e == cudaSuccess) e = cudaMemsetAsync(r->wait_status, 0, sizeof(unsigned int), r->stream);
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking);
@@ -144,6 +147,7 @@ int rt_destroy(RtRenderer* r) {
     cudaFree(r->cl_blob);
     cudaFree(r->tile_counter);
     cudaFree(r->counters);
+    cudaFree(r->wait_status);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
     if (r->ev_end) cudaEventDestroy(r->ev_end);
     if (r->stream) cudaStreamDestroy(r->stream);
@@ -218,6 +222,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         // memory for the primary pass; the bounce kernel copies its image into shared memory when it fits there
         r->clusters_stale = false;
         rtt::Tree tree;
+        const auto t_build = std::chrono::steady_clock::now();
         if (rtt::build(r->host_spheres.data(), r->n_spheres, tree)) {
             const size_t rec_bytes = ((size_t)tree.n_nodes * rtk::kTreeStride + tree.n_entry_pad) * sizeof(float4);
             if (tree.bytes() > r->cl_capacity || rec_bytes > r->prim_tree_capacity) {
@@ -247,6 +252,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
             // too large for shared memory: the bounce kernel walks the tree where it lies (16-bit node numbers on its stack)
             r->cl_global = (!fits && tree.n_nodes < 65536u && r->n_spheres < 0x80000000u && r->cl_stack_cap <= rtk::kTreeStackMax) ? 1u : 0u;
         }
+        r->tree_build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build).count();
     }
     p.prim_tree = r->cl_n_nodes ? r->prim_tree : nullptr;
     p.cl_blob = r->cl_blob;
@@ -269,8 +275,13 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.wf_capacity = (uint32_t)r->n_texels;
     p.wf_bounce = 0;
     p.rgba8_out = nullptr;
+    p.precision = (uint32_t)r->precision;
     r->rgba8_fresh = false;
-    if (r->rgba8_output && rtk::fused_shade_applies(p, r->variant)) {
+    r->target_fresh = false;
+    if (r->rgba8_target && rtk::fused_shade_applies(p, r->variant)) {
+        p.rgba8_out = r->rgba8_target;   // fused gather: the texels go where the caller wants them, possibly a peer GPU
+        r->target_fresh = true;
+    } else if (r->rgba8_output && rtk::fused_shade_applies(p, r->variant)) {
         // the slot the next rt_read_rgba8_async will send: its previous copy must have left it
         const int b = (int)(r->async_reads & 1u);
         if (b && !r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
@@ -280,7 +291,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     int launched = 0;
     RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched));
     r->launches += (uint64_t)launched;
-    r->rgba8_fresh = p.rgba8_out != nullptr;
+    r->rgba8_fresh = p.rgba8_out != nullptr && !r->target_fresh;
     return RT_OK;
 }
 
@@ -329,6 +340,8 @@ int rt_quantize(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
     // a fused update (rt_set_rgba8_output) may have written this very buffer already: slot 0 of the asynchronous reads
     if (r->rgba8_fresh && (r->async_reads & 1u) == 0u) return RT_OK;
+    // r->rgba8 is slot 0 of the asynchronous reads as well: an earlier rt_read_rgba8_async may still be copying out of it
+    if (r->async_reads > 0) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[0], 0));
     RT_CUDA(rtk::launch_quantize(r->accum, r->rgba8, r->n_texels, r->stream));
     r->launches += 1;
     return RT_OK;
@@ -378,6 +391,53 @@ int rt_set_rgba8_output(RtRenderer* r, int enable) {
     RT_CHECK_HANDLE(r);
     r->rgba8_output = enable != 0;
     r->rgba8_fresh = false;
+    return RT_OK;
+}
+
+int rt_set_rgba8_target(RtRenderer* r, void* device_rgba8) {
+    RT_CHECK_HANDLE(r);
+    r->rgba8_target = static_cast<uint32_t*>(device_rgba8);
+    r->target_fresh = false;
+    r->rgba8_fresh = false;
+    return RT_OK;
+}
+
+int rt_stream_signal(RtRenderer* r, void* device_flag, uint32_t value) {
+    RT_CHECK_HANDLE(r);
+    if (!device_flag) return fail(RT_ERR_INVALID_ARG, "flag is null");
+    RT_CUDA(rtk::launch_signal(device_flag, value, r->stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
+int rt_stream_wait(RtRenderer* r, const void* device_flags, uint32_t n, uint32_t value, uint32_t timeout_ms) {
+    RT_CHECK_HANDLE(r);
+    if (!device_flags || n == 0) return fail(RT_ERR_INVALID_ARG, "no flags");
+    RT_CUDA(rtk::launch_wait_flags(device_flags, n, value, timeout_ms ? timeout_ms : 1u, r->wait_status, r->stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
+int rt_stream_wait_timed_out(RtRenderer* r, uint32_t* count) {
+    RT_CHECK_HANDLE(r);
+    if (!count) return fail(RT_ERR_INVALID_ARG, "count is null");
+    unsigned int v = 0;
+    RT_CUDA(cudaMemcpyAsync(&v, r->wait_status, sizeof(v), cudaMemcpyDeviceToHost, r->stream));
+    RT_CUDA(cudaStreamSynchronize(r->stream));
+    *count = v;
+    return RT_OK;
+}
+
+int rt_set_precision(RtRenderer* r, int precision) {
+    if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    if (precision != RT_PRECISION_EXACT && precision != RT_PRECISION_FAST) return fail(RT_ERR_INVALID_ARG, "precision %d", precision);
+    r->precision = precision;
+    return RT_OK;
+}
+
+int rt_tree_build_ms(RtRenderer* r, double* ms) {
+    if (!r || !ms) return fail(RT_ERR_INVALID_ARG, "null argument");
+    *ms = r->tree_build_ms;
     return RT_OK;
 }
 

@@ -52,6 +52,72 @@ RT_DEV_SHARED f3 normalize_shared(f3 a) {
     return mk(a.x / s, a.y / s, a.z / s);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tolerance mode (rt_set_precision(RT_PRECISION_FAST)).  The functions below that take a
+// `bool F` template argument have two instantiations: F = false is the bit-exact restatement (one IEEE rounding per
+// WGSL operator, pinned sin / cos), F = true evaluates the same formulas with the hardware approximations the port
+// target names — MUFU rcp / rsqrt / sqrt / sin / cos (about 1-2 ulp, sin / cos 2^-21 absolute) and explicit FMA
+// contraction — which is what a WGSL implementation is allowed to do as well (builtin precision is implementation
+// defined).  What decides WHICH sphere a ray hits (discriminant sign, root order, rtc::sphere_root) stays IEEE in both
+// modes, so the two modes differ by rounding of colours, not by geometry, until a path's second bounce.
+// ---------------------------------------------------------------------------------------------
+namespace fastm {
+RT_DEV float rcp(float x) {
+#if defined(__CUDA_ARCH__)
+    float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+    return 1.0f / x;
+#endif
+}
+RT_DEV float rsq(float x) {
+#if defined(__CUDA_ARCH__)
+    float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+    return 1.0f / sqrtf(x);
+#endif
+}
+RT_DEV float sqr(float x) {
+#if defined(__CUDA_ARCH__)
+    float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+#else
+    return sqrtf(x);
+#endif
+}
+// sin and cos of an angle in [0, 2 pi] (the shader only forms u * 2 pi): MUFU.SIN / MUFU.COS are accurate to 2^-21
+// absolute on [-pi, pi], so the argument is shifted by pi and the signs flipped.
+RT_DEV void sincos2pi(float a, float* s_out, float* c_out) {
+#if defined(__CUDA_ARCH__)
+    const float b = a - 3.14159274101257324f;
+    float s, c;
+    asm("sin.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(b));
+    asm("cos.approx.ftz.f32 %0, %1;" : "=f"(c) : "f"(b));
+    *s_out = -s; *c_out = -c;
+#else
+    *s_out = sinf(a); *c_out = cosf(a);
+#endif
+}
+// 1 / sqrt(a) to ~2^-23: MUFU.RSQ and one Newton step (the broad phases assume unit directions good to 2^-22)
+RT_DEV float rsq_refined(float a) {
+    const float y = rsq(a);
+    const float h = 0.5f * a * y;
+    return fmaf(y, fmaf(-h, y, 0.5f), y);
+}
+}  // namespace fastm
+
+template <bool F> RT_DEV float dot_t(f3 a, f3 b) {
+    if constexpr (F) return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z));
+    else return dot(a, b);
+}
+template <bool F> RT_DEV f3 axpy_t(float s, f3 a, f3 b) {   // s * a + b
+    if constexpr (F) return mk(fmaf(s, a.x, b.x), fmaf(s, a.y, b.y), fmaf(s, a.z, b.z));
+    else return add(b, scale(s, a));
+}
+// normalize() of the metal / dielectric branches: the shared out-of-line IEEE copy, or v * rsqrt(v.v) inline
+template <bool F> RT_DEV f3 normalize_branch(f3 a) {
+    if constexpr (F) return scale(fastm::rsq(dot_t<true>(a, a)), a);
+    else return normalize_shared(a);
+}
+
 // WGSL u32(f32): truncate, saturate, NaN -> 0
 RT_DEV uint32_t f2u(float f) {
 #if defined(__CUDA_ARCH__)
@@ -77,13 +143,20 @@ RT_DEV uint32_t hash(uint32_t s) {
 RT_DEV float random_float(uint32_t v) { return (float)hash(v) * 2.3283064365386963e-10f; }
 
 // compute_shader.wgsl:234-243
+template <bool F = false>
 RT_DEV f3 random_unit_vector(uint32_t seed) {
     float z = 2.0f * random_float(seed) - 1.0f;
     float a = random_float(seed + 1u) * 6.283185307f;
-    float r = sqrtf(1.0f - z * z);
     float sn, cs;
-    rt_sincos(a, &sn, &cs);
-    return mk(r * cs, r * sn, z);
+    if constexpr (F) {
+        const float r = fastm::sqr(fmaxf(fmaf(-z, z, 1.0f), 0.0f));
+        fastm::sincos2pi(a, &sn, &cs);
+        return mk(r * cs, r * sn, z);
+    } else {
+        float r = sqrtf(1.0f - z * z);
+        rt_sincos(a, &sn, &cs);
+        return mk(r * cs, r * sn, z);
+    }
 }
 
 struct Ray {
@@ -91,12 +164,26 @@ struct Ray {
 };
 
 // compute_shader.wgsl:305-331 (get_ray, sample_square, defocus_disk_sample)
+template <bool F = false>
 RT_DEV Ray get_ray(const SceneCamera& cam, int x, int y, uint32_t sample_index, uint32_t seed_bits) {
     uint32_t seed = hash(hash((uint32_t)x * 73u) ^ hash((uint32_t)y * 51u) ^ (sample_index * 25u + seed_bits));
     float ox = random_float(seed) - 0.5f;
     float oy = random_float(seed * seed) - 0.5f;
     float sx = ((float)x + 0.5f) + ox;
     float sy = ((float)y + 0.5f) + oy;
+    if constexpr (F) {
+        Ray r;
+        const f3 pc = axpy_t<true>(sy, mk(cam.pixel_delta_v), axpy_t<true>(sx, mk(cam.pixel_delta_u), mk(cam.viewport_upper_left)));
+        r.o = mk(cam.center);
+        if (cam.defocus_angle > 0.0f) {
+            // (cos, sin) of the approximation is unit to 2^-20: the reference's normalize of it is a no-op at that level
+            float sn, cs;
+            fastm::sincos2pi((2.0f * 3.1415926f) * random_float(seed + 1u), &sn, &cs);
+            r.o = axpy_t<true>(sn, mk(cam.defocus_disk_v), axpy_t<true>(cs, mk(cam.defocus_disk_u), r.o));
+        }
+        r.d = sub(pc, r.o);
+        return r;
+    }
     f3 pc = add(add(mk(cam.viewport_upper_left), mk(cam.pixel_delta_u.x * sx, cam.pixel_delta_u.y * sx, cam.pixel_delta_u.z * sx)),
                 mk(cam.pixel_delta_v.x * sy, cam.pixel_delta_v.y * sy, cam.pixel_delta_v.z * sy));
     Ray r;
@@ -134,9 +221,12 @@ RT_DEV bool sphere_root(f3 o, f3 d, float a, f3 center, float radius, float tmin
 }
 
 // Sky gradient of ray_color (compute_shader.wgsl:293-296) times the accumulated factor.
+template <bool F = false>
 RT_DEV f3 sky_times(f3 factor, f3 dir) {
-    f3 u = normalize(dir);
-    float a = 0.5f * (u.y + 1.0f);
+    float uy;
+    if constexpr (F) uy = dir.y * fastm::rsq(dot_t<true>(dir, dir));
+    else uy = normalize(dir).y;
+    float a = 0.5f * (uy + 1.0f);
     float ia = 1.0f - a;
     f3 sky = mk(ia * 1.0f + a * 0.5f, ia * 1.0f + a * 0.7f, ia * 1.0f + a * 1.0f);
     return mul(factor, sky);
@@ -146,12 +236,19 @@ RT_DEV f3 sky_times(f3 factor, f3 dir) {
 // dispatch of ray_color (compute_shader.wgsl:268-286).  On return *ray is the scattered ray and
 // *factor has been multiplied by the attenuation.  Returns false when the sample is absorbed
 // (ray_color returns black, compute_shader.wgsl:274,278,282).
+template <bool F = false>
 RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
     f3 o = ray->o, d = ray->d;
     f3 center = mk(sp.position);
-    f3 p = add(o, scale(t, d));
-    f3 outward = divs(sub(p, center), sp.radius);
-    bool front = dot(d, outward) < 0.0f;
+    f3 p, outward;
+    if constexpr (F) {
+        p = axpy_t<true>(t, d, o);
+        outward = scale(fastm::rcp(sp.radius), sub(p, center));
+    } else {
+        p = add(o, scale(t, d));
+        outward = divs(sub(p, center), sp.radius);
+    }
+    bool front = dot_t<F>(d, outward) < 0.0f;
     f3 n = front ? outward : neg(outward);
     float w = sp.color[3];
     f3 albedo = mk(sp.color[0], sp.color[1], sp.color[2]);
@@ -159,46 +256,54 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
     out.o = p;
     if (w < -1.0f) {
         // lambertian_scatter, compute_shader.wgsl:84-93
-        f3 dir = add(n, random_unit_vector(bounce_seed));
-        if (dot(dir, dir) < 1e-6f) dir = n;
+        f3 dir = add(n, random_unit_vector<F>(bounce_seed));
+        if (dot_t<F>(dir, dir) < 1e-6f) dir = n;
         out.d = dir;
         *factor = mul(*factor, albedo);
         *ray = out;
         return true;
     } else if (w <= 1.0f) {
         // metal_scatter, compute_shader.wgsl:95-100; reflect(e1,e2) = e1 - 2 dot(e2,e1) e2
-        f3 refl = sub(d, scale(2.0f * dot(n, d), n));
-        f3 reflected = add(normalize_shared(refl), scale(w, random_unit_vector(bounce_seed)));
-        out.d = normalize_shared(reflected);
+        f3 refl = sub(d, scale(2.0f * dot_t<F>(n, d), n));
+        f3 reflected = add(normalize_branch<F>(refl), scale(w, random_unit_vector<F>(bounce_seed)));
+        out.d = normalize_branch<F>(reflected);
         *factor = mul(*factor, albedo);
         *ray = out;
-        return dot(reflected, n) > 0.0f;
+        return dot_t<F>(reflected, n) > 0.0f;
     } else {
         // dielectric_scatter + reflectance, compute_shader.wgsl:102-141
         float ior = sp.color[0];
-        float ratio = front ? (1.0f / ior) : ior;
-        f3 ud = normalize_shared(d);
-        float cos_theta = fminf(dot(neg(ud), n), 1.0f);
-        float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        float ratio, sin_theta, r0;
+        f3 ud = normalize_branch<F>(d);
+        float cos_theta = fminf(dot_t<F>(neg(ud), n), 1.0f);
+        if constexpr (F) {
+            ratio = front ? fastm::rcp(ior) : ior;
+            sin_theta = fastm::sqr(fmaxf(fmaf(-cos_theta, cos_theta, 1.0f), 0.0f));
+            r0 = (1.0f - ratio) * fastm::rcp(1.0f + ratio);
+        } else {
+            ratio = front ? (1.0f / ior) : ior;
+            sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+            r0 = (1.0f - ratio) / (1.0f + ratio);
+        }
         bool cannot_refract = ratio * sin_theta > 1.0f;
-        float r0 = (1.0f - ratio) / (1.0f + ratio);
         r0 = r0 * r0;
         float refl_prob = r0 + (1.0f - r0) * rt_pow5(1.0f - cos_theta);
         bool should_reflect = cannot_refract || refl_prob > random_float(bounce_seed);
         f3 dir;
         if (should_reflect) {
-            dir = sub(ud, scale(2.0f * dot(n, ud), n));
+            dir = sub(ud, scale(2.0f * dot_t<F>(n, ud), n));
         } else {
             // WGSL refract(e1, e2, e3)
-            float dn = dot(n, ud);
+            float dn = dot_t<F>(n, ud);
             float k = 1.0f - (ratio * ratio) * (1.0f - dn * dn);
             if (k < 0.0f) {
                 dir = mk(0.0f, 0.0f, 0.0f);
             } else {
-                dir = sub(scale(ratio, ud), scale(ratio * dn + sqrtf(k), n));
+                const float sk = F ? fastm::sqr(k) : sqrtf(k);
+                dir = sub(scale(ratio, ud), scale(ratio * dn + sk, n));
             }
         }
-        out.d = normalize_shared(dir);
+        out.d = normalize_branch<F>(dir);
         // attenuation = vec3(1.0): color_factor *= 1.0 is exact, skipped
         *ray = out;
         return true;
@@ -220,9 +325,12 @@ struct BroadRay {
     float thr;            // |O|^2 (1 - kappa)
 };
 
+template <bool F = false>
 RT_DEV BroadRay broad_arm(f3 o, f3 d, float a) {
     BroadRay b;
-    float inv = 1.0f / sqrtf(a);
+    float inv;
+    if constexpr (F) inv = fastm::rsq_refined(a);
+    else inv = 1.0f / sqrtf(a);
     b.ux = d.x * inv; b.uy = d.y * inv; b.uz = d.z * inv;
     b.h0 = -((o.x * b.ux + o.y * b.uy) + o.z * b.uz);
     b.mox = -2.0f * o.x; b.moy = -2.0f * o.y; b.moz = -2.0f * o.z;
@@ -329,13 +437,16 @@ RT_DEV void primary_record_pad(float out[4]) { out[0] = 0.0f; out[1] = 0.0f; out
 
 // Unit direction of a ray for the common-origin test.  Returns false (and u = 0) when |d|^2 is
 // outside [2^-40, 2^40] or not finite: such a ray has to be traced with the exact test only.
+template <bool F = false>
 RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz, float* inv_len = nullptr) {
     const bool ok = (a >= 9.094947017729282e-13f) && (a <= 1099511627776.0f);
     if (!ok) {
         *ux = 0.0f; *uy = 0.0f; *uz = 0.0f;
         return false;
     }
-    const float inv = 1.0f / sqrtf(a);
+    float inv;
+    if constexpr (F) inv = fastm::rsq_refined(a);
+    else inv = 1.0f / sqrtf(a);
     *ux = d.x * inv; *uy = d.y * inv; *uz = d.z * inv;
     if (inv_len) *inv_len = inv;   // 1 / |d|
     return true;

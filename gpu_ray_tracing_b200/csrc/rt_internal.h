@@ -46,6 +46,13 @@ struct RtRenderer {
     uint32_t async_reads = 0;
     uint64_t launches = 0;
     int variant = 0;
+    int precision = 0;                    // RT_PRECISION_* (rt_set_precision)
+    // rt_set_rgba8_target: where fused depth-1 updates store the window's RGBA8 texels instead of the read-back slots —
+    // this device's memory or a peer's (the gather target of a sharded image); target_fresh: the last update did
+    uint32_t* rgba8_target = nullptr;
+    bool target_fresh = false;
+    double tree_build_ms = 0.0;           // host time of the last tree build + pack (rt_tree_build_ms)
+    unsigned int* wait_status = nullptr;  // device word a timed-out rt_stream_wait sets
 };
 
 namespace rti {

@@ -19,6 +19,7 @@
 
 #include "rt_kernels.cuh"
 #include "rt_core.cuh"
+#include "rt_tree_layout.h"
 
 namespace rtk {
 
@@ -71,13 +72,14 @@ __device__ __forceinline__ float broad_g(const float4 sp, const Lanes& L, int p)
                         half(L.mox[q], p), half(L.moy[q], p), half(L.moz[q], p));
 }
 
+template <bool F = false>
 __device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
     const int q = p >> 1;
     L.dx[p] = d.x; L.dy[p] = d.y; L.dz[p] = d.z;
     L.ox[p] = o.x; L.oy[p] = o.y; L.oz[p] = o.z;
     const float a = rtc::dot(d, d);
     L.a[p] = a;
-    const rtc::BroadRay b = rtc::broad_arm(o, d, a);
+    const rtc::BroadRay b = rtc::broad_arm<F>(o, d, a);
     half(L.mox[q], p) = b.mox; half(L.moy[q], p) = b.moy; half(L.moz[q], p) = b.moz;
     half(L.ux[q], p) = b.ux; half(L.uy[q], p) = b.uy; half(L.uz[q], p) = b.uz;
     half(L.h0[q], p) = b.h0;
@@ -207,6 +209,15 @@ struct PixelJob {
 
 namespace {
 
+// mean += (color - mean) / f32(n + 1).  The first sample divides by 1.0, which is exact for every operand: skipped
+// (same bits).  Tolerance mode multiplies by the MUFU reciprocal.
+template <bool F>
+__device__ __forceinline__ f3 running_mean(f3 mean, f3 color, uint32_t n) {
+    const f3 delta = rtc::sub(color, mean);
+    if (n == 0u) return rtc::add(mean, delta);
+    if constexpr (F) return rtc::axpy_t<true>(rtc::fastm::rcp((float)(n + 1u)), delta, mean);
+    else return rtc::add(mean, rtc::divs(delta, (float)(n + 1u)));
+}
 // Load the texels of one warp tile, apply the reset / sample-count rule of `update`
 // (compute_shader.wgsl:339-353) and arm the primary rays (get_ray, :305-325).
 __device__ __forceinline__ void begin_tile(const UpdateParams& P, uint32_t tile, int lane, uint32_t seed_bits,
@@ -285,8 +296,7 @@ __device__ __forceinline__ void end_tile(const UpdateParams& P, const Lanes& L, 
         if (J.sampling[p]) {
             f3 color = J.black[p] ? rtc::mk(0.0f, 0.0f, 0.0f)
                                   : rtc::sky_times(J.factor[p], rtc::mk(L.dx[p], L.dy[p], L.dz[p]));
-            float denom = (float)(n + 1u);
-            mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), denom));
+            mean = running_mean<false>(mean, color, n);
             n += 1u;
         }
         *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
@@ -475,6 +485,7 @@ __device__ __forceinline__ void prim_exact(uint32_t cand, int idx, const float4 
 
 // Primary rays of a strip (get_ray, compute_shader.wgsl:305-325): exact (d, o) parked in shared memory, unit
 // directions in registers.  `untraced` collects sampling rays outside primary_arm's window.
+template <bool F>
 __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
                                            float* __restrict__ s_tmp, uint32_t seed_bits, uint32_t spp, bool reset, PrimLanes& L,
                                            uint32_t& untraced) {
@@ -490,7 +501,7 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
             if (!reset) n = rtc::f2u(P.accum[(size_t)row * P.width + x].w);
             if (n < spp) {
                 const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
-                const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
+                const rtc::Ray r = rtc::get_ray<F>(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
                 d = r.d;
                 o = r.o;
                 L.alive |= 1u << p;
@@ -499,7 +510,7 @@ __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row
         // unit direction of the common-origin test (rtc::primary_arm), here in the rolled loop: parked in the slots
         // of the nearest hit, which are initialised when the directions are picked up below
         float ux, uy, uz, inv = __int_as_float(0x7f800000);
-        const bool ok = rtc::primary_arm(d, rtc::dot(d, d), &ux, &uy, &uz, &inv);
+        const bool ok = rtc::primary_arm<F>(d, rtc::dot(d, d), &ux, &uy, &uz, &inv);
         if (!ok && (L.alive & (1u << p))) {
             untraced |= 1u << p;
             L.alive &= ~(1u << p);
@@ -710,6 +721,7 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
 }
 
 // Running mean and texel store for a finished path (compute_shader.wgsl:356-363).
+template <bool F = false>
 __device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t texel_index, uint32_t n, f3 color, bool reset) {
     float4* texel = &P.accum[texel_index];
     f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
@@ -717,7 +729,7 @@ __device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t t
         const float4 t = *texel;
         mean = rtc::mk(t.x, t.y, t.z);
     }
-    mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+    mean = running_mean<F>(mean, color, n);
     *texel = make_float4(mean.x, mean.y, mean.z, (float)(n + 1u));
 }
 
@@ -742,24 +754,25 @@ __device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_b
 
 // What happens to a traced ray (compute_shader.wgsl:267-296): returns true when the path continues (then o, d,
 // factor are the scattered ray), false when the texel has been finished.
+template <bool F = false>
 __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
                                             f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
                                             bool reset) {
     if (best_i < 0) {
-        finalize_texel(P, texel_index, n, rtc::sky_times(factor, d), reset);
+        finalize_texel<F>(P, texel_index, n, rtc::sky_times<F>(factor, d), reset);
         return false;
     }
     const GpuSphere sp = load_sphere(P.spheres, best_i);
     rtc::Ray r;
     r.o = o;
     r.d = d;
-    const bool ok = rtc::scatter(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
+    const bool ok = rtc::scatter<F>(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
     if (!ok) {
-        finalize_texel(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
+        finalize_texel<F>(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
         return false;
     }
     if (last) {
-        finalize_texel(P, texel_index, n, rtc::sky_times(factor, r.d), reset);
+        finalize_texel<F>(P, texel_index, n, rtc::sky_times<F>(factor, r.d), reset);
         return false;
     }
     o = r.o;
@@ -773,10 +786,10 @@ __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t boun
 //         attenuation and the outgoing direction, sky colour, running mean, store (compute_shader.wgsl:267-296,
 //         356-363) — and no second kernel runs.
 // kMode = kPrimQueue (wavefront, 1 < max_depth <= kWfMaxDepth): the first hit is resolved here as well — texel finished
-//         (miss, absorbed) or the scattered path appended to queue 1 (resolve_hit + push_path, what shade_first_kernel
-//         did from P.first_hit in a pass of its own: 8 B written and read back per texel, every ray generated twice).
+//         (miss, absorbed) or the scattered path appended to queue 1 (resolve_hit; a texel-per-thread pass of its own
+//         over P.first_hit did this in round 1: 8 B written and read back per texel, every ray generated twice).
 constexpr int kPrimHits = 0, kPrimShade = 1, kPrimQueue = 2;
-template <int kMode>
+template <int kMode, bool F>
 __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
                                             const PrimLanes& L, uint32_t untraced, uint32_t seed_bits, bool reset,
                                             uint32_t& rays) {
@@ -809,7 +822,7 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 ++rays;
                 f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
                 const uint32_t bseed = 2u + n + seed_bits;   // hash seed of bounce 0 (compute_shader.wgsl:353, 268)
-                if (resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset)) {
+                if (resolve_hit<F>(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset)) {
                     dp[0] = d.x; dp[kPrimThreads] = d.y; dp[2 * kPrimThreads] = d.z;
                     dp[3 * kPrimThreads] = o.x; dp[4 * kPrimThreads] = o.y; dp[5 * kPrimThreads] = o.z;
                     dp[6 * kPrimThreads] = __uint_as_float(n);
@@ -896,10 +909,10 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 if (best_i >= 0) {
                     const GpuSphere sp = load_sphere(P.spheres, best_i);
                     const uint32_t seed = 1u + n + seed_bits;                       // compute_shader.wgsl:353
-                    black = !rtc::scatter(&r, &factor, best_t, sp, rtc::hash(seed + 1u));   // :268 with i = 0
+                    black = !rtc::scatter<F>(&r, &factor, best_t, sp, rtc::hash(seed + 1u));   // :268 with i = 0
                 }
-                const f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times(factor, r.d);
-                mean = rtc::add(mean, rtc::divs(rtc::sub(color, mean), (float)(n + 1u)));
+                const f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times<F>(factor, r.d);
+                mean = running_mean<F>(mean, color, n);
                 n += 1u;
             }
             *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
@@ -954,7 +967,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
 // finishes the texels.  Shared memory per warp: the per-ray slots (8 KB) and the warp's work stack and candidate
 // lists (2.1 KB); 2 CTAs of 11 warps per SM (rt_kernels.cuh).
-template <int kMode>
+template <int kMode, bool F>
 __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
@@ -974,18 +987,14 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
     const uint32_t tiles_x = (P.width + kPrimTileW - 1) / kPrimTileW;
     const uint32_t n_tiles = tiles_x * ((P.row_count + kPrimTileH - 1) / kPrimTileH);
     PrimTree T;
-    T.rec = P.prim_tree;
-    T.link = reinterpret_cast<const uint32_t*>(static_cast<const unsigned char*>(P.cl_blob) + (size_t)P.cl_n_nodes * kTreeStride * 16u);
-    T.first_leaf = P.cl_first_leaf;
-    T.n_entry = P.cl_n_entry;
     {
+        const rtt::ImageLayout lay = rtt::image_layout(P.cl_n_nodes, P.cl_n_entry);
         const unsigned char* blob = static_cast<const unsigned char*>(P.cl_blob);
-        const size_t off_link = (size_t)P.cl_n_nodes * kTreeStride * 16u;
-        const size_t off_r = off_link + ((size_t)P.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
-        const size_t off_entry = off_r + ((size_t)P.cl_n_nodes * 4u + 15u) / 16u * 16u;
-        const uint32_t n_entry_pad = (P.cl_n_entry + 3u) / 4u * 4u;
-        const size_t off_entry_node = off_entry + (size_t)n_entry_pad * 16u;
-        T.entry_node = reinterpret_cast<const uint32_t*>(blob + off_entry_node);
+        T.rec = P.prim_tree;
+        T.link = reinterpret_cast<const uint32_t*>(blob + lay.off_link);
+        T.first_leaf = P.cl_first_leaf;
+        T.n_entry = P.cl_n_entry;
+        T.entry_node = reinterpret_cast<const uint32_t*>(blob + lay.off_entry_node);
         T.entry_rec = P.prim_tree + (size_t)P.cl_n_nodes * kTreeStride;
     }
     uint32_t exact_tests = 0, rays = 0;
@@ -999,14 +1008,14 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
         const int row0 = (int)((tile / tiles_x) * kPrimTileH);
         PrimLanes L;
         uint32_t untraced;
-        prim_setup(P, x, row0, s_d, reinterpret_cast<float*>(s_rec) + lane, seed_bits, spp, reset, L, untraced);
+        prim_setup<F>(P, x, row0, s_d, reinterpret_cast<float*>(s_rec) + lane, seed_bits, spp, reset, L, untraced);
         if (__any_sync(kFull, L.alive != 0u)) {
             f3 m;
             float chord;
             prim_tile_bound(L, m, chord);
             prim_tree_walk(T, s_work, s_rec, s_idx, s_near, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
-        prim_finish<kMode>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
+        prim_finish<kMode, F>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
     }
     prim_flush(P, exact_tests, rays, lane);
 }
@@ -1014,8 +1023,8 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
 // ---------------------------------------------------------------------------------------------
 // Wavefront bounces (max_depth > 1 behind a primary pass).  Paths that survive
 // a bounce are compacted into a queue, so every traversal launch works on dense warps of live rays
-// instead of dragging finished pixels along: shade_first_kernel turns first_hit into colours or
-// queued paths, bounce_kernel traces queue b (general 7-FFMA broad phase, records streamed through
+// instead of dragging finished pixels along: the primary pass (kPrimQueue) turns first hits into colours or
+// queued paths, the bounce kernel traces queue b (general 7-FFMA broad phase, records streamed through
 // shared memory by bulk copies) and appends the survivors to queue b + 1.  Bounce rays are incoherent,
 // so the exact tests are DEFERRED: a thread notes the groups in which one of its rays passed the broad
 // test and the warp drains those notes together, every lane working on its own candidates, instead of
@@ -1113,61 +1122,11 @@ __device__ __forceinline__ void scan_spheres_deferred(const float4* __restrict__
 
 }  // namespace
 
-// One thread per texel: the `update` bookkeeping around the primary hit found by primary_hits_kernel<kPrimHits>.
-// Superseded by primary_hits_kernel<kPrimQueue>; kept as the A/B arm (-DRT_WF_SEPARATE_SHADE=1).
-__global__ void __launch_bounds__(256) shade_first_kernel(const __grid_constant__ UpdateParams P) {
-    const uint64_t n_texels = (uint64_t)P.width * P.row_count;
-    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int lane = threadIdx.x & 31;
-    const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
-    const uint32_t spp = rtc::f2u(P.cam.samples_per_pixel);
-    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
-    const bool reset = P.cam.camera_has_moved > 0.5f;
-    bool push = false;
-    f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = rtc::mk(1.0f, 1.0f, 1.0f);
-    uint32_t bseed = 0, n = 0, rays = 0, exact_tests = 0;
-    if (t < n_texels) {
-        const int row = (int)(t / P.width), x = (int)(t % P.width);
-        if (!reset) n = rtc::f2u(P.accum[t].w);
-        if (n < spp) {
-            const uint32_t seed = 1u + n + seed_bits;   // compute_shader.wgsl:353
-            const rtc::Ray r = rtc::get_ray(P.cam, x, (int)P.row_begin + row, seed, seed_bits);
-            o = r.o;
-            d = r.d;
-            bseed = seed + 1u;
-            const float2 fh = P.first_hit[t];
-            float best_t = fh.x;
-            int best_i = __float_as_int(fh.y);
-            if (best_i == -2) {
-                // not traced by the primary pass: the reference loop itself (compute_shader.wgsl:164-180)
-                const float a = rtc::dot(d, d);
-                best_t = kTMax;
-                best_i = -1;
-                for (uint32_t si = 0; si < P.n_spheres; ++si) {
-                    const float4 g = __ldg(reinterpret_cast<const float4*>(P.spheres + si));
-                    float root;
-                    ++exact_tests;
-                    if (rtc::sphere_root(o, d, a, rtc::mk(g.x, g.y, g.z), g.w, kTMin, best_t, &root)) {
-                        best_t = root;
-                        best_i = (int)si;
-                    }
-                }
-            }
-            rays = 1;
-            push = resolve_hit(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, (uint32_t)t, bseed, n, reset);
-        } else if (reset) {
-            P.accum[t] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // reset rule with nothing to sample (spp == 0)
-        }
-    }
-    push_path(P, 1u, push, o, d, factor, (uint32_t)t, bseed, n, lane);
-    prim_flush(P, exact_tests, rays, lane);
-}
-
 namespace {
 
 // Rays j0 + p (p < NR) of the queue — consecutive entries, paths of neighbouring pixels, so the two rays of an FFMA2
 // pair tend to meet the same clusters — into the thread's first NR lanes; the others idle.
-template <int NR>
+template <int NR, bool F = false>
 __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                              uint32_t j0, Lanes& L, uint32_t& rays) {
 #pragma unroll
@@ -1175,7 +1134,7 @@ __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4
         const uint32_t j = j0 + (uint32_t)p;
         if (p < NR && j < count) {
             const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
-            arm_ray(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
+            arm_ray<F>(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
             ++rays;
         } else {
             idle_ray(L, p);
@@ -1238,7 +1197,7 @@ __device__ __forceinline__ uint32_t parked_word(const CandT* s_cand, int k) {
     if constexpr (sizeof(CandT) == 4) return s_cand[k * kBlockThreads];
     else return (uint32_t)s_cand[(2 * k) * kBlockThreads] | ((uint32_t)s_cand[(2 * k + 1) * kBlockThreads] << 16);
 }
-template <typename CandT>
+template <bool F, typename CandT>
 __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
                                                  const Lanes& L, uint32_t bounce, bool last, bool reset, int lane,
                                                  CandT* s_park) {
@@ -1262,7 +1221,7 @@ __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const fl
             d = second ? rtc::mk(L.dx[1], L.dy[1], L.dz[1]) : rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
             const float best_t = second ? L.best_t[1] : L.best_t[0];
             const int best_i = second ? L.best_i[1] : L.best_i[0];
-            push = resolve_hit(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+            push = resolve_hit<F>(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
         }
         if (p == 0) {
             push0 = push;
@@ -1330,18 +1289,15 @@ struct TreeView {
 __device__ __forceinline__ TreeView tree_view(const void* blob, uint32_t n_nodes, uint32_t first_leaf, uint32_t n_entry,
                                               float entry_r, uint32_t stack_cap) {
     const unsigned char* b = static_cast<const unsigned char*>(blob);
+    const rtt::ImageLayout lay = rtt::image_layout(n_nodes, n_entry);
     TreeView tv;
     tv.rec = reinterpret_cast<const float4*>(b);
-    const size_t off_link = (size_t)n_nodes * kTreeStride * 16u;
-    tv.link = reinterpret_cast<const uint32_t*>(b + off_link);
-    const size_t off_r = off_link + ((size_t)n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
-    tv.node_r = reinterpret_cast<const float*>(b + off_r);
-    const size_t off_entry = off_r + ((size_t)n_nodes * 4u + 15u) / 16u * 16u;
-    const uint32_t n_entry_pad = (n_entry + 3u) / 4u * 4u;
-    tv.entry_rec = reinterpret_cast<const float4*>(b + off_entry);
-    tv.entry_node = reinterpret_cast<const uint32_t*>(b + off_entry + (size_t)n_entry_pad * 16u);
+    tv.link = reinterpret_cast<const uint32_t*>(b + lay.off_link);
+    tv.node_r = reinterpret_cast<const float*>(b + lay.off_r);
+    tv.entry_rec = reinterpret_cast<const float4*>(b + lay.off_entry_rec);
+    tv.entry_node = reinterpret_cast<const uint32_t*>(b + lay.off_entry_node);
     tv.first_leaf = (int)first_leaf;
-    tv.n_entry_pad = (int)n_entry_pad;
+    tv.n_entry_pad = (int)lay.n_entry_pad;
     tv.stack_cap = (int)stack_cap;
     tv.entry_r = entry_r;
     return tv;
@@ -1479,16 +1435,10 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 // remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
 // costs the full-queue loops of bounce_kernel 3 % (measured), and it runs when the machine is mostly idle anyway.
-#ifndef RT_WF_BATCH_APPEND
-#define RT_WF_BATCH_APPEND 1
-#endif
-#ifndef RT_WF_SEPARATE_SHADE
-#define RT_WF_SEPARATE_SHADE 0
-#endif
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
 #endif
-template <typename CandT>
+template <bool F, typename CandT>
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                           const TreeView& tv, unsigned short* __restrict__ s_stack, CandT* __restrict__ s_cand,
                                           unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
@@ -1503,7 +1453,7 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
         if (batch >= n_batches) break;
         const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
         Lanes L;
-        wf_load_rays<2>(P, qin, count, j0, L, rays);
+        wf_load_rays<2, F>(P, qin, count, j0, L, rays);
         f3 factor[2];
         uint32_t texel_index[2], bseed[2], n_samples[2];
 #pragma unroll
@@ -1525,10 +1475,10 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
             for (int p = 0; p < 2; ++p) {
                 if (!L.alive[p]) continue;
                 f3 o = origin_of(L, p), d = rtc::mk(L.dx[p], L.dy[p], L.dz[p]);
-                const bool go = resolve_hit(P, b, b + 1u >= max_depth, L.best_i[p], L.best_t[p], o, d, factor[p],
-                                            texel_index[p], bseed[p], n_samples[p], reset);
+                const bool go = resolve_hit<F>(P, b, b + 1u >= max_depth, L.best_i[p], L.best_t[p], o, d, factor[p],
+                                               texel_index[p], bseed[p], n_samples[p], reset);
                 if (go) {
-                    arm_ray(L, p, o, d);
+                    arm_ray<F>(L, p, o, d);
                 } else {
                     idle_ray(L, p);
                 }
@@ -1569,7 +1519,7 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
 // kGlobal: the instantiation for scenes whose image does not fit shared memory (cl_bytes == 0): the same traversal
 // reads the tree where it lies in global memory (L1 / L2; the upper levels stay hot), and the candidate codes are
 // 32 bits wide, so the sphere count is not limited by the code's 15 index bits either.
-template <bool kFinish, bool kGlobal>
+template <bool kFinish, bool kGlobal, bool F>
 __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
@@ -1616,16 +1566,12 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
             if (batch >= n_batches) break;
             const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
             Lanes L;
-            wf_load_rays<2>(P, qin, count, j0, L, rays);
+            wf_load_rays<2, F>(P, qin, count, j0, L, rays);
             trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
-#if RT_WF_BATCH_APPEND
-            wf_resolve_batch(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
-#else
-            wf_resolve<2>(P, qin, count, j0, L, bounce, last, reset, lane);
-#endif
+            wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
         }
     } else {
-        finish_paths(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+        finish_paths<F>(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
     }
     wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
 }
@@ -1706,9 +1652,14 @@ __global__ void prep_primary_tree_kernel(const float4* __restrict__ tree_rec, co
                                          const float* __restrict__ child_r, const GpuSphere* __restrict__ spheres,
                                          const uint32_t* __restrict__ entry_slot, uint32_t n_entry,
                                          float4* __restrict__ out, uint32_t n_nodes, uint32_t first_leaf, float ox, float oy,
-                                         float oz, double rho, float m_cam) {
-    // threads past the child slots write the entry list's records once more, contiguously, behind them
+                                         float oz, double rho, float m_cam, unsigned int* __restrict__ tile_counter,
+                                         unsigned int* __restrict__ wf_counts) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    // the frame's tile tickets and (deep frames) queue lengths, batch tickets and per-bounce counters start at zero:
+    // done here rather than by memset nodes of their own, the kernels that use them are ordered behind this one
+    if (t < 2u) tile_counter[t] = 0u;
+    if (wf_counts != nullptr && t < kWfWords) wf_counts[t] = 0u;
+    // threads past the child slots write the entry list's records once more, contiguously, behind them
     if (t >= n_nodes * kTreeStride + n_entry) return;
     uint32_t slot = t;
     if (t >= n_nodes * kTreeStride) {
@@ -1929,35 +1880,31 @@ static size_t clustered_global_smem_bytes(uint32_t stack_cap) {   // tree in glo
     return (size_t)kWfCand * kBlockThreads * sizeof(uint32_t) + (size_t)stack_cap * kBlockThreads * sizeof(unsigned short);
 }
 
+template <typename K>
+static cudaError_t set_smem(K kernel, size_t bytes) {
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
 cudaError_t configure_kernels() {
-    cudaError_t e = cudaFuncSetAttribute(update_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)((kResidentMaxSpheres + kGeomTail) * sizeof(float4)));
+    cudaError_t e = set_smem(update_resident_kernel, (kResidentMaxSpheres + kGeomTail) * sizeof(float4));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimHits>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)prim_smem_bytes());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimShade>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)prim_smem_bytes());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(primary_hits_kernel<kPrimQueue>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)prim_smem_bytes());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bounce_smem_bytes());
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_global_smem_bytes(kTreeStackMax));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(bounce_clustered_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)clustered_global_smem_bytes(kTreeStackMax));
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(update_streamed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(2 * (kChunkSpheres + kGeomTail) * sizeof(float4)));
+    const size_t prim = prim_smem_bytes();
+    if ((e = set_smem(primary_hits_kernel<kPrimHits, false>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimShade, false>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimQueue, false>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimShade, true>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimQueue, true>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_streamed_kernel, bounce_smem_bytes())) != cudaSuccess) return e;
+    const size_t cl = clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax), clg = clustered_global_smem_bytes(kTreeStackMax);
+    if ((e = set_smem(bounce_clustered_kernel<false, false, false>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, false, false>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, true, false>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, true, false>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, false, true>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, false, true>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, true, true>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, true, true>, clg)) != cudaSuccess) return e;
+    return set_smem(update_streamed_kernel, 2 * (kChunkSpheres + kGeomTail) * sizeof(float4));
 }
 
 bool fused_shade_applies(const UpdateParams& p, int variant) {
@@ -1967,6 +1914,23 @@ bool fused_shade_applies(const UpdateParams& p, int variant) {
 bool primary_pass_applies(const UpdateParams& p) {
     return p.prim_tree != nullptr && p.cl_n_nodes != 0u && p.first_hit != nullptr && p.n_spheres > 0 && rtc::primary_rho(p.cam) >= 0.0 &&
            rtc::f2u(p.cam.max_depth) > 0u;
+}
+
+// One bounce launch of the wavefront: which instantiation depends on where the tree lives, whether this launch may finish
+// a short queue to the end, and the precision mode.
+template <bool F>
+static void launch_bounce(const UpdateParams& p, bool finishing, uint32_t full_grid, uint32_t finish_grid, cudaStream_t stream) {
+    if (p.cl_bytes == 0u && p.cl_global != 0u) {   // the tree stays in global memory
+        const size_t smem = clustered_global_smem_bytes(p.cl_stack_cap);
+        if (!finishing) bounce_clustered_kernel<false, true, F><<<full_grid, kBlockThreads, smem, stream>>>(p);
+        else bounce_clustered_kernel<true, true, F><<<finish_grid, kBlockThreads, smem, stream>>>(p);
+    } else if (p.cl_bytes == 0u) {   // no tree the bounce kernel can walk (node numbers beyond 16 bits): exact mode only
+        bounce_streamed_kernel<<<finish_grid, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
+    } else {
+        const size_t smem = clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap);
+        if (!finishing) bounce_clustered_kernel<false, false, F><<<full_grid, kBlockThreads, smem, stream>>>(p);
+        else bounce_clustered_kernel<true, false, F><<<finish_grid, kBlockThreads, smem, stream>>>(p);
+    }
 }
 
 cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
@@ -1983,12 +1947,9 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         if (launches) *launches = 1;
         return cudaGetLastError();
     }
-    cudaError_t e = cudaMemsetAsync(p.tile_counter, 0, 2 * sizeof(unsigned int), stream);
-    if (e != cudaSuccess) return e;
+    cudaError_t e;
     const uint32_t resident = (uint32_t)sm_count * 2u;
     if (primary) {
-        e = launch_prep_primary_tree(p, stream);
-        if (e != cudaSuccess) return e;
         const uint32_t tiles = ((p.width + kPrimTileW - 1) / kPrimTileW) * ((p.row_count + kPrimTileH - 1) / kPrimTileH);
         constexpr uint32_t warps = kPrimThreads / 32;
         uint32_t blocks = (tiles + warps - 1) / warps;
@@ -1996,13 +1957,20 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         const uint32_t depth = rtc::f2u(p.cam.max_depth);
         const bool shade = depth == 1u;
         const bool wavefront = !shade && p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth;
-        if (wavefront) {   // queue lengths, batch tickets and per-bounce counters of this frame
-            e = cudaMemsetAsync(p.wf_counts, 0, kWfWords * sizeof(unsigned int), stream);
-            if (e != cudaSuccess) return e;
+        // tolerance mode exists for the fused depth-1 pass and the wavefront; the other paths are exact whatever the mode
+        const bool fast = p.precision != 0u && (shade || wavefront);
+        // per-frame records; the same launch zeroes the tile tickets and (wavefront) the frame's queue counters
+        e = launch_prep_primary_tree(p, wavefront, stream);
+        if (e != cudaSuccess) return e;
+        if (shade) {
+            if (fast) primary_hits_kernel<kPrimShade, true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else primary_hits_kernel<kPrimShade, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        } else if (wavefront) {
+            if (fast) primary_hits_kernel<kPrimQueue, true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else primary_hits_kernel<kPrimQueue, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+        } else {
+            primary_hits_kernel<kPrimHits, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         }
-        if (shade) primary_hits_kernel<kPrimShade><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
-        else if (wavefront && !RT_WF_SEPARATE_SHADE) primary_hits_kernel<kPrimQueue><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
-        else primary_hits_kernel<kPrimHits><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         n_launch += 2;
@@ -2013,10 +1981,6 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         if (wavefront) {
             // the primary pass has resolved the first hits and queued the survivors (kPrimQueue): one launch per bounce
             const uint64_t n_texels = (uint64_t)p.width * p.row_count;
-            if (RT_WF_SEPARATE_SHADE) {   // A/B arm: first hits resolved from P.first_hit by a pass of their own
-                shade_first_kernel<<<(unsigned)((n_texels + 255) / 256), 256, 0, stream>>>(p);
-                n_launch += 1;
-            }
             // First bounce launched with the finishing code compiled in: not before the queue can be short enough to
             // use it, assuming it shrinks by no more than a fifth per bounce (texels * 0.8^b < 8 * the short-queue
             // threshold).  A scene that sheds paths faster only delays the switch by a few cheap launches.
@@ -2026,23 +1990,16 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (p.cl_bytes == 0u && p.cl_global != 0u) {   // the tree stays in global memory
-                    const size_t smem = clustered_global_smem_bytes(p.cl_stack_cap);
-                    if (b < finish_from) bounce_clustered_kernel<false, true><<<(uint32_t)sm_count * 3u, kBlockThreads, smem, stream>>>(p);
-                    else bounce_clustered_kernel<true, true><<<resident, kBlockThreads, smem, stream>>>(p);
-                } else if (p.cl_bytes == 0u) {   // no tree the bounce kernel can walk (node numbers beyond 16 bits)
-                    bounce_streamed_kernel<<<resident, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
-                } else if (b < finish_from) {
-                    bounce_clustered_kernel<false, false><<<(uint32_t)sm_count * 3u, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
-                } else {
-                    bounce_clustered_kernel<true, false><<<resident, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
-                }
+                if (fast) launch_bounce<true>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
+                else launch_bounce<false>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
                 n_launch += 1;
             }
             if (launches) *launches = n_launch;
             return cudaGetLastError();
         }
     }
+    e = cudaMemsetAsync(p.tile_counter, 0, 2 * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
     const uint32_t n_pad = (p.n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
     uint32_t blocks = (p.n_tiles + 7) / 8;
     if (blocks > resident) blocks = resident;
@@ -2056,22 +2013,61 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
     return cudaGetLastError();
 }
 
-cudaError_t launch_prep_primary_tree(const UpdateParams& p, cudaStream_t stream) {
+cudaError_t launch_prep_primary_tree(const UpdateParams& p, bool zero_wavefront, cudaStream_t stream) {
+    const rtt::ImageLayout lay = rtt::image_layout(p.cl_n_nodes, p.cl_n_entry);
     const unsigned char* blob = static_cast<const unsigned char*>(p.cl_blob);
-    const size_t off_link = (size_t)p.cl_n_nodes * kTreeStride * 16u;
-    const size_t off_r = off_link + ((size_t)p.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
-    const size_t off_entry = off_r + ((size_t)p.cl_n_nodes * 4u + 15u) / 16u * 16u;
-    const uint32_t n_entry_pad = (p.cl_n_entry + 3u) / 4u * 4u;
-    const size_t off_child_r = off_entry + (size_t)n_entry_pad * 16u + ((size_t)n_entry_pad * 4u + 15u) / 16u * 16u;
     const double rho = rtc::primary_rho(p.cam);
     const float m_cam = rtc::primary_m_cam(p.cam, rho);
-    const size_t off_entry_slot = off_child_r + ((size_t)p.cl_n_nodes * kTreeWide * 4u + 15u) / 16u * 16u;
-    const uint32_t n_slots = p.cl_n_nodes * kTreeStride + p.cl_n_entry;
-    prep_primary_tree_kernel<<<(n_slots + 255) / 256, 256, 0, stream>>>(
-        reinterpret_cast<const float4*>(blob), reinterpret_cast<const uint32_t*>(blob + off_link),
-        reinterpret_cast<const float*>(blob + off_child_r), p.spheres, reinterpret_cast<const uint32_t*>(blob + off_entry_slot),
+    uint32_t n_threads = p.cl_n_nodes * kTreeStride + p.cl_n_entry;
+    if (n_threads < kWfWords) n_threads = kWfWords;
+    prep_primary_tree_kernel<<<(n_threads + 255) / 256, 256, 0, stream>>>(
+        reinterpret_cast<const float4*>(blob), reinterpret_cast<const uint32_t*>(blob + lay.off_link),
+        reinterpret_cast<const float*>(blob + lay.off_child_r), p.spheres, reinterpret_cast<const uint32_t*>(blob + lay.off_entry_slot),
         p.cl_n_entry, const_cast<float4*>(p.prim_tree), p.cl_n_nodes,
-        p.cl_first_leaf, p.cam.center.x, p.cam.center.y, p.cam.center.z, rho, m_cam);
+        p.cl_first_leaf, p.cam.center.x, p.cam.center.y, p.cam.center.z, rho, m_cam, p.tile_counter,
+        zero_wavefront ? p.wf_counts : nullptr);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Completion flags of a fused gather (rt_stream_signal / rt_stream_wait): one release store, resp. a bounded spin of
+// acquire loads, at system scope — the flag may live in a peer GPU's memory.
+// ---------------------------------------------------------------------------------------------
+__global__ void signal_kernel(unsigned int* flag, unsigned int value) {
+    // the stores of the kernels ahead of this one in the stream have been performed; the fence orders them before the
+    // flag for an observer on another device
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
+__global__ void wait_flags_kernel(const unsigned int* flags, unsigned int n, unsigned int value, unsigned long long timeout_ns,
+                                  unsigned int* status) {
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) {
+        for (;;) {
+            unsigned int v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+            if ((int)(v - value) >= 0) break;
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) {   // never hang the device on a peer that does not come
+                atomicAdd(status, 1u);
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+    __threadfence_system();
+}
+
+cudaError_t launch_signal(void* flag, uint32_t value, cudaStream_t stream) {
+    signal_kernel<<<1, 1, 0, stream>>>(static_cast<unsigned int*>(flag), value);
+    return cudaGetLastError();
+}
+cudaError_t launch_wait_flags(const void* flags, uint32_t n, uint32_t value, uint32_t timeout_ms, unsigned int* status,
+                              cudaStream_t stream) {
+    wait_flags_kernel<<<1, 32, 0, stream>>>(static_cast<const unsigned int*>(flags), n, value, (unsigned long long)timeout_ms * 1000000ull, status);
     return cudaGetLastError();
 }
 

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include "../../include/rt_abi.h"
+#include "rt_tree_layout.h"
 
 
 namespace rtk {
@@ -48,8 +49,8 @@ constexpr int kPrimWork = RT_PRIM_WORK;   // per-warp stack of tree nodes awaiti
 constexpr int kPrimList = RT_PRIM_LIST;   // per-warp list of spheres that passed the tile test, scanned when it fills
 constexpr uint32_t kWfMaxDepth = 64; // deeper paths fall back to the in-kernel bounce loop of variants 2 / 3
 constexpr uint32_t kWfWords = 3 * (kWfMaxDepth + 1);   // length of wf_counts
-constexpr int kTreeWide = 8;                           // children per node of the bounce rays' tree (rtt::kWide)
-constexpr int kTreeStride = kTreeWide + 1;             // record slots per node in the image (rtt::kStride)
+constexpr int kTreeWide = rtt::kWide;                  // children per node of the scene's tree (rt_tree_layout.h)
+constexpr int kTreeStride = rtt::kStride;              // record slots per node in the image
 constexpr int kTreeBacklog = 16;                       // entry nodes a lane may stack up before the warp traverses
 constexpr uint32_t kTreeStackMax = 96;                 // deepest per-thread node stack the bounce kernel is configured for
 constexpr uint32_t kWfFinishFrom = 3;                   // first bounce whose launch may finish a short queue to the end
@@ -84,7 +85,9 @@ struct UpdateParams {
     // cl_global: cl_bytes == 0 but the bounce kernel can walk the tree in global memory (node numbers fit 16 bits)
     uint32_t cl_n_nodes, cl_first_leaf, cl_bytes, cl_stack_cap, cl_n_entry, cl_global;
     float cl_entry_r;
-    uint32_t* rgba8_out;            // non-null: the fused shading pass (max_depth 1) also stores the texel's RGBA8 here
+    uint32_t* rgba8_out;            // non-null: the fused shading pass (max_depth 1) also stores the texel's RGBA8 here:
+                                    // window-relative texel index, in this device's memory or in a peer's (NVLink stores)
+    uint32_t precision;             // RT_PRECISION_EXACT / RT_PRECISION_FAST (rt_set_precision)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };
 
@@ -97,9 +100,12 @@ bool primary_pass_applies(const UpdateParams& p);
 bool fused_shade_applies(const UpdateParams& p, int variant);
 // variant 4 = common-origin primary pass followed by the update kernel (chosen by variant 0 whenever the camera is
 // a pinhole, defocus_angle <= 0); p.prim / p.first_hit must be set.
-cudaError_t launch_prep_primary_tree(const UpdateParams& p, cudaStream_t stream);
+cudaError_t launch_prep_primary_tree(const UpdateParams& p, bool zero_wavefront, cudaStream_t stream);
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream);
 cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream);
+cudaError_t launch_signal(void* flag, uint32_t value, cudaStream_t stream);
+cudaError_t launch_wait_flags(const void* flags, uint32_t n, uint32_t value, uint32_t timeout_ms, unsigned int* status,
+                              cudaStream_t stream);
 cudaError_t configure_kernels();   // one-off cudaFuncSetAttribute calls
 
 }  // namespace rtk

@@ -28,11 +28,10 @@
 #include <vector>
 
 #include "rt_core.cuh"
+#include "rt_tree_layout.h"
 
 namespace rtt {
 
-constexpr int kWide = 8;                // children per node
-constexpr int kStride = kWide + 1;      // record slots per node in the image: the odd stride spreads the nodes over the banks
 constexpr uint32_t kMaxEntry = 160;     // longest entry list (coherent scan) before the per-lane traversal takes over
 constexpr uint32_t kMaxAlways = 64;     // at most this many oversized spheres are pulled out of the tree
 constexpr double kMargin = 0.0078125;   // 2^-7
@@ -60,15 +59,16 @@ struct Tree {
 
     // Device image: [rec | link | node_r | entry_rec | entry_node | child_r | entry_slot], every part padded to 16 bytes.  The
     // bounce kernel copies the image up to child_r (bounce_bytes) into shared memory.
-    static size_t pad16(size_t b) { return (b + 15) / 16 * 16; }
-    size_t off_link() const { return (size_t)n_nodes * kStride * 16; }
-    size_t off_r() const { return off_link() + pad16((size_t)n_nodes * kWide * 4); }
-    size_t off_entry_rec() const { return off_r() + pad16((size_t)n_nodes * 4); }
-    size_t off_entry_node() const { return off_entry_rec() + (size_t)n_entry_pad * 16; }
-    size_t off_child_r() const { return off_entry_node() + pad16((size_t)n_entry_pad * 4); }
-    size_t bounce_bytes() const { return off_child_r(); }
-    size_t off_entry_slot() const { return off_child_r() + pad16((size_t)n_nodes * kWide * 4); }
-    size_t bytes() const { return off_entry_slot() + pad16((size_t)n_entry_pad * 4); }
+    // offsets: rt_tree_layout.h, the one definition the kernels use as well
+    ImageLayout layout() const { return image_layout(n_nodes, n_entry); }
+    size_t off_link() const { return layout().off_link; }
+    size_t off_r() const { return layout().off_r; }
+    size_t off_entry_rec() const { return layout().off_entry_rec; }
+    size_t off_entry_node() const { return layout().off_entry_node; }
+    size_t off_child_r() const { return layout().off_child_r; }
+    size_t bounce_bytes() const { return layout().off_child_r; }
+    size_t off_entry_slot() const { return layout().off_entry_slot; }
+    size_t bytes() const { return layout().bytes; }
     void pack(unsigned char* blob) const {
         memset(blob, 0, bytes());
         memcpy(blob, rec.data(), rec.size() * 4);

@@ -168,6 +168,22 @@ RT_API int rt_read_wait(RtRenderer* r);   /* every asynchronous read issued so f
  * image, into the buffer the next rt_read_rgba8_async sends, so that read needs no quantise pass of its own (one kernel
  * less per frame, 166 MB less HBM traffic at 4K).  Other updates and reads behave as before.  Off by default. */
 RT_API int rt_set_rgba8_output(RtRenderer* r, int enable);
+/* Fused gather.  device_rgba8 != NULL: updates whose shading is finished inside the primary pass (max_depth == 1) store
+ * the window's RGBA8 texels straight to device_rgba8[window-relative texel index] — device memory of this GPU or of a
+ * peer (mapped with rt_ipc_open, or any pointer of a peer with access enabled): the row block of a sharded image lands in
+ * the owner's frame WHILE the kernel computes, 128 contiguous bytes per warp row over NVLink, and no copy follows the
+ * kernel ("the final image is gathered by peer copy over NVLink", fused into the producing pass).  NULL: off.
+ * rt_read_rgba8* keep working (they quantise into the renderer's own buffers). */
+RT_API int rt_set_rgba8_target(RtRenderer* r, void* device_rgba8);
+/* Completion protocol of such a gather, enqueued on the renderer's stream (no host synchronisation):
+ * rt_stream_signal: after everything queued so far — including the fused stores above — *device_flag = value, released at
+ * system scope (device_flag may be peer memory).  rt_stream_wait: the stream does not proceed until every one of
+ * device_flags[0..n) is >= value (wrap-safe), or `timeout_ms` of device time has passed, in which case the wait gives up
+ * and rt_stream_wait_timed_out reports it.  Together: rank i signals arrived[i] = frame + 1 behind its update, the owner
+ * waits for all of them and then knows the frame is whole. */
+RT_API int rt_stream_signal(RtRenderer* r, void* device_flag, uint32_t value);
+RT_API int rt_stream_wait(RtRenderer* r, const void* device_flags, uint32_t n, uint32_t value, uint32_t timeout_ms);
+RT_API int rt_stream_wait_timed_out(RtRenderer* r, uint32_t* count);   /* synchronises; number of waits that gave up */
 /* Device buffers that other processes can write into.  A multi-process run (one process per GPU) keeps its gather
  * target in one process (rt_device_alloc + rt_ipc_export), the others map it (rt_ipc_open, peer access enabled
  * lazily) and hand the mapped address to rt_read_rgba8_async, whose destination may be pinned host memory or device
@@ -193,6 +209,9 @@ RT_API int rt_wavefront_counts(RtRenderer* r, uint32_t* counts, uint32_t capacit
  * 2 = walked where it lies in global memory (scenes past the shared-memory budget), 3 = not walked: plain records
  * streamed (node numbers beyond 16 bits, or kernel variant 5). */
 RT_API int rt_tree_info(RtRenderer* r, uint32_t* n_nodes, uint32_t* depth, uint32_t* bounce_path);
+/* Host time (ms) of the last tree build + pack + upload; the build runs inside the first update after rt_set_scene
+ * brought new sphere bytes (the reference scene is static, src/scene/sphere.rs:167-170, so this is paid once). */
+RT_API int rt_tree_build_ms(RtRenderer* r, double* ms);
 
 /* Device-side timing of the update kernels on the renderer's own stream (CUDA events). */
 RT_API int rt_timer_begin(RtRenderer* r);
@@ -217,6 +236,19 @@ RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
  * for the bounces, 5 = as 4 with the bounce rays forced through the streamed-record kernel (the path of scenes whose
  * tree the bounce kernel cannot walk).  0 picks 4 when it applies, else 2 or 3. */
 RT_API int rt_set_kernel_variant(RtRenderer* r, int variant);
+
+/* Arithmetic of the per-ray O(1) work (camera ray, scatter, sky colour, running mean).
+ *   RT_PRECISION_EXACT (default): one IEEE-754 rounding per WGSL operator, pinned sin / cos — bit-identical to the CPU
+ *                                 oracle of this repository.
+ *   RT_PRECISION_FAST:            the same formulas through the hardware approximations (MUFU rcp / rsqrt / sqrt / sin /
+ *                                 cos, FMA contraction) — what a WGSL implementation may do too, its builtin precision
+ *                                 being implementation defined.  Which sphere a ray hits is still decided by the
+ *                                 reference's IEEE quadratic, so a depth-1 image differs from the exact one by colour
+ *                                 rounding only (<= 1/255 after RGBA8 quantisation, counted in bench.py and the tests).
+ * Applies to the primary pass with fused shading (max_depth == 1) and to the wavefront (1 < max_depth <= 64); other
+ * kernel variants ignore it. */
+enum { RT_PRECISION_EXACT = 0, RT_PRECISION_FAST = 1 };
+RT_API int rt_set_precision(RtRenderer* r, int precision);
 
 /* ---------------------------------------------------------------------------------------
  * Headless one-shot entries (new surface asked for by the port target; the reference has
