@@ -1,19 +1,29 @@
 #!/usr/bin/env python
 """bench.py — Mrays/s of the per-pixel ray-trace pass on B200 (BASELINE.json metric).
 
-Workload (config["workload"]): 1024 random spheres, 3840x2160, max_depth 1, 1 sample — one
-`update` dispatch per frame, rays == pixels.  A step renders one frame per GPU (frames of a camera
-batch are sharded over the ranks, scene replicated; weak scaling); with N > 1 every frame's RGBA8
-image is gathered to rank 0 over NCCL, overlapped with the next step's kernel.
+Workload (config["workload"]): 1024 random spheres (seed 1234), 3840x2160, max_depth 1, 1 sample — one `update`
+dispatch per frame, rays == pixels.  A step renders one frame per GPU (frames of a camera batch sharded over the ranks,
+scene replicated: weak scaling); with N > 1 every frame's RGBA8 image lands in rank 0's device memory (fused peer stores
+over NVLink out of the shading pass, completion flags behind them).
 
   python bench.py [--gpus N --steps K --warmup W]          our arm (CUDA kernels through the C ABI)
-  python bench.py --impl reference [...]                   the CPU restatement of the shader (oracle)
-                                                           on the box's host cores, same metric/config
+  python bench.py --impl reference [...]                   the CPU restatement of the shader (oracle) on the box's
+                                                           host cores, same metric / config
 
-One JSON line on stdout (rank 0).  Keys beyond the base contract: roofline (FP32-FMA bound; the
-denominator is measured in the same run by tools/ffma_peak.cu because MEASURED_PEAKS.json carries no
-FP32 figure), hbm (the accumulation-image traffic against the measured copy bandwidth),
-cpu_baseline, e2e, clocks, gpu_launches, parity.
+One JSON line on stdout (rank 0).  Every number in it is measured in this run, except the block `executed.from_capture`,
+which is loaded from a committed ncu capture (profiles/*.json) and carries the commit it was taken at.
+Keys beyond the base contract:
+  roofline      contract model (18 flop per (ray, sphere) pair over all N spheres) against the FP32-FMA peak measured in
+                this process; `model` says that the shipped kernel does not execute that work
+  executed      what the shipped kernel does execute: exact tests per ray (device counters), and — from the committed
+                capture — warp instructions per launch, issue-slot fraction, executed FP32 flop against the FMA peak
+  bruteforce    the design the port target describes (every sphere tested for every ray, shared-memory tiles, FFMA2),
+                timed in the same run: the arm for which a fraction of the FP32 peak is a meaningful figure
+  fast          the opt-in tolerance mode (rt_set_precision): time and mismatch count against the oracle
+  strong        ONE 7680x4320 image split by row blocks over the N ranks, gathered into rank 0 (BASELINE config 4)
+  weak_like_for_like   the headline step with the RGBA8 delivery every N > 1 rank performs, also at N = 1
+  sustained     the headline update looped for >= 2 s with NVML clock / power samples
+  parity, parity_libm, deep, hbm, cpu_baseline, e2e, clocks, gpu_launches
 """
 import argparse
 import ctypes as C
@@ -30,6 +40,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, N_SPHERES = 3840, 2160, 1024
+W8K, H8K = 7680, 4320
 FLOP_PER_TEST = 18   # oc 3 + h 5 + c 7 + disc 3, a = d.d hoisted (the reference's test as written)
 METRIC = "Mrays/s at 4K/1024 spheres"
 
@@ -57,65 +68,88 @@ def emit_json(line):
     os.write(_JSON_FD if _JSON_FD is not None else 1, data)
 
 
+def host_threads():
+    """Cores this process may use.  torchrun exports OMP_NUM_THREADS=1, so omp_get_max_threads() is not the answer."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def workload_config(n_gpus):
     return {
         "workload": f"{N_SPHERES} random spheres (seed 1234) at {W}x{H}, max_depth 1, 1 sample/pixel, one frame per GPU per step",
         "spheres": N_SPHERES, "width": W, "height": H, "max_depth": 1, "frames_per_step": n_gpus,
-        "parallelism": f"frames sharded over {n_gpus} GPU(s), scene replicated" + (", every frame's RGBA8 image (written by the shading pass itself) copied into rank 0's device memory over NVLink (CUDA IPC peer copy on a copy stream, overlapping the next frame)" if n_gpus > 1 else ""),
+        "parallelism": f"frames sharded over {n_gpus} GPU(s), scene replicated" + (
+            ", every frame's RGBA8 image stored into rank 0's device memory over NVLink by the shading pass itself "
+            "(rt_set_rgba8_target on a CUDA-IPC mapping; a release flag per frame behind the stores)" if n_gpus > 1 else ""),
         "l2": "accumulation image (132.7 MB float4, stored once per step) exceeds the 126 MB L2; the 32 KB sphere buffer is shared-memory resident by design",
     }
 
 
-class ClockSampler:
-    """nvidia-smi sampler running during the timed region (B200_PROFILING.md clocks line)."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+class NvmlSampler:
+    """SM clock / power / throttle reasons of one GPU, polled through NVML from a thread while the GPU works
+    (`nvidia-smi -lms` does not produce a sample inside a few-millisecond region)."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, index):
-        self.index, self.samples, self.proc = index, [], None
+    def __init__(self, local_rank, period_s=0.0008):
+        self.samples, self.period, self.ok, self.err = [], period_s, False, None
+        self._stop = threading.Event()
+        self.thread = None
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            pr = torch.cuda.get_device_properties(local_rank)
+            try:
+                bdf = f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+                self.h = pynvml.nvmlDeviceGetHandleByPciBusId(bdf.encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:   # no NVML: say so in the record
+            self.err = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "50"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+        if self.ok:
+            self.thread = threading.Thread(target=self._run, daemon=True)
             self.thread.start()
-        except Exception:
-            self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.samples.append((time.perf_counter(), line.strip()))
-
-    def stop(self, since=None):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        mhz, mx, reasons, power = [], None, set(), []
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        timed = [x for t, x in self.samples if since is None or t >= since]
-        if len(timed) < 3:   # a very short timed region: fall back to everything sampled under load (warm-up included)
-            timed = [x for _, x in self.samples]
-        for s in timed:
-            f = [x.strip() for x in s.split(",")]
-            if len(f) < 7:
-                continue
+    def _run(self):
+        nv, h = self.nv, self.h
+        while not self._stop.is_set():
             try:
-                mhz.append(float(f[0]))
-                mx = float(f[1])
-                power.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(mhz) if mhz else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "power_w_max": max(power) if power else None, "samples": len(mhz)}
+                mhz = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                mw = nv.nvmlDeviceGetPowerUsage(h)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((time.perf_counter(), float(mhz), mw / 1000.0, int(rs)))
+            except Exception as e:
+                self.err = repr(e)
+                break
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self.thread:
+            self.thread.join(timeout=2)
+
+    def window(self, t0, t1):
+        """Summary of the samples taken in [t0, t1] (perf_counter): the clocks line of the JSON record."""
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + str(self.err)], "samples": 0}
+        sel = [s for s in self.samples if t0 <= s[0] <= t1]
+        bits = 0
+        for s in sel:
+            bits |= s[3]
+        return {"sm_mhz": statistics.median(s[1] for s in sel) if sel else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(name for bit, name in self.REASONS.items() if bits & bit),
+                "power_w_max": max((s[2] for s in sel), default=None), "samples": len(sel), "source": "nvml thread"}
 
 
 def measured_peaks():
@@ -136,41 +170,66 @@ def ffma_peak_tflops(device):
     return tf.value, sms.value
 
 
+def git_head():
+    try:
+        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip() or None
+    except Exception:
+        return None
+
+
+def committed_capture():
+    """The ncu counters of the dominant kernel, from the newest committed capture (profiles/r*_primary_capture.json).
+    NOT measured in this run: the block says which commit and workload it was taken at."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_primary_capture.json")))
+    if not files:
+        return None
+    try:
+        with open(files[-1]) as f:
+            cap = json.load(f)
+        cap["file"] = os.path.relpath(files[-1], ROOT)
+        return cap
+    except Exception:
+        return None
+
+
 # ------------------------------------------------------------------------------------------------
-# CPU arms (the only places the oracle is executed outside tests/)
+# CPU arms (the only places the oracle is executed outside tests/): inputs from committed bytes + the oracle's own
+# camera derivation (tests/ref_inputs.py), so these legs never map the product library.
 # ------------------------------------------------------------------------------------------------
-def cpu_sample(rows, row_begin, threads=0):
-    """Time one oracle `update` over a row window of the 4K workload.  Returns (Mrays/s, seconds, rays, threads)."""
-    import numpy as np
+def cpu_frame(cam, rows, row_begin, threads, scene=None, libm=False):
+    """One oracle `update` over a row window of the 4K workload.  Returns (accum, rays, seconds)."""
     import oracle_lib as ol
-    import scenes
-    scene, cam = scenes.random_scene(N_SPHERES), scenes.camera(W, H, 1, 1)
-    accum = np.zeros((rows, W, 4), dtype=np.float32)
-    nthreads = threads or ol.oracle().oracle_max_threads()
+    import ref_inputs as ri
+    scene = scene or ri.random_scene_1024()
     t0 = time.perf_counter()
-    _, rays = ol.oracle_update(cam, scene, W, H, accum=accum, row_begin=row_begin, row_count=rows, threads=nthreads)
-    dt = time.perf_counter() - t0
-    return rays / dt / 1e6, dt, rays, nthreads
+    accum, rays = ol.oracle_update(cam, scene, W, H, row_begin=row_begin, row_count=rows, threads=threads, libm=libm)
+    return accum, rays, time.perf_counter() - t0
 
 
 def run_reference(args):
-    """--impl reference: the reference's shader math on the host cores.  The WGSL itself cannot run
-    here (no wgpu / graphics stack / Rust: 'unavailable on this box'), so this is the C++ port."""
+    """--impl reference: the reference's shader math on the host cores.  The WGSL itself cannot run here (no wgpu /
+    graphics stack / Rust: 'unavailable on this box'), so this is the C++ port — every host core, whatever
+    OMP_NUM_THREADS says (torchrun sets it to 1)."""
+    import ref_inputs as ri
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    rows = 216   # bounded sample: a tenth of the frame, centred (horizon + spheres in view)
+    threads = host_threads()
+    rows = 216   # bounded sample: a tenth of the frame
     row_begin = (H - rows) // 2
+    scene = ri.random_scene_1024()
     for _ in range(max(args.warmup, 1)):
-        cpu_sample(48, row_begin)
+        cpu_frame(ri.camera(W, H), 48, row_begin, threads, scene)
     t0 = time.perf_counter()
-    rays_total, threads = 0, 1
-    for _ in range(args.steps):
-        _, _, rays, threads = cpu_sample(rows, row_begin)
+    rays_total = 0
+    for i in range(args.steps):
+        _, rays, _ = cpu_frame(ri.camera(W, H, random_seed=(i * 2654435761 % (1 << 24)) / float(1 << 24)), rows, row_begin, threads, scene)
         rays_total += rays
     dt = time.perf_counter() - t0
     value = rays_total / dt / 1e6
-    sample = f"rows {row_begin}..{row_begin + rows} of the {W}x{H} frame per step ({rows * W} rays x {N_SPHERES} spheres)"
+    sample = (f"rows {row_begin}..{row_begin + rows} of the {W}x{H} frame per step ({rows * W} rays x {N_SPHERES} spheres): the centred tenth "
+              "of the frame, where the spheres are (at depth 1 every ray tests every sphere, so the band's cost per ray is the frame's)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
@@ -178,8 +237,9 @@ def run_reference(args):
         "config": workload_config(args.gpus),
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "note": "CPU restatement of compute_shader.wgsl (oracle/rt_oracle.cpp, g++ -O2 -ffp-contract=off, OpenMP); "
-                "the reference shader via wgpu/lavapipe is unavailable on this box",
+        "note": "CPU restatement of compute_shader.wgsl (oracle/rt_oracle.cpp, g++ -O2 -ffp-contract=off, OpenMP over rows); "
+                "the reference shader via wgpu/lavapipe is unavailable on this box.  Inputs: tests/golden/random1024_seed1234.bin "
+                "and the oracle's own SceneCamera::from",
     }
     emit_json(line)
 
@@ -187,6 +247,40 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------
+class Gather:
+    """Rank 0's gather buffer, mapped by every rank: [2 slots x n_ranks x frame_bytes | flags].  flags: arrived[rank]
+    (u32, frame counter released behind that rank's stores) and one `consumed` word (rank 0: frames it has seen whole)."""
+
+    def __init__(self, rt, dist, torch, rank, world, local_rank, slot_bytes):
+        self.rank, self.world, self.slot_bytes = rank, world, slot_bytes
+        self.flags_off = 2 * slot_bytes
+        total = self.flags_off + 4096
+        handle = torch.zeros(64, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            self.base = rt.device_alloc(local_rank, total)
+            self.zero(torch)
+            handle.copy_(torch.frombuffer(bytearray(rt.ipc_export(local_rank, self.base)), dtype=torch.uint8))
+        if world > 1:
+            dist.broadcast(handle, src=0)
+            if rank != 0:
+                self.base = rt.ipc_open(local_rank, bytes(handle.cpu().numpy().tobytes()))
+
+    def zero(self, torch):
+        from cuda.bindings import runtime as cudart
+        err, = cudart.cudaMemset(self.base + self.flags_off, 0, 4096)
+        assert int(err) == 0, err
+        torch.cuda.synchronize()
+
+    def slot(self, step):
+        return self.base + (step & 1) * self.slot_bytes
+
+    def arrived(self, of_rank=0):
+        return self.base + self.flags_off + 4 * of_rank
+
+    def consumed(self):
+        return self.base + self.flags_off + 2048
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -206,154 +300,461 @@ def run_ours(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def allreduce(vals, op):
+        if world == 1:
+            return [float(x) for x in vals]
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=op)
+        return [float(x) for x in t.tolist()]
+
     K, Wm = args.steps, max(args.warmup, 3)
     scene = scenes.random_scene(N_SPHERES)
+
     # one camera per (step, rank): the same pose with a re-rolled random_seed (camera.rs:346) — depth-1
     # cost is pose independent (every ray tests every sphere), so steps are comparable
-    def cam_for(step, of_rank=None):
+    def cam_for(step, of_rank=None, depth=1, spp=1, w=W, h=H):
         k = rank if of_rank is None else of_rank
         seed = ((step * world + k) * 2654435761 % (1 << 24)) / float(1 << 24)
-        return scenes.camera(W, H, 1, 1, random_seed=seed)
+        return scenes.camera(w, h, depth, spp, random_seed=seed)
 
     r = rt.Renderer(W, H, device=local_rank)
     r.set_scene(scene)
     r.init()
-    ext = torch.cuda.ExternalStream(r.stream(), device=torch.device("cuda", local_rank))
-
-    # ---- parity spot check against the oracle (rank 0, 16 rows of the real workload) ----------
-    parity = None
-    if rank == 0:
-        import oracle_lib as ol
-        cam = cam_for(0)
-        r.update(cam)
-        gpu_rows = r.read_accum()[1072:1088]
-        cpu_rows, _ = ol.oracle_update(cam, scene, W, H, row_begin=1072, row_count=16)
-        parity = ol.compare_images(cpu_rows, gpu_rows)
-        parity["checked"] = "rows 1072..1088 of the benchmark frame vs oracle"
-        r.init()
-
-    # ---- gather target (N > 1): every finished frame goes to rank 0's device memory by peer copy over NVLink -----
-    # rank 0 owns one buffer of 2 x world RGBA8 frames and exports it through CUDA IPC; the others map it and point
-    # rt_read_rgba8_async at their slot, so a frame's RGBA8 image (rt_set_rgba8_output) is copied on the renderer's copy
-    # stream while the next frame's kernel runs (two frames in flight per rank).
     frame_bytes = W * H * 4
-    gather_base = None
-    if world > 1:
-        handle = torch.zeros(64, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            gather_base = rt.device_alloc(local_rank, 2 * world * frame_bytes)
-            handle.copy_(torch.frombuffer(bytearray(rt.ipc_export(local_rank, gather_base)), dtype=torch.uint8))
-        dist.broadcast(handle, src=0)
-        if rank != 0:
-            gather_base = rt.ipc_open(local_rank, bytes(handle.cpu().numpy().tobytes()))
+    sampler = NvmlSampler(local_rank)
+    sampler.start()
 
-    def slot_ptr(step, of_rank):
-        return gather_base + ((step & 1) * world + of_rank) * frame_bytes
+    # ---- gather target: rank 0 owns 2 slots x world RGBA8 frames + flags; every rank's shading pass stores its frame's
+    # RGBA8 texels straight into its place there (rt_set_rgba8_target: local stores on rank 0, NVLink stores elsewhere) and
+    # releases arrived[rank] = step + 1 behind them; rank 0 waits for the flags of the last step before the clock stops.
+    gather = Gather(rt, dist, torch, rank, world, local_rank, world * frame_bytes) if (world > 1 or args.like_for_like) else None
 
-    def step(i):
+    def weak_step(i, deliver):
+        if deliver:
+            r.set_rgba8_target(gather.slot(i) + rank * frame_bytes)
         r.update(cam_for(i))
-        if world > 1:
-            r.read_rgba8_async_into(slot_ptr(i, rank))
+        if deliver:
+            r.stream_signal(gather.arrived(rank), i + 1)
 
-    def drain():
-        if world > 1:
-            r.read_wait()
+    def weak_region(n_steps, first, deliver):
+        """n_steps headline steps, device-timed on the renderer's stream; returns (ms, wall window)."""
+        barrier()
+        t0 = time.perf_counter()
+        r.timer_begin()
+        for i in range(n_steps):
+            weak_step(first + i, deliver)
+        if deliver and rank == 0:
+            r.stream_wait(gather.arrived(0), world, first + n_steps, 5000)   # every rank's last frame is whole
+        ms = r.timer_end()
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        barrier()
+        return ms, (t0, t1)
 
-    # the gathered frame is written by the shading pass itself (rt_set_rgba8_output): no quantise kernel per frame
-    r.set_rgba8_output(world > 1)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    deliver = world > 1
     for i in range(Wm):
-        step(i)
-    drain()
+        weak_step(i, deliver)
     r.synchronize()
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
     r.reset_counters()
     launches0 = r.kernel_launches()
-    t_region = time.perf_counter()
-    r.timer_begin()
-    for i in range(K):
-        step(Wm + i)
-    drain()                                    # the end event is ordered after the last gather
-    ms = r.timer_end()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    wall_ms = (time.perf_counter() - t_region) * 1e3
-    r.set_rgba8_output(False)
-    clocks = sampler.stop(since=t_region) if rank == 0 else None
+    ms, region = weak_region(K, Wm, deliver)
     rays = r.rays_traced()
     launches = r.kernel_launches() - launches0
-    stats = torch.tensor([ms, float(rays), float(launches), wall_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        mx = stats.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = stats.clone()
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        ms, rays, launches, wall_ms = mx[0].item(), int(sm[1].item()), int(sm[2].item()), mx[3].item()
+    r.set_rgba8_target(None)
+    timed_out = r.stream_wait_timed_out()
+    mx = allreduce([ms], dist.ReduceOp.MAX)
+    sm = allreduce([float(rays), float(launches)], dist.ReduceOp.SUM)
+    ms, rays, launches = mx[0], int(sm[0]), int(sm[1])
     value = rays / (ms * 1e-3) / 1e6
+    clocks = sampler.window(*region) if rank == 0 else None
+
+    # ---- the same step with the delivery at N = 1 too (what every rank does at N > 1): like-for-like basis for the
+    # scaling efficiency — the N = 1 headline above skips the RGBA8 stores because there is nothing to gather
+    like = None
+    if world == 1 and args.like_for_like:
+        for i in range(3):
+            weak_step(i, True)
+        r.synchronize()
+        ms_l, _ = weak_region(K, Wm, True)
+        r.set_rgba8_target(None)
+        like = {"value": K * W * H / (ms_l * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms_l / K,
+                "what": "headline step + the frame's RGBA8 image stored by the shading pass into the gather buffer + completion flag, "
+                        "i.e. the per-GPU work of every rank at N > 1"}
+    elif world > 1:
+        inbound = (world - 1) * frame_bytes * K / (ms * 1e-3) / 1e9
+        like = {"value": value, "unit": "Mrays/s", "ms_per_step": ms / K, "rank0_ingress_gbs": inbound,
+                "nvlink_ingress_peak_gbs": 900.0,
+                "what": "same work per GPU as weak_like_for_like of the N = 1 run; rank 0 takes in (N-1) x 33.2 MB per step over NVLink "
+                        "(900 GB/s per direction nominal)"}
 
     # ---- the gathered frames are the frames: rank 0 re-renders rank 1's last frame and compares it with its slot ---
     gather_check = None
     if world > 1:
-        dist.barrier()
+        barrier()
         if rank == 0:
-            try:
-                try:
-                    from cuda.bindings import runtime as cudart
-                except ImportError:
-                    from cuda import cudart
-                last = Wm + K - 1
-                r.update(cam_for(last, of_rank=1))
-                expect = r.read_rgba8()
-                got = torch.empty(frame_bytes, dtype=torch.uint8, device="cuda")
-                err, = cudart.cudaMemcpy(got.data_ptr(), slot_ptr(last, 1), frame_bytes, cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice)
-                same = bool(np.array_equal(got.cpu().numpy().reshape(H, W, 4), expect))
-                gather_check = {"frame": "last step of rank 1, re-rendered on rank 0", "identical": same, "cudart": str(err)}
-            except Exception as e:   # cuda-python missing: the check is skipped, not faked
-                gather_check = {"skipped": repr(e)}
+            last = Wm + K - 1
+            r.update(cam_for(last, of_rank=1))
+            expect = r.read_rgba8()
+            got = device_bytes(torch, gather.slot(last) + 1 * frame_bytes, frame_bytes).reshape(H, W, 4)
+            gather_check = {"frame": "last step of rank 1, re-rendered on rank 0", "identical": bool(np.array_equal(got, expect)),
+                            "waits_timed_out": timed_out}
             r.init()
-        dist.barrier()
+        barrier()
+
+    # ---- strong scaling: ONE 7680x4320 frame split by row blocks over the ranks (BASELINE config 4) ----------------
+    strong = strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barrier, allreduce, args)
 
     # ---- dominant kernel alone (roofline): CUDA events on the launching stream ------------------
     n_k = 20
     cam = cam_for(0)
     r.update(cam)
     r.synchronize()
+    r.reset_counters()
     r.timer_begin()
     for _ in range(n_k):
         r.update(cam)
     kernel_ms = r.timer_end() / n_k
+    exact_per_ray = r.exact_tests() / max(1, r.rays_traced())
     flops_per_launch = float(W) * H * N_SPHERES * FLOP_PER_TEST
     achieved_tf = flops_per_launch / (kernel_ms * 1e-3) / 1e12
 
+    if rank != 0:
+        # e2e is measured on every rank at once (N host read-backs share the host side)
+        e2e = e2e_leg(rt, torch, np, r, scene, cam_for, local_rank, world, K, barrier, allreduce)
+        barrier()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- brute force (variant 2): every sphere for every ray from shared-memory tiles, FFMA2 broad phase -----------
+    r.set_kernel_variant(2)
+    r.update(cam)
+    r.synchronize()
+    r.timer_begin()
+    for _ in range(5):
+        r.update(cam)
+    bf_ms = r.timer_end() / 5
+    bf_img = r.read_accum()
+    r.set_kernel_variant(0)
+
+    # ---- tolerance mode ------------------------------------------------------------------------
+    r.set_precision(rt.RT_PRECISION_FAST)
+    r.update(cam)
+    r.synchronize()
+    r.timer_begin()
+    for _ in range(n_k):
+        r.update(cam)
+    fast_ms = r.timer_end() / n_k
+    fast_img = r.read_accum()
+    r.set_precision(rt.RT_PRECISION_EXACT)
+    r.update(cam)
+    exact_img = r.read_accum()
+
     # ---- the reference's default depth (max_depth 30), rays counted by the kernels (SURVEY.md 8(d), config 3) -------
-    deep = None
-    if rank == 0:
-        cam30 = scenes.camera(W, H, 30, 500)
-        r.init()
-        r.update(cam30)
-        r.synchronize()
-        r.reset_counters()
-        r.timer_begin()
-        n_deep = 5
-        for _ in range(n_deep):
-            r.update(cam30)            # camera_has_moved = 1: every frame restarts the same first sample
-        deep_ms = r.timer_end() / n_deep
-        deep_rays = r.rays_traced() / n_deep
-        deep = {"max_depth": 30, "ms_per_frame": deep_ms, "rays_per_frame": deep_rays, "mrays_s": deep_rays / deep_ms / 1e3,
-                "note": "primary pass (first hits resolved and survivors queued in the same kernel) + 29 wavefront bounce launches over compacted path queues"}
-        r.init()
+    deep, deep_img, deep_fast_img, cam30 = deep_leg(rt, np, scenes, r, scene, local_rank)
+
+    # ---- sustained: the headline update looped for >= 2 s, clocks and power sampled through NVML ------------------
+    sustained = sustained_leg(r, cam_for, sampler, args.sustain_s if world == 1 else 0.0)
+    if clocks is not None and clocks.get("samples", 0) < 3 and sustained and sustained.get("samples", 0) >= 3:
+        # a timed region of a few milliseconds can fall between two NVML polls: the same update under sustained load
+        clocks = {k: sustained[k] for k in ("sm_mhz", "sm_max_mhz", "reasons", "power_w_max", "samples")}
+        clocks["source"] = "nvml thread during the sustained leg (the timed region held fewer than 3 samples)"
 
     # ---- end to end through the C ABI with HOST buffers ----------------------------------------
-    # per step: sphere buffer uploaded from pinned host memory (the reference re-creates its buffers
-    # from host memory every frame, src/lib.rs:151-207), the 176-byte camera uniform rides in the
-    # kernel parameters, and the frame comes back as RGBA8 into pinned host memory.
-    # pinned frames are allocated from a thread bound to the GPU's own NUMA node when the box says which that is:
-    # a read-back that crosses the socket interconnect runs at ~39 GB/s instead of ~54 (seen between otherwise equal boxes)
+    e2e = e2e_leg(rt, torch, np, r, scene, cam_for, local_rank, world, K, barrier, allreduce)
+    sampler.stop()
+
+    # ---- denominators, CPU baseline, parity, the JSON line ---------------------------------------
+    import oracle_lib as ol
+    import ref_inputs as ri
+    peak_tf, sms = ffma_peak_tflops(local_rank)
+    peaks = measured_peaks()
+    sm_max = (clocks or {}).get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    theo_tf = sms * 128 * 2 * sm_max * 1e6 / 1e12
+    hbm_bytes = float(W) * H * 16      # reset frames: one float4 store per pixel, nothing read
+    hbm_gbs = hbm_bytes / (kernel_ms * 1e-3) / 1e9
+    threads = host_threads()
+    cpu, parity, parity_libm = None, None, None
+    ref_scene = ri.random_scene_1024()
+    same_inputs = bool(np.array_equal(ref_scene.spheres.view(np.uint8), scene.spheres.view(np.uint8)))
+    if world == 1 and not args.no_cpu_baseline:
+        # bounded sample: whole frames of the same workload until ~10 s of wall time (>= 2 frames); the FIRST of them
+        # is the frame the GPU rendered above and is compared texel by texel — all 8,294,400 of them
+        cpu_rays, dt, frames = 0, 0.0, 0
+        while frames < 2 or (dt < 10.0 and frames < 8):
+            img, r1, t1 = cpu_frame(cam if frames == 0 else cam_for(frames), H, 0, threads, ref_scene)
+            if frames == 0:
+                parity = ol.compare_images(img, exact_img)
+                parity["checked"] = "the whole benchmark frame (camera of step 0) vs oracle/rt_oracle.cpp, same bytes in"
+                parity["inputs_identical_to_fixture"] = same_inputs
+                parity["oracle"] = "parity unpinned by the reference (no vectors, WGSL cannot run here); sin/cos/pow5 from include/rt_pinned_math.h on both sides"
+                fast_rep = ol.compare_images(img, fast_img)
+                bf_rep = ol.compare_images(img, bf_img)
+            cpu_rays += r1
+            dt += t1
+            frames += 1
+        cpu = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+               "sample": f"{frames} full frames of the same workload ({cpu_rays} rays x {N_SPHERES} spheres) in {dt:.1f} s, "
+                         "oracle/rt_oracle.cpp (g++ -O2 -ffp-contract=off) with OpenMP over rows"}
+        # the mismatch count the port target asks for: against an implementation with DIFFERENT builtin rounding (libm
+        # sinf / cosf / powf instead of the pinned polynomials), at depth 1 and at the reference's depth 30
+        libm1, _, _ = cpu_frame(cam, H, 0, threads, ref_scene, libm=True)
+        rep1 = ol.compare_images(libm1, exact_img)
+        libm30, _ = ol.oracle_update(cam30, ref_scene, W, H, threads=threads, libm=True)
+        pin30, _ = ol.oracle_update(cam30, ref_scene, W, H, threads=threads)
+        rep30 = ol.compare_images(libm30, deep_img)
+        parity_libm = {
+            "what": "GPU (exact mode) vs liboracle_libm.so: the same restatement with libm sinf/cosf/powf — a stand-in for a WGSL "
+                    "implementation whose builtins round differently; tolerance 1/255 per channel after RGBA8 quantisation",
+            "depth1": {k: rep1[k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")},
+            "depth30": {k: rep30[k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")},
+            "depth30_pinned_vs_libm_oracles": {k: v for k, v in ol.compare_images(libm30, pin30).items() if k != "bit_identical"},
+        }
+        deep["parity"] = ol.compare_images(pin30, deep_img)
+        if deep_fast_img is not None:
+            rep = ol.compare_images(pin30, deep_fast_img)
+            deep["fast"]["vs_oracle"] = {k: rep[k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")}
+    else:
+        # N > 1 (or --no-cpu-baseline): a band of the frame against the oracle, the arms against the exact image
+        rows, row_begin = 216, (H - 216) // 2
+        img, _, _ = cpu_frame(cam, rows, row_begin, threads, ref_scene)
+        parity = ol.compare_images(img, exact_img[row_begin:row_begin + rows])
+        parity["checked"] = f"rows {row_begin}..{row_begin + rows} of the benchmark frame vs oracle (the whole frame is compared in the N = 1 run)"
+        fast_rep = ol.compare_images(exact_img, fast_img)
+        bf_rep = ol.compare_images(exact_img, bf_img)
+
+    capture = committed_capture()
+    executed = {
+        "exact_tests_per_ray": exact_per_ray,
+        "what": "device counters of this run: (ray, sphere) pairs that reach the reference quadratic after the tile / tree / sign-test "
+                "cascade; the other N - that many pairs are discarded by conservative tests with identical results",
+        "from_capture": capture,
+    }
+    if capture and capture.get("warp_instructions_per_launch") and clocks and clocks.get("sm_mhz"):
+        slots = sms * 4 * clocks["sm_mhz"] * 1e6 * kernel_ms * 1e-3
+        executed["issue_slot_frac"] = capture["warp_instructions_per_launch"] / slots
+        executed["issue_slot_frac_note"] = "captured warp instructions / (SMs x 4 schedulers x median SM clock of this run x kernel_ms of this run)"
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(world),
+        "roofline": {"bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": achieved_tf / peak_tf, "traffic": (capture or {}).get("dram_bytes_per_launch"),
+                     "traffic_source": (capture or {}).get("file"),
+                     "model": "18 flop x N spheres per ray (SURVEY.md 8(d)) — brute force, NOT executed by this kernel: frac > 1 says "
+                              "the kernel reaches the same nearest hits without that work, it is not an efficiency. See `executed` "
+                              "for what it does execute and `bruteforce` for the arm that does the modelled work",
+                     "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
+                     "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
+                     "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
+                     "kernel": "primary_hits_kernel<kPrimShade, exact> (+ prep_primary_tree_kernel, ~3 us)"},
+        "executed": executed,
+        "bruteforce": {"kernel": "update_resident_kernel (variant 2): all 1024 records from shared memory for every ray, 7-FFMA2 "
+                                 "conservative test per pair + the reference quadratic on its candidates",
+                       "ms": bf_ms, "mrays_s": W * H / bf_ms / 1e3, "tflops": flops_per_launch / (bf_ms * 1e-3) / 1e12,
+                       "frac": flops_per_launch / (bf_ms * 1e-3) / 1e12 / peak_tf,
+                       "bit_identical_to_oracle": bf_rep["bit_identical"]},
+        "fast": {"mode": "RT_PRECISION_FAST (opt-in; default is exact)", "kernel_ms": fast_ms, "mrays_s": W * H / fast_ms / 1e3,
+                 "speedup_vs_exact": kernel_ms / fast_ms,
+                 "vs_oracle": {k: fast_rep[k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")}},
+        "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
+                "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
+                "algorithmic_bytes_per_launch": hbm_bytes,
+                "note": "one float4 accumulator store per pixel (camera_has_moved = 1: no read); not the bound"},
+        "cpu_baseline": cpu, "e2e": e2e, "deep": deep, "strong": strong, "weak_like_for_like": like,
+        "sustained": sustained, "gather_check": gather_check, "gpu_launches": int(launches), "clocks": clocks,
+        "parity": parity, "parity_libm": parity_libm,
+        "tree": {"build_ms_1024_spheres": r.tree_build_ms(), "info": r.tree_info()},
+        "git_head": git_head(),
+    }
+    emit_json(line)
+    barrier()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def device_bytes(torch, ptr, nbytes):
+    """Copy `nbytes` at device address `ptr` (current device) to a numpy array."""
+    from cuda.bindings import runtime as cudart
+    host = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    err, = cudart.cudaMemcpy(host.data_ptr(), ptr, nbytes, cudart.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+    assert int(err) == 0, err
+    return host.numpy()
+
+
+def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barrier, allreduce, args):
+    """One 7680x4320 / 1024-sphere frame per step, rows split over the ranks with rt_shard_rows, every rank's shading pass
+    storing its RGBA8 row block into rank 0's frame (fused gather over NVLink).  Protocol per frame f and rank i:
+    wait consumed >= f - 1 (the slot's previous frame has been seen whole) -> update -> release arrived[i] = f + 1;
+    rank 0 then waits for every arrived[*] >= f + 1 — the frame is whole in its memory — and releases consumed = f + 1.
+    Time = rank 0's device time for K whole frames.  Afterwards rank 0 renders the same frame alone (t1) and compares."""
+    K = max(5, min(args.steps, 20))
+    frame8 = W8K * H8K * 4
+    row_begin, rows = rt.shard_rows(H8K, world, rank)
+    g = Gather(rt, dist, torch, rank, world, local_rank, frame8)
+    rs = rt.Renderer(W8K, H8K, device=local_rank, row_begin=row_begin, row_count=rows)
+    rs.set_scene(scene)
+    rs.init()
+
+    def cam8(f):
+        return scenes.camera(W8K, H8K, 1, 1, random_seed=((f + 1) * 2654435761 % (1 << 24)) / float(1 << 24))
+
+    def frame(f):
+        if f >= 2:
+            rs.stream_wait(g.consumed(), 1, f - 1, 5000)
+        rs.set_rgba8_target(g.slot(f) + row_begin * W8K * 4)
+        rs.update(cam8(f))
+        rs.stream_signal(g.arrived(rank), f + 1)
+        if rank == 0:
+            rs.stream_wait(g.arrived(0), world, f + 1, 5000)
+            rs.stream_signal(g.consumed(), f + 1)
+
+    for f in range(3):
+        frame(f)
+    rs.synchronize()
+    torch.cuda.synchronize()
+    barrier()
+    rs.timer_begin()
+    for f in range(3, 3 + K):
+        frame(f)
+    ms = rs.timer_end()
+    torch.cuda.synchronize()
+    barrier()
+    timed_out = rs.stream_wait_timed_out()
+    # without the gather: the row blocks stay where they are rendered
+    rs.set_rgba8_target(None)
+    rs.update(cam8(0))
+    rs.synchronize()
+    barrier()
+    rs.timer_begin()
+    for f in range(K):
+        rs.update(cam8(f))
+    ms_nog = rs.timer_end()
+    barrier()
+    mx = allreduce([ms, ms_nog, float(timed_out)], dist.ReduceOp.MAX)
+    ms, ms_nog, timed_out = mx[0] / K, mx[1] / K, int(mx[2])
+    out = None
+    if rank == 0:
+        last = 3 + K - 1
+        got = device_bytes(torch, g.slot(last), frame8).reshape(H8K, W8K, 4).copy()
+    rs.close()
+    barrier()
+    if rank == 0:
+        # the same frame on this GPU alone: t1, and the image the gathered one must equal
+        with rt.Renderer(W8K, H8K, device=local_rank) as r1:
+            r1.set_scene(scene)
+            r1.init()
+            r1.set_rgba8_target(g.slot(0))
+            r1.update(cam8(last))
+            r1.synchronize()
+            r1.timer_begin()
+            for f in range(K):
+                r1.update(cam8(last))
+            t1 = r1.timer_end() / K
+            want = device_bytes(torch, g.slot(0), frame8).reshape(H8K, W8K, 4)
+            identical = bool(np.array_equal(got, want))
+        out = {"workload": f"one {W8K}x{H8K} frame / {N_SPHERES} spheres / depth 1 per step, rows split over {world} rank(s) "
+                           "(rt_shard_rows), RGBA8 row blocks stored into rank 0's frame by the shading pass over NVLink, "
+                           "arrived / consumed flags per frame",
+               "ms": ms, "mrays_s": W8K * H8K / ms / 1e3, "ms_without_gather": ms_nog,
+               "t1_ms_same_run": t1, "speedup_vs_1": t1 / ms, "speedup_vs_1_without_gather": t1 / ms_nog,
+               "rank0_ingress_gbs": (world - 1) / world * frame8 / (ms * 1e-3) / 1e9 if world > 1 else 0.0,
+               "identical_to_single_gpu_frame": identical, "frames": K, "waits_timed_out": timed_out}
+    barrier()
+    return out
+
+
+def deep_leg(rt, np, scenes, r, scene, local_rank):
+    cam30 = scenes.camera(W, H, 30, 500)
+    r.init()
+    r.update(cam30)
+    r.synchronize()
+    r.reset_counters()
+    l0 = r.kernel_launches()
+    r.timer_begin()
+    n_deep = 5
+    for _ in range(n_deep):
+        r.update(cam30)            # camera_has_moved = 1: every frame restarts the same first sample
+    deep_ms = r.timer_end() / n_deep
+    deep_rays = r.rays_traced() / n_deep
+    deep_launches = (r.kernel_launches() - l0) / n_deep
+    deep_img = r.read_accum()
+    deep = {"max_depth": 30, "ms_per_frame": deep_ms, "rays_per_frame": deep_rays, "mrays_s": deep_rays / deep_ms / 1e3,
+            "launches_per_frame": deep_launches,
+            "note": "primary pass (first hits resolved and survivors queued in the same kernel) + 29 wavefront bounce launches over compacted path queues"}
+    r.set_precision(rt.RT_PRECISION_FAST)
+    r.update(cam30)
+    r.synchronize()
+    r.reset_counters()
+    r.timer_begin()
+    for _ in range(n_deep):
+        r.update(cam30)
+    fast_ms = r.timer_end() / n_deep
+    fast_rays = r.rays_traced() / n_deep
+    deep_fast_img = r.read_accum()
+    r.set_precision(rt.RT_PRECISION_EXACT)
+    deep["fast"] = {"ms_per_frame": fast_ms, "rays_per_frame": fast_rays, "speedup_vs_exact": deep_ms / fast_ms}
+    r.init()
+    # the application's own working point (src/lib.rs:25, src/camera.rs:33-34): default scene, 1280x720, depth 30, 500 spp
+    dscene = scenes.default_scene()
+    with rt.Renderer(1280, 720, device=local_rank) as rd:
+        rd.set_scene(dscene)
+        rd.init()
+        first = scenes.camera(1280, 720, 30, 500, random_seed=0.5, moved=1)
+        rd.update(first)
+        rd.synchronize()
+        rd.timer_begin()
+        for _ in range(10):
+            rd.update(first)
+        frame_ms = rd.timer_end() / 10
+        cams = [scenes.camera(1280, 720, 30, 500, random_seed=((i + 1) * 2654435761 % (1 << 24)) / float(1 << 24), moved=1 if i == 0 else 0)
+                for i in range(500)]
+        rd.init()
+        t0 = time.perf_counter()
+        rd.timer_begin()
+        rd.update_n(cams)
+        spp_ms = rd.timer_end()
+        wall_ms = (time.perf_counter() - t0) * 1e3
+        n_done = float(rd.read_accum()[..., 3].min())
+        deep["app_default"] = {"workload": "default scene (199 spheres) 1280x720, max_depth 30", "ms_per_frame": frame_ms,
+                               "time_to_500_spp_ms": spp_ms, "wall_ms": wall_ms, "samples_reached": n_done,
+                               "call": "rt_update_n with 500 per-frame uniforms (random_seed re-rolled per frame, camera.rs:346)"}
+    return deep, deep_img, deep_fast_img, cam30
+
+
+def sustained_leg(r, cam_for, sampler, seconds):
+    if seconds <= 0:
+        return None
+    r.init()
+    t0 = time.perf_counter()
+    r.timer_begin()
+    n, chunk = 0, 200
+    while True:
+        for i in range(chunk):
+            r.update(cam_for(i & 63))
+        n += chunk
+        r.synchronize()
+        if time.perf_counter() - t0 >= seconds:
+            break
+    ms = r.timer_end()
+    t1 = time.perf_counter()
+    out = sampler.window(t0, t1)
+    out.update({"seconds": ms * 1e-3, "steps": n, "ms_per_step": ms / n, "mrays_s": n * W * H / ms / 1e3,
+                "what": "the headline update back to back for the stated time (synchronised every 200 steps so that the queue stays short)"})
+    return out
+
+
+def e2e_leg(rt, torch, np, r, scene, cam_for, local_rank, world, K, barrier, allreduce):
+    """Per step: sphere buffer uploaded from pinned host memory (the reference re-creates its buffers from host memory
+    every frame, src/lib.rs:151-207), the 176-byte camera uniform rides in the kernel parameters, and the frame comes
+    back as RGBA8 into pinned host memory.  Pinned frames are allocated from a thread bound to the GPU's own NUMA node
+    when the box says which that is."""
+    import torch.distributed as dist
     with numa_local(local_rank) as numa_note:
         host_spheres = torch.from_numpy(scene.spheres.view(np.uint8).copy()).pin_memory()
         host_images = [torch.empty((H, W, 4), dtype=torch.uint8).pin_memory() for _ in range(2)]
@@ -372,18 +773,17 @@ def run_ours(args):
     for i in range(2):
         e2e_step(i)
     r.read_wait()
-    if world > 1:
-        dist.barrier()
+    barrier()
     t0 = time.perf_counter()
     for i in range(K_e2e):
         e2e_step(i)
     r.read_wait()                                     # every frame of the timed region is on the host
     e2e_s = time.perf_counter() - t0
     r.set_rgba8_output(False)
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = K_e2e * world * W * H / e2e_t.item() / 1e6
+    e2e_max = allreduce([e2e_s], dist.ReduceOp.MAX)[0]
+    per_rank_gbs = K_e2e * W * H * 4 / e2e_s / 1e9
+    sum_gbs = allreduce([per_rank_gbs], dist.ReduceOp.SUM)[0]
+    e2e_value = K_e2e * world * W * H / e2e_max / 1e6
     host_image = host_images[(K_e2e - 1) & 1]
     checksum = int(host_image.view(-1)[::4099].to(torch.int64).sum().item())
     # the same loop with the blocking read (rt_read_rgba8): what a strictly frame-synchronous caller sees
@@ -393,71 +793,13 @@ def run_ours(args):
         r.update(cam_for(i))
         r.read_rgba8_into(host_image.data_ptr())
     e2e_sync_value = K_e2e * W * H / (time.perf_counter() - t0) / 1e6
-
-    if rank != 0:
-        if world > 1:
-            dist.barrier()
-            dist.destroy_process_group()
-        return
-
-    # ---- rank 0: denominators, CPU baseline, the JSON line ---------------------------------------
-    peak_tf, sms = ffma_peak_tflops(local_rank)
-    peaks = measured_peaks()
-    theo_tf = sms * 128 * 2 * (clocks.get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6 / 1e12
-    hbm_bytes = float(W) * H * 16      # reset frames: one float4 store per pixel, nothing read
-    hbm_gbs = hbm_bytes / (kernel_ms * 1e-3) / 1e9
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:
-        # bounded sample: whole frames of the same workload until ~10 s of wall time (>= 2 frames)
-        cpu_rays, dt, frames, threads = 0, 0.0, 0, 1
-        while frames < 2 or (dt < 10.0 and frames < 8):
-            _, t1, r1, threads = cpu_sample(H, 0)
-            cpu_rays += r1
-            dt += t1
-            frames += 1
-        cpu = {"value": cpu_rays / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-               "sample": f"{frames} full frames of the same workload ({cpu_rays} rays x {N_SPHERES} spheres) in {dt:.1f} s, "
-                         "oracle/rt_oracle.cpp (g++ -O2 -ffp-contract=off) with OpenMP"}
-    line = {
-        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(world),
-        "roofline": {"bound": "fp32_fma", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved_tf / peak_tf, "traffic": 75208704,
-                     "peak_source": "FFMA microbenchmark run in this process (tools/ffma_peak.cu); MEASURED_PEAKS.json has no FP32 figure",
-                     "frac_of_theoretical": achieved_tf / theo_tf, "theoretical_peak": theo_tf,
-                     "algorithmic_flop_per_launch": flops_per_launch, "kernel_ms": kernel_ms,
-                     "kernel": "primary_hits_kernel<kPrimShade> (+ prep_primary_tree_kernel, 3 us)",
-                     "ncu": {"source": "profiles/r1_primary_cull_ncu.md (ncu --set full of this kernel on this workload)",
-                             "warp_instructions_per_launch": 247215710, "issue_slots_busy_pct": 76.0,
-                             "pipe_fma_pct": 33.5, "pipe_alu_pct": 39.2, "pipe_xu_pct": 29.5, "stall_no_inst_pct": 8.7,
-                             "dram_bytes_read": 94464, "dram_bytes_written": 75114240},
-                     "note": "achieved/frac count the reference's 18 flop per (ray, sphere) test over all N spheres (SURVEY.md "
-                             "8(d)).  The kernel reaches the same nearest hit without doing that work: each 32x8 pixel tile "
-                             "walks an 8-wide tree of bounding spheres with one conservative test per node, the rays of the "
-                             "tile run a 3-FFMA sign test on the ~6 surviving spheres, nearest first, and the reference quadratic on "
-                             "their candidates until every ray of a strip holds a nearer hit (2.1 exact tests per ray), so frac "
-                             "exceeds 1.  What is left is per-ray scalar work that bit-exactness fixes "
-                             "(IEEE division / sqrt / the pinned sin-cos of get_ray and scatter): the kernel is issue-bound "
-                             "(ncu block), not FMA- or HBM-bound."},
-        "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
-                "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
-                "algorithmic_bytes_per_launch": hbm_bytes,
-                "note": "one float4 accumulator store per pixel (camera_has_moved = 1: no read); ncu sees 75 MB of it reach DRAM inside the launch, the rest is still in the 126 MB L2"},
-        "cpu_baseline": cpu,
-        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(scene.spheres) * 32 + 176),
-                "d2h_bytes_per_step": W * H * 4, "steps": K_e2e,
-                "pinned_host_memory": str(numa_note),
-                "call": "rt_set_scene + rt_update + rt_read_rgba8_async per frame (two pinned host frames, read-back of "
-                        "frame i overlaps the kernel of frame i+1), rt_read_wait before the clock stops",
-                "blocking_read_value": e2e_sync_value, "checksum": checksum},
-        "deep": deep, "gather_check": gather_check, "gpu_launches": int(launches), "clocks": clocks, "parity": parity,
-        "wall_ms_per_step": wall_ms / K,
-    }
-    emit_json(line)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    return {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(len(scene.spheres) * 32 + 176),
+            "d2h_bytes_per_step": W * H * 4, "steps": K_e2e, "pinned_host_memory": str(numa_note),
+            "d2h_gbs_this_rank": per_rank_gbs, "d2h_gbs_all_ranks": sum_gbs,
+            "bound": "host read-back: 33.2 MB of RGBA8 per frame over PCIe (the kernel needs about half that time)",
+            "call": "rt_set_scene + rt_update + rt_read_rgba8_async per frame (two pinned host frames, read-back of "
+                    "frame i overlaps the kernel of frame i+1), rt_read_wait before the clock stops",
+            "blocking_read_value": e2e_sync_value, "checksum": checksum}
 
 
 class numa_local:
@@ -507,6 +849,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the sustained leg (0 = skip)")
+    ap.add_argument("--no-like-for-like", dest="like_for_like", action="store_false",
+                    help="N = 1: skip the second timing of the headline step with the RGBA8 delivery of the N > 1 ranks")
     args = ap.parse_args()
     capture_stdout()
     if args.impl == "reference":

@@ -200,6 +200,7 @@ int rt_init(RtRenderer* r) {
     RT_CHECK_HANDLE(r);
     RT_CUDA(cudaMemsetAsync(r->accum, 0, r->n_texels * sizeof(float4), r->stream));
     r->rgba8_fresh = false;
+    r->target_fresh = false;
     return RT_OK;
 }
 
@@ -331,6 +332,7 @@ int rt_write_accum(RtRenderer* r, const float* host) {
     RT_CHECK_HANDLE(r);
     if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");
     r->rgba8_fresh = false;
+    r->target_fresh = false;
     RT_CUDA(cudaMemcpyAsync(r->accum, host, r->n_texels * sizeof(float4), cudaMemcpyHostToDevice, r->stream));
     RT_CUDA(cudaStreamSynchronize(r->stream));
     return RT_OK;

@@ -1,8 +1,10 @@
-// rt_multi.cu — one image sharded by contiguous row blocks over several devices of one host,
-// scene replicated, result gathered into devices[0] by peer copies over NVLink
-// (cudaMemcpyPeerAsync on each shard's own stream, so every shard's copy starts the moment its
-// kernel retires and overlaps the other shards' compute).  No collective is needed: the shader has
-// no inter-pixel dependency (compute_shader.wgsl:333-364 touches only its own texel).
+// rt_multi.cu — one image sharded by contiguous row blocks over several devices of one host, scene
+// replicated, result gathered into devices[0] over NVLink.  Depth-1 frames are gathered BY THE SHADING
+// PASS: every shard's kernel stores its RGBA8 texels straight into its rows of the full frame on
+// devices[0] (rt_set_rgba8_target on a peer pointer), so the gather is finished when the kernels are;
+// deeper frames (and shards without peer access) are quantised and sent with cudaMemcpyPeerAsync on
+// the shard's own stream.  No collective is needed: the shader has no inter-pixel dependency
+// (compute_shader.wgsl:333-364 touches only its own texel).
 #include <cuda_runtime.h>
 
 #include <new>
@@ -16,6 +18,7 @@ using rti::fail_cuda;
 
 struct RtMultiRenderer {
     std::vector<RtRenderer*> shards;
+    std::vector<char> direct;        // shard i can store into devices[0]'s memory (same device or peer access)
     uint32_t width = 0, height = 0;
     uchar4* full_rgba8 = nullptr;    // on devices[0]
     float4* full_accum = nullptr;    // on devices[0], allocated on first use
@@ -77,8 +80,10 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
         m->shards.push_back(s);
     }
     // peer access devices[0] <-> devices[i]; cudaMemcpyPeerAsync falls back to staging when absent
+    m->direct.assign(n_devices, 0);
+    m->direct[0] = 1;
     for (uint32_t i = 1; i < n_devices; ++i) {
-        if (devices[i] == devices[0]) continue;
+        if (devices[i] == devices[0]) { m->direct[i] = 1; continue; }
         int can = 0;
         if (cudaDeviceCanAccessPeer(&can, devices[0], devices[i]) == cudaSuccess && can) {
             cudaSetDevice(devices[0]);
@@ -88,6 +93,7 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
             e = cudaDeviceEnablePeerAccess(devices[0], 0);
             if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { rt_multi_destroy(m); return fail_cuda(e, "cudaDeviceEnablePeerAccess"); }
             cudaGetLastError();
+            m->direct[i] = 1;
         }
     }
     // the gather sends RGBA8 blocks: depth-1 updates write them in the shading pass (no quantise kernel per shard)
@@ -95,6 +101,9 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
     cudaError_t e = cudaSetDevice(devices[0]);
     if (e == cudaSuccess) e = cudaMalloc(&m->full_rgba8, (size_t)width * height * sizeof(uchar4));
     if (e != cudaSuccess) { rt_multi_destroy(m); return fail_cuda(e, "rt_multi_create"); }
+    // fused gather: the shading pass of a depth-1 update stores the shard's rows straight into the full frame
+    for (uint32_t i = 0; i < n_devices; ++i)
+        if (m->direct[i]) rt_set_rgba8_target(m->shards[i], m->full_rgba8 + (size_t)m->shards[i]->row_begin * width);
     *out = m;
     return RT_OK;
 }
@@ -130,6 +139,7 @@ int rt_multi_gather_rgba8(RtMultiRenderer* m, uint8_t* host) {
     if (!m) return fail(RT_ERR_INVALID_ARG, "null renderer");
     const int dev0 = m->shards[0]->device;
     for (RtRenderer* s : m->shards) {
+        if (s->target_fresh) continue;   // the last update's shading pass has already stored these rows in place
         int rc = rt_quantize(s);
         if (rc != RT_OK) return rc;
         RTM_CUDA(cudaSetDevice(s->device));
