@@ -442,15 +442,16 @@ def run_ours(args):
     bf_img = r.read_accum()
     r.set_kernel_variant(0)
 
-    # ---- tolerance mode ------------------------------------------------------------------------
-    r.set_precision(rt.RT_PRECISION_FAST)
-    r.update(cam)
-    r.synchronize()
-    r.timer_begin()
-    for _ in range(n_k):
+    # ---- tolerance modes -----------------------------------------------------------------------
+    fast_runs = {}
+    for name, level in (("fast_shading", rt.RT_PRECISION_FAST_SHADING), ("fast_all", rt.RT_PRECISION_FAST_ALL)):
+        r.set_precision(level)
         r.update(cam)
-    fast_ms = r.timer_end() / n_k
-    fast_img = r.read_accum()
+        r.synchronize()
+        r.timer_begin()
+        for _ in range(n_k):
+            r.update(cam)
+        fast_runs[name] = (r.timer_end() / n_k, r.read_accum())
     r.set_precision(rt.RT_PRECISION_EXACT)
     r.update(cam)
     exact_img = r.read_accum()
@@ -493,7 +494,7 @@ def run_ours(args):
                 parity["checked"] = "the whole benchmark frame (camera of step 0) vs oracle/rt_oracle.cpp, same bytes in"
                 parity["inputs_identical_to_fixture"] = same_inputs
                 parity["oracle"] = "parity unpinned by the reference (no vectors, WGSL cannot run here); sin/cos/pow5 from include/rt_pinned_math.h on both sides"
-                fast_rep = ol.compare_images(img, fast_img)
+                fast_rep = {k: ol.compare_images(img, v[1]) for k, v in fast_runs.items()}
                 bf_rep = ol.compare_images(img, bf_img)
             cpu_rays += r1
             dt += t1
@@ -525,7 +526,7 @@ def run_ours(args):
         img, _, _ = cpu_frame(cam, rows, row_begin, threads, ref_scene)
         parity = ol.compare_images(img, exact_img[row_begin:row_begin + rows])
         parity["checked"] = f"rows {row_begin}..{row_begin + rows} of the benchmark frame vs oracle (the whole frame is compared in the N = 1 run)"
-        fast_rep = ol.compare_images(exact_img, fast_img)
+        fast_rep = {k: ol.compare_images(exact_img, v[1]) for k, v in fast_runs.items()}
         bf_rep = ol.compare_images(exact_img, bf_img)
 
     capture = committed_capture()
@@ -559,9 +560,11 @@ def run_ours(args):
                        "ms": bf_ms, "mrays_s": W * H / bf_ms / 1e3, "tflops": flops_per_launch / (bf_ms * 1e-3) / 1e12,
                        "frac": flops_per_launch / (bf_ms * 1e-3) / 1e12 / peak_tf,
                        "bit_identical_to_oracle": bf_rep["bit_identical"]},
-        "fast": {"mode": "RT_PRECISION_FAST (opt-in; default is exact)", "kernel_ms": fast_ms, "mrays_s": W * H / fast_ms / 1e3,
-                 "speedup_vs_exact": kernel_ms / fast_ms,
-                 "vs_oracle": {k: fast_rep[k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")}},
+        "fast": {"note": "opt-in tolerance modes of rt_set_precision (the default and the headline are exact): FAST_SHADING = MUFU + FMA "
+                         "in scatter / sky / running mean with exact primary rays; FAST_ALL = ray generation too (silhouette samples may flip)",
+                 **{name: {"kernel_ms": t, "mrays_s": W * H / t / 1e3, "speedup_vs_exact": kernel_ms / t,
+                           "vs_oracle": {k: fast_rep[name][k] for k in ("pixels", "pixels_over_1_255", "pixels_differing", "max_abs")}}
+                    for name, (t, _) in fast_runs.items()}},
         "hbm": {"achieved": hbm_gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": (hbm_gbs / peaks["hbm_gbs"]) if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_launch": hbm_bytes,
@@ -687,7 +690,7 @@ def deep_leg(rt, np, scenes, r, scene, local_rank):
     deep = {"max_depth": 30, "ms_per_frame": deep_ms, "rays_per_frame": deep_rays, "mrays_s": deep_rays / deep_ms / 1e3,
             "launches_per_frame": deep_launches,
             "note": "primary pass (first hits resolved and survivors queued in the same kernel) + 29 wavefront bounce launches over compacted path queues"}
-    r.set_precision(rt.RT_PRECISION_FAST)
+    r.set_precision(rt.RT_PRECISION_FAST_SHADING)
     r.update(cam30)
     r.synchronize()
     r.reset_counters()

@@ -92,7 +92,7 @@ SPHERE_DTYPE = np.dtype([("position", "<f4", 3), ("radius", "<f4"), ("color", "<
 assert SPHERE_DTYPE.itemsize == 32 and C.sizeof(GpuSphere) == 32 and C.sizeof(SceneCamera) == 176
 
 RT_OK = 0
-RT_PRECISION_EXACT, RT_PRECISION_FAST = 0, 1
+RT_PRECISION_EXACT, RT_PRECISION_FAST_SHADING, RT_PRECISION_FAST_ALL = 0, 1, 2
 RT_ERR_INVALID_ARG, RT_ERR_CUDA, RT_ERR_NO_DEVICE, RT_ERR_NO_SCENE, RT_ERR_OUT_OF_MEMORY, RT_ERR_STATE = -1, -2, -3, -4, -5, -6
 
 
@@ -425,7 +425,8 @@ class Renderer:
         return v.value
 
     def set_precision(self, precision: int):
-        """RT_PRECISION_EXACT (default, bit-identical to the oracle) or RT_PRECISION_FAST (MUFU + FMA per-ray arithmetic)."""
+        """RT_PRECISION_EXACT (default, bit-identical to the oracle), RT_PRECISION_FAST_SHADING (MUFU + FMA in scatter / sky /
+        running mean, primary rays exact) or RT_PRECISION_FAST_ALL (ray generation too)."""
         _check(lib().rt_set_precision(self._h, precision))
 
     def tree_build_ms(self) -> float:

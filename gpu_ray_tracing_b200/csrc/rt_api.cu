@@ -432,7 +432,7 @@ int rt_stream_wait_timed_out(RtRenderer* r, uint32_t* count) {
 
 int rt_set_precision(RtRenderer* r, int precision) {
     if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
-    if (precision != RT_PRECISION_EXACT && precision != RT_PRECISION_FAST) return fail(RT_ERR_INVALID_ARG, "precision %d", precision);
+    if (precision < RT_PRECISION_EXACT || precision > RT_PRECISION_FAST_ALL) return fail(RT_ERR_INVALID_ARG, "precision %d", precision);
     r->precision = precision;
     return RT_OK;
 }

@@ -53,13 +53,16 @@ RT_DEV_SHARED f3 normalize_shared(f3 a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tolerance mode (rt_set_precision(RT_PRECISION_FAST)).  The functions below that take a
-// `bool F` template argument have two instantiations: F = false is the bit-exact restatement (one IEEE rounding per
-// WGSL operator, pinned sin / cos), F = true evaluates the same formulas with the hardware approximations the port
-// target names — MUFU rcp / rsqrt / sqrt / sin / cos (about 1-2 ulp, sin / cos 2^-21 absolute) and explicit FMA
-// contraction — which is what a WGSL implementation is allowed to do as well (builtin precision is implementation
-// defined).  What decides WHICH sphere a ray hits (discriminant sign, root order, rtc::sphere_root) stays IEEE in both
-// modes, so the two modes differ by rounding of colours, not by geometry, until a path's second bounce.
+// Tolerance modes (rt_set_precision).  The functions below that take an `int F` template
+// argument have up to three instantiations: F = 0 is the bit-exact restatement (one IEEE rounding per WGSL operator,
+// pinned sin / cos); F >= 1 evaluates scatter, sky colour, running mean and the broad phases' unit directions with
+// the hardware approximations the port target names — MUFU rcp / rsqrt / sqrt / sin / cos (about 1-2 ulp, sin / cos
+// 2^-21 absolute) and explicit FMA contraction — which is what a WGSL implementation is allowed to do as well (builtin
+// precision is implementation defined); F >= 2 does the same to get_ray.  What decides WHICH sphere a ray hits
+// (discriminant sign, root order, rtc::sphere_root) stays IEEE in every mode.  With F = 1 the primary rays are the
+// reference's bit for bit, so a depth-1 image differs from the exact one by colour rounding only (and by the odd
+// material-branch decision that sits on its threshold); with F = 2 a primary ray is displaced by ~1e-7 relative and a
+// sample that grazes a silhouette may land on the other side of it.
 // ---------------------------------------------------------------------------------------------
 namespace fastm {
 RT_DEV float rcp(float x) {
@@ -104,17 +107,17 @@ RT_DEV float rsq_refined(float a) {
 }
 }  // namespace fastm
 
-template <bool F> RT_DEV float dot_t(f3 a, f3 b) {
+template <int F> RT_DEV float dot_t(f3 a, f3 b) {
     if constexpr (F) return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z));
     else return dot(a, b);
 }
-template <bool F> RT_DEV f3 axpy_t(float s, f3 a, f3 b) {   // s * a + b
+template <int F> RT_DEV f3 axpy_t(float s, f3 a, f3 b) {   // s * a + b
     if constexpr (F) return mk(fmaf(s, a.x, b.x), fmaf(s, a.y, b.y), fmaf(s, a.z, b.z));
     else return add(b, scale(s, a));
 }
 // normalize() of the metal / dielectric branches: the shared out-of-line IEEE copy, or v * rsqrt(v.v) inline
-template <bool F> RT_DEV f3 normalize_branch(f3 a) {
-    if constexpr (F) return scale(fastm::rsq(dot_t<true>(a, a)), a);
+template <int F> RT_DEV f3 normalize_branch(f3 a) {
+    if constexpr (F) return scale(fastm::rsq(dot_t<1>(a, a)), a);
     else return normalize_shared(a);
 }
 
@@ -143,7 +146,7 @@ RT_DEV uint32_t hash(uint32_t s) {
 RT_DEV float random_float(uint32_t v) { return (float)hash(v) * 2.3283064365386963e-10f; }
 
 // compute_shader.wgsl:234-243
-template <bool F = false>
+template <int F = 0>
 RT_DEV f3 random_unit_vector(uint32_t seed) {
     float z = 2.0f * random_float(seed) - 1.0f;
     float a = random_float(seed + 1u) * 6.283185307f;
@@ -164,22 +167,22 @@ struct Ray {
 };
 
 // compute_shader.wgsl:305-331 (get_ray, sample_square, defocus_disk_sample)
-template <bool F = false>
+template <int F = 0>
 RT_DEV Ray get_ray(const SceneCamera& cam, int x, int y, uint32_t sample_index, uint32_t seed_bits) {
     uint32_t seed = hash(hash((uint32_t)x * 73u) ^ hash((uint32_t)y * 51u) ^ (sample_index * 25u + seed_bits));
     float ox = random_float(seed) - 0.5f;
     float oy = random_float(seed * seed) - 0.5f;
     float sx = ((float)x + 0.5f) + ox;
     float sy = ((float)y + 0.5f) + oy;
-    if constexpr (F) {
+    if constexpr (F >= 2) {   // RT_PRECISION_FAST_ALL: the primary ray itself is approximate (silhouette pixels may flip)
         Ray r;
-        const f3 pc = axpy_t<true>(sy, mk(cam.pixel_delta_v), axpy_t<true>(sx, mk(cam.pixel_delta_u), mk(cam.viewport_upper_left)));
+        const f3 pc = axpy_t<1>(sy, mk(cam.pixel_delta_v), axpy_t<1>(sx, mk(cam.pixel_delta_u), mk(cam.viewport_upper_left)));
         r.o = mk(cam.center);
         if (cam.defocus_angle > 0.0f) {
             // (cos, sin) of the approximation is unit to 2^-20: the reference's normalize of it is a no-op at that level
             float sn, cs;
             fastm::sincos2pi((2.0f * 3.1415926f) * random_float(seed + 1u), &sn, &cs);
-            r.o = axpy_t<true>(sn, mk(cam.defocus_disk_v), axpy_t<true>(cs, mk(cam.defocus_disk_u), r.o));
+            r.o = axpy_t<1>(sn, mk(cam.defocus_disk_v), axpy_t<1>(cs, mk(cam.defocus_disk_u), r.o));
         }
         r.d = sub(pc, r.o);
         return r;
@@ -221,10 +224,10 @@ RT_DEV bool sphere_root(f3 o, f3 d, float a, f3 center, float radius, float tmin
 }
 
 // Sky gradient of ray_color (compute_shader.wgsl:293-296) times the accumulated factor.
-template <bool F = false>
+template <int F = 0>
 RT_DEV f3 sky_times(f3 factor, f3 dir) {
     float uy;
-    if constexpr (F) uy = dir.y * fastm::rsq(dot_t<true>(dir, dir));
+    if constexpr (F) uy = dir.y * fastm::rsq(dot_t<1>(dir, dir));
     else uy = normalize(dir).y;
     float a = 0.5f * (uy + 1.0f);
     float ia = 1.0f - a;
@@ -236,13 +239,13 @@ RT_DEV f3 sky_times(f3 factor, f3 dir) {
 // dispatch of ray_color (compute_shader.wgsl:268-286).  On return *ray is the scattered ray and
 // *factor has been multiplied by the attenuation.  Returns false when the sample is absorbed
 // (ray_color returns black, compute_shader.wgsl:274,278,282).
-template <bool F = false>
+template <int F = 0>
 RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
     f3 o = ray->o, d = ray->d;
     f3 center = mk(sp.position);
     f3 p, outward;
     if constexpr (F) {
-        p = axpy_t<true>(t, d, o);
+        p = axpy_t<1>(t, d, o);
         outward = scale(fastm::rcp(sp.radius), sub(p, center));
     } else {
         p = add(o, scale(t, d));
@@ -325,7 +328,7 @@ struct BroadRay {
     float thr;            // |O|^2 (1 - kappa)
 };
 
-template <bool F = false>
+template <int F = 0>
 RT_DEV BroadRay broad_arm(f3 o, f3 d, float a) {
     BroadRay b;
     float inv;
@@ -437,7 +440,7 @@ RT_DEV void primary_record_pad(float out[4]) { out[0] = 0.0f; out[1] = 0.0f; out
 
 // Unit direction of a ray for the common-origin test.  Returns false (and u = 0) when |d|^2 is
 // outside [2^-40, 2^40] or not finite: such a ray has to be traced with the exact test only.
-template <bool F = false>
+template <int F = 0>
 RT_DEV bool primary_arm(f3 d, float a, float* ux, float* uy, float* uz, float* inv_len = nullptr) {
     const bool ok = (a >= 9.094947017729282e-13f) && (a <= 1099511627776.0f);
     if (!ok) {

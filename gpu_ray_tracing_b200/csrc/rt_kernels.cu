@@ -72,7 +72,7 @@ __device__ __forceinline__ float broad_g(const float4 sp, const Lanes& L, int p)
                         half(L.mox[q], p), half(L.moy[q], p), half(L.moz[q], p));
 }
 
-template <bool F = false>
+template <int F = 0>
 __device__ __forceinline__ void arm_ray(Lanes& L, int p, f3 o, f3 d) {
     const int q = p >> 1;
     L.dx[p] = d.x; L.dy[p] = d.y; L.dz[p] = d.z;
@@ -211,11 +211,11 @@ namespace {
 
 // mean += (color - mean) / f32(n + 1).  The first sample divides by 1.0, which is exact for every operand: skipped
 // (same bits).  Tolerance mode multiplies by the MUFU reciprocal.
-template <bool F>
+template <int F>
 __device__ __forceinline__ f3 running_mean(f3 mean, f3 color, uint32_t n) {
     const f3 delta = rtc::sub(color, mean);
     if (n == 0u) return rtc::add(mean, delta);
-    if constexpr (F) return rtc::axpy_t<true>(rtc::fastm::rcp((float)(n + 1u)), delta, mean);
+    if constexpr (F) return rtc::axpy_t<1>(rtc::fastm::rcp((float)(n + 1u)), delta, mean);
     else return rtc::add(mean, rtc::divs(delta, (float)(n + 1u)));
 }
 // Load the texels of one warp tile, apply the reset / sample-count rule of `update`
@@ -296,7 +296,7 @@ __device__ __forceinline__ void end_tile(const UpdateParams& P, const Lanes& L, 
         if (J.sampling[p]) {
             f3 color = J.black[p] ? rtc::mk(0.0f, 0.0f, 0.0f)
                                   : rtc::sky_times(J.factor[p], rtc::mk(L.dx[p], L.dy[p], L.dz[p]));
-            mean = running_mean<false>(mean, color, n);
+            mean = running_mean<0>(mean, color, n);
             n += 1u;
         }
         *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
@@ -485,7 +485,7 @@ __device__ __forceinline__ void prim_exact(uint32_t cand, int idx, const float4 
 
 // Primary rays of a strip (get_ray, compute_shader.wgsl:305-325): exact (d, o) parked in shared memory, unit
 // directions in registers.  `untraced` collects sampling rays outside primary_arm's window.
-template <bool F>
+template <int F>
 __device__ __forceinline__ void prim_setup(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
                                            float* __restrict__ s_tmp, uint32_t seed_bits, uint32_t spp, bool reset, PrimLanes& L,
                                            uint32_t& untraced) {
@@ -721,7 +721,7 @@ __device__ __forceinline__ void prim_tree_walk(const PrimTree& T, uint32_t* __re
 }
 
 // Running mean and texel store for a finished path (compute_shader.wgsl:356-363).
-template <bool F = false>
+template <int F = 0>
 __device__ __forceinline__ void finalize_texel(const UpdateParams& P, uint32_t texel_index, uint32_t n, f3 color, bool reset) {
     float4* texel = &P.accum[texel_index];
     f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
@@ -754,7 +754,7 @@ __device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_b
 
 // What happens to a traced ray (compute_shader.wgsl:267-296): returns true when the path continues (then o, d,
 // factor are the scattered ray), false when the texel has been finished.
-template <bool F = false>
+template <int F = 0>
 __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
                                             f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
                                             bool reset) {
@@ -789,7 +789,7 @@ __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t boun
 //         (miss, absorbed) or the scattered path appended to queue 1 (resolve_hit; a texel-per-thread pass of its own
 //         over P.first_hit did this in round 1: 8 B written and read back per texel, every ray generated twice).
 constexpr int kPrimHits = 0, kPrimShade = 1, kPrimQueue = 2;
-template <int kMode, bool F>
+template <int kMode, int F>
 __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int row0, float* __restrict__ s_d,
                                             const PrimLanes& L, uint32_t untraced, uint32_t seed_bits, bool reset,
                                             uint32_t& rays) {
@@ -967,7 +967,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // own (no block barrier anywhere), sets up its rays, walks the tree with the tile, scans the surviving spheres and
 // finishes the texels.  Shared memory per warp: the per-ray slots (8 KB) and the warp's work stack and candidate
 // lists (2.1 KB); 2 CTAs of 11 warps per SM (rt_kernels.cuh).
-template <int kMode, bool F>
+template <int kMode, int F>
 __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     float* s_d = reinterpret_cast<float*>(s_dyn) + threadIdx.x;                       // ray slots, this thread's column
@@ -1126,7 +1126,7 @@ namespace {
 
 // Rays j0 + p (p < NR) of the queue — consecutive entries, paths of neighbouring pixels, so the two rays of an FFMA2
 // pair tend to meet the same clusters — into the thread's first NR lanes; the others idle.
-template <int NR, bool F = false>
+template <int NR, int F = 0>
 __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                              uint32_t j0, Lanes& L, uint32_t& rays) {
 #pragma unroll
@@ -1197,7 +1197,7 @@ __device__ __forceinline__ uint32_t parked_word(const CandT* s_cand, int k) {
     if constexpr (sizeof(CandT) == 4) return s_cand[k * kBlockThreads];
     else return (uint32_t)s_cand[(2 * k) * kBlockThreads] | ((uint32_t)s_cand[(2 * k + 1) * kBlockThreads] << 16);
 }
-template <bool F, typename CandT>
+template <int F, typename CandT>
 __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
                                                  const Lanes& L, uint32_t bounce, bool last, bool reset, int lane,
                                                  CandT* s_park) {
@@ -1438,7 +1438,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
 #endif
-template <bool F, typename CandT>
+template <int F, typename CandT>
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                           const TreeView& tv, unsigned short* __restrict__ s_stack, CandT* __restrict__ s_cand,
                                           unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
@@ -1519,7 +1519,7 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
 // kGlobal: the instantiation for scenes whose image does not fit shared memory (cl_bytes == 0): the same traversal
 // reads the tree where it lies in global memory (L1 / L2; the upper levels stay hot), and the candidate codes are
 // 32 bits wide, so the sphere count is not limited by the code's 15 index bits either.
-template <bool kFinish, bool kGlobal, bool F>
+template <bool kFinish, bool kGlobal, int F>
 __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
@@ -1889,21 +1889,23 @@ cudaError_t configure_kernels() {
     cudaError_t e = set_smem(update_resident_kernel, (kResidentMaxSpheres + kGeomTail) * sizeof(float4));
     if (e != cudaSuccess) return e;
     const size_t prim = prim_smem_bytes();
-    if ((e = set_smem(primary_hits_kernel<kPrimHits, false>, prim)) != cudaSuccess) return e;
-    if ((e = set_smem(primary_hits_kernel<kPrimShade, false>, prim)) != cudaSuccess) return e;
-    if ((e = set_smem(primary_hits_kernel<kPrimQueue, false>, prim)) != cudaSuccess) return e;
-    if ((e = set_smem(primary_hits_kernel<kPrimShade, true>, prim)) != cudaSuccess) return e;
-    if ((e = set_smem(primary_hits_kernel<kPrimQueue, true>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimHits, 0>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimShade, 0>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimQueue, 0>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimShade, 1>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimQueue, 1>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimShade, 2>, prim)) != cudaSuccess) return e;
+    if ((e = set_smem(primary_hits_kernel<kPrimQueue, 2>, prim)) != cudaSuccess) return e;
     if ((e = set_smem(bounce_streamed_kernel, bounce_smem_bytes())) != cudaSuccess) return e;
     const size_t cl = clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax), clg = clustered_global_smem_bytes(kTreeStackMax);
-    if ((e = set_smem(bounce_clustered_kernel<false, false, false>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, false, false>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, true, false>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, true, false>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, false, true>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, false, true>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, true, true>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, true, true>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, false, 0>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, false, 0>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, true, 0>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, true, 0>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, false, 1>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, false, 1>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, true, 1>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, true, 1>, clg)) != cudaSuccess) return e;
     return set_smem(update_streamed_kernel, 2 * (kChunkSpheres + kGeomTail) * sizeof(float4));
 }
 
@@ -1918,7 +1920,7 @@ bool primary_pass_applies(const UpdateParams& p) {
 
 // One bounce launch of the wavefront: which instantiation depends on where the tree lives, whether this launch may finish
 // a short queue to the end, and the precision mode.
-template <bool F>
+template <int F>
 static void launch_bounce(const UpdateParams& p, bool finishing, uint32_t full_grid, uint32_t finish_grid, cudaStream_t stream) {
     if (p.cl_bytes == 0u && p.cl_global != 0u) {   // the tree stays in global memory
         const size_t smem = clustered_global_smem_bytes(p.cl_stack_cap);
@@ -1958,18 +1960,20 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         const bool shade = depth == 1u;
         const bool wavefront = !shade && p.wf_queue[0] != nullptr && p.wf_counts != nullptr && depth <= kWfMaxDepth;
         // tolerance mode exists for the fused depth-1 pass and the wavefront; the other paths are exact whatever the mode
-        const bool fast = p.precision != 0u && (shade || wavefront);
+        const uint32_t fast = (shade || wavefront) ? p.precision : 0u;
         // per-frame records; the same launch zeroes the tile tickets and (wavefront) the frame's queue counters
         e = launch_prep_primary_tree(p, wavefront, stream);
         if (e != cudaSuccess) return e;
         if (shade) {
-            if (fast) primary_hits_kernel<kPrimShade, true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
-            else primary_hits_kernel<kPrimShade, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            if (fast >= 2u) primary_hits_kernel<kPrimShade, 2><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else if (fast == 1u) primary_hits_kernel<kPrimShade, 1><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else primary_hits_kernel<kPrimShade, 0><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         } else if (wavefront) {
-            if (fast) primary_hits_kernel<kPrimQueue, true><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
-            else primary_hits_kernel<kPrimQueue, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            if (fast >= 2u) primary_hits_kernel<kPrimQueue, 2><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else if (fast == 1u) primary_hits_kernel<kPrimQueue, 1><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            else primary_hits_kernel<kPrimQueue, 0><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         } else {
-            primary_hits_kernel<kPrimHits, false><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
+            primary_hits_kernel<kPrimHits, 0><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -1990,8 +1994,8 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (fast) launch_bounce<true>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
-                else launch_bounce<false>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
+                if (fast) launch_bounce<1>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);   // (bounce rays: one fast level)
+                else launch_bounce<0>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
                 n_launch += 1;
             }
             if (launches) *launches = n_launch;

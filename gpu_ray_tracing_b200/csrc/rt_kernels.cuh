@@ -87,7 +87,7 @@ struct UpdateParams {
     float cl_entry_r;
     uint32_t* rgba8_out;            // non-null: the fused shading pass (max_depth 1) also stores the texel's RGBA8 here:
                                     // window-relative texel index, in this device's memory or in a peer's (NVLink stores)
-    uint32_t precision;             // RT_PRECISION_EXACT / RT_PRECISION_FAST (rt_set_precision)
+    uint32_t precision;             // RT_PRECISION_* (rt_set_precision)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };
 

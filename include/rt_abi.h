@@ -240,14 +240,17 @@ RT_API int rt_set_kernel_variant(RtRenderer* r, int variant);
 /* Arithmetic of the per-ray O(1) work (camera ray, scatter, sky colour, running mean).
  *   RT_PRECISION_EXACT (default): one IEEE-754 rounding per WGSL operator, pinned sin / cos — bit-identical to the CPU
  *                                 oracle of this repository.
- *   RT_PRECISION_FAST:            the same formulas through the hardware approximations (MUFU rcp / rsqrt / sqrt / sin /
- *                                 cos, FMA contraction) — what a WGSL implementation may do too, its builtin precision
- *                                 being implementation defined.  Which sphere a ray hits is still decided by the
- *                                 reference's IEEE quadratic, so a depth-1 image differs from the exact one by colour
- *                                 rounding only (<= 1/255 after RGBA8 quantisation, counted in bench.py and the tests).
- * Applies to the primary pass with fused shading (max_depth == 1) and to the wavefront (1 < max_depth <= 64); other
- * kernel variants ignore it. */
-enum { RT_PRECISION_EXACT = 0, RT_PRECISION_FAST = 1 };
+ *   RT_PRECISION_FAST_SHADING:    scatter, sky colour and running mean through the hardware approximations (MUFU rcp /
+ *                                 rsqrt / sqrt / sin / cos, FMA contraction) — what a WGSL implementation may do too, its
+ *                                 builtin precision being implementation defined.  Primary rays are generated exactly
+ *                                 and which sphere a ray hits is decided by the reference's IEEE quadratic, so a depth-1
+ *                                 image differs from the exact one by colour rounding only (<= 1/255 after RGBA8
+ *                                 quantisation; bench.py and the tests count the pixels over it).
+ *   RT_PRECISION_FAST_ALL:        get_ray as well.  A primary ray is then displaced by ~1e-7 relative, and a sample that
+ *                                 grazes a silhouette can land on the other side of it (a few pixels per million).
+ * Applies to the primary pass with fused shading (max_depth == 1) and to the wavefront (1 < max_depth <= 64), whose
+ * bounce rays know one fast level; other kernel variants ignore it. */
+enum { RT_PRECISION_EXACT = 0, RT_PRECISION_FAST_SHADING = 1, RT_PRECISION_FAST_ALL = 2 };
 RT_API int rt_set_precision(RtRenderer* r, int precision);
 
 /* ---------------------------------------------------------------------------------------

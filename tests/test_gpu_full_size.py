@@ -131,17 +131,19 @@ def test_gpu_vs_libm_oracle_mismatch_counts():
         assert rep["pixels_over_1_255"] <= bound * rep["pixels"], (depth, rep)
 
 
+@pytest.mark.parametrize("level", [rt.RT_PRECISION_FAST_SHADING, rt.RT_PRECISION_FAST_ALL])
 @pytest.mark.parametrize("depth", [1, 8])
-def test_fast_precision_mode_within_tolerance(depth):
-    """rt_set_precision(RT_PRECISION_FAST): same rays, same hit decisions for the primary rays; colours within the
-    stated tolerance of the oracle except for a bounded number of pixels (reported)."""
+def test_fast_precision_mode_within_tolerance(depth, level):
+    """rt_set_precision: FAST_SHADING keeps the primary rays and every hit decision of the exact mode, so a depth-1
+    image may differ by colour rounding and the odd material-branch decision only; FAST_ALL also approximates get_ray,
+    which moves samples across silhouettes (a few pixels per 100,000).  Counts are reported and bounded."""
     W, H = 1280, 720
     scene, cam = scenes.random_scene(1024), scenes.camera(W, H, depth, 500)
     cpu, rays_cpu = ol.oracle_update(cam, scene, W, H)
     with rt.Renderer(W, H) as r:
         r.set_scene(scene)
         r.init()
-        r.set_precision(rt.RT_PRECISION_FAST)
+        r.set_precision(level)
         r.update(cam)
         fast, rays_fast = r.read_accum(), r.rays_traced()
         r.set_precision(rt.RT_PRECISION_EXACT)
@@ -149,13 +151,12 @@ def test_fast_precision_mode_within_tolerance(depth):
         r.update(cam)
         exact = r.read_accum()
     rep = ol.compare_images(cpu, fast)
-    print(f"fast mode vs oracle, depth {depth}:", rep, "rays", rays_fast, rays_cpu)
+    print(f"precision level {level} vs oracle, depth {depth}:", rep, "rays", rays_fast, rays_cpu)
     assert_bit_identical(exact, cpu, "exact mode after switching back")
     assert (fast[..., 3] == 1.0).all()
     if depth == 1:
         assert rays_fast == rays_cpu
-        assert rep["pixels_over_1_255"] <= 2e-5 * rep["pixels"], rep
-        assert rep["max_abs"] < 1.0
+        assert rep["pixels_over_1_255"] <= (4 if level == rt.RT_PRECISION_FAST_SHADING else 1e-4 * rep["pixels"]), rep
     else:
         assert abs(rays_fast - rays_cpu) <= 0.01 * rays_cpu
         assert rep["pixels_over_1_255"] <= 0.05 * rep["pixels"], rep
