@@ -580,6 +580,74 @@ def render_frames(scene: SphereCollection, cameras, width: int, height: int, dev
     return out
 
 
+def write_png(path: str, rgba8: np.ndarray, gamma: float = None, alpha: bool = False) -> None:
+    """Write an RGBA8 image (h, w, 4) as a PNG (8-bit RGB, or RGBA with alpha=True) using only zlib: the display path
+    of the reference shows the Rgba32Float texture through a sprite (src/lib.rs:63-102); headless, the frame goes to a
+    file instead.  gamma as in write_ppm."""
+    import struct
+    import zlib
+    img = np.asarray(rgba8, dtype=np.uint8)
+    img = img[..., :4] if alpha else img[..., :3]
+    if gamma:
+        rgb = np.round(255.0 * (img[..., :3].astype(np.float32) / 255.0) ** (1.0 / gamma)).astype(np.uint8)
+        img = np.concatenate([rgb, img[..., 3:]], axis=-1) if alpha else rgb
+    h, w, c = img.shape
+    raw = np.empty((h, 1 + w * c), dtype=np.uint8)
+    raw[:, 0] = 0                                   # filter type 0 (none) per scanline
+    raw[:, 1:] = img.reshape(h, w * c)
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n")
+        f.write(chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 6 if alpha else 2, 0, 0, 0)))
+        f.write(chunk(b"IDAT", zlib.compress(raw.tobytes(), 6)))
+        f.write(chunk(b"IEND", b""))
+
+
+def read_png(path: str) -> np.ndarray:
+    """Inverse of write_png for the files it writes (8-bit RGB / RGBA, filter 0): (h, w, 3 or 4) uint8."""
+    import struct
+    import zlib
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h, c = 8, b"", 0, 0, 3
+    while pos < len(data):
+        n, tag = struct.unpack(">I", data[pos:pos + 4])[0], data[pos + 4:pos + 8]
+        body = data[pos + 8:pos + 8 + n]
+        if tag == b"IHDR":
+            w, h, depth, ctype = struct.unpack(">IIBB", body[:10])
+            assert depth == 8 and ctype in (2, 6)
+            c = 4 if ctype == 6 else 3
+        elif tag == b"IDAT":
+            idat += body
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, 1 + w * c)
+    assert not raw[:, 0].any(), "only filter type 0 is supported"
+    return raw[:, 1:].reshape(h, w, c).copy()
+
+
+def diff_image(a: np.ndarray, b: np.ndarray, scale: int = 32):
+    """Parity debugging: per-pixel difference of two rgba32f accumulations (or RGBA8 frames).  Returns
+    (rgba8 picture, report): the picture shows |a - b| of the RGBA8 quantisations times `scale` (clamped), pixels over
+    the 1/255 tolerance in pure red; the report counts them (the mismatch-pixel count the port target asks for)."""
+    def q(x):
+        x = np.asarray(x)
+        if x.dtype == np.uint8:
+            return x[..., :3].astype(np.int16)
+        return np.floor(np.clip(np.nan_to_num(x[..., :3].astype(np.float32), nan=0.0), 0.0, 1.0) * 255.0 + 0.5).astype(np.int16)
+    d = np.abs(q(a) - q(b))
+    worst = d.max(axis=-1)
+    pic = np.zeros(d.shape[:2] + (4,), dtype=np.uint8)
+    pic[..., :3] = np.clip(d * scale, 0, 255).astype(np.uint8)
+    pic[worst > 1] = (255, 0, 0, 0)
+    pic[..., 3] = 255
+    report = {"pixels": int(worst.size), "pixels_differing": int((worst > 0).sum()), "pixels_over_1_255": int((worst > 1).sum()),
+              "max_levels": int(worst.max()) if worst.size else 0}
+    return pic, report
+
+
 def write_ppm(path: str, rgba8: np.ndarray, gamma: float = None) -> None:
     """Write an RGBA8 image (h, w, 4) — e.g. Renderer.read_rgba8() — as a binary PPM for inspection.  The shader stores
     linear colour (the reference leaves any transfer curve to the display path, src/lib.rs:63-102); pass gamma=2.2 to

@@ -239,14 +239,29 @@ RT_DEV f3 sky_times(f3 factor, f3 dir) {
 // dispatch of ray_color (compute_shader.wgsl:268-286).  On return *ray is the scattered ray and
 // *factor has been multiplied by the attenuation.  Returns false when the sample is absorbed
 // (ray_color returns black, compute_shader.wgsl:274,278,282).
-template <int F = 0>
-RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
+//
+// Tolerance modes (F >= 1) evaluate the same formulas with approximations, and the branch DECISIONS in here — front
+// face, lambertian degenerate direction, metal absorb, dielectric reflect / refract — sit on thresholds: a grazing hit
+// has dot(d, n) ~ 0, and which side it falls on follows from the last bits of p.  Each decision is therefore taken with
+// a margin several times the approximation's error; a ray inside a margin sets *risky, and scatter<F> then repeats it
+// with the exact arithmetic (one shared out-of-line copy).  The tolerance modes so make the reference's decisions, ray
+// for ray, and differ from the exact mode by the rounding of the values only.
+template <int F>
+RT_DEV bool scatter_impl(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed, bool* risky) {
     f3 o = ray->o, d = ray->d;
     f3 center = mk(sp.position);
     f3 p, outward;
     if constexpr (F) {
         p = axpy_t<1>(t, d, o);
-        outward = scale(fastm::rcp(sp.radius), sub(p, center));
+        const float inv_r = fastm::rcp(sp.radius);
+        outward = scale(inv_r, sub(p, center));
+        // |dot(d, outward)| against the rounding of p (a few 2^-24 of |o| + |t d| + |c|, divided by r) times |d|
+        const float dd = dot_t<1>(d, d);
+        const float len_d = dd * fastm::rsq(dd);
+        const float mag = (fabsf(o.x) + fabsf(o.y) + fabsf(o.z)) + fabsf(t) * (fabsf(d.x) + fabsf(d.y) + fabsf(d.z)) +
+                          (fabsf(center.x) + fabsf(center.y) + fabsf(center.z));
+        const float tol = len_d * fmaf(mag * 7.62939453125e-06f /* 2^-17 */, fabsf(inv_r), 7.62939453125e-06f);
+        *risky = !(fabsf(dot_t<1>(d, outward)) > tol);
     } else {
         p = add(o, scale(t, d));
         outward = divs(sub(p, center), sp.radius);
@@ -260,6 +275,7 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
     if (w < -1.0f) {
         // lambertian_scatter, compute_shader.wgsl:84-93
         f3 dir = add(n, random_unit_vector<F>(bounce_seed));
+        if constexpr (F) *risky |= !(dot_t<1>(dir, dir) > 1e-3f);   // nearly opposite vectors: the direction is ill-conditioned
         if (dot_t<F>(dir, dir) < 1e-6f) dir = n;
         out.d = dir;
         *factor = mul(*factor, albedo);
@@ -272,6 +288,7 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
         out.d = normalize_branch<F>(reflected);
         *factor = mul(*factor, albedo);
         *ray = out;
+        if constexpr (F) *risky |= !(fabsf(dot_t<1>(reflected, n)) > 1e-4f) || !(dot_t<1>(reflected, reflected) > 1e-3f);
         return dot_t<F>(reflected, n) > 0.0f;
     } else {
         // dielectric_scatter + reflectance, compute_shader.wgsl:102-141
@@ -292,6 +309,8 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
         r0 = r0 * r0;
         float refl_prob = r0 + (1.0f - r0) * rt_pow5(1.0f - cos_theta);
         bool should_reflect = cannot_refract || refl_prob > random_float(bounce_seed);
+        if constexpr (F)
+            *risky |= !(fabsf(ratio * sin_theta - 1.0f) > 1e-4f) || !(fabsf(refl_prob - random_float(bounce_seed)) > 1e-4f);
         f3 dir;
         if (should_reflect) {
             dir = sub(ud, scale(2.0f * dot_t<F>(n, ud), n));
@@ -310,6 +329,25 @@ RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t
         // attenuation = vec3(1.0): color_factor *= 1.0 is exact, skipped
         *ray = out;
         return true;
+    }
+}
+RT_DEV_SHARED bool scatter_exact_shared(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
+    bool unused = false;
+    return scatter_impl<0>(ray, factor, t, sp, bounce_seed, &unused);
+}
+template <int F = 0>
+RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
+    bool risky = false;
+    if constexpr (F == 0) {
+        return scatter_impl<0>(ray, factor, t, sp, bounce_seed, &risky);
+    } else {
+        Ray r = *ray;
+        f3 f = *factor;
+        const bool ok = scatter_impl<F>(&r, &f, t, sp, bounce_seed, &risky);
+        if (risky) return scatter_exact_shared(ray, factor, t, sp, bounce_seed);
+        *ray = r;
+        *factor = f;
+        return ok;
     }
 }
 

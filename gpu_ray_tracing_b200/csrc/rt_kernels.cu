@@ -409,11 +409,9 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_resident_kernel(const
 // the update kernel, which skips its own first traversal when first_hit is present.
 // ---------------------------------------------------------------------------------------------
 // Linear RGBA8 of the running mean: q(x) = floor(clamp(x, 0, 1) * 255 + 0.5), alpha 255.
-__device__ __forceinline__ unsigned quant1(float v) {
-    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
-    float q = floorf(v * 255.0f + 0.5f);
-    return (q == q) ? (unsigned)q : 0u;
-}
+// (saturate maps NaN to 0 as the two-comparison clamp + NaN check of the oracle does; multiply and add round separately
+// under -fmad=false; the conversion rounds toward -infinity = floor)
+__device__ __forceinline__ unsigned quant1(float v) { return __float2uint_rd(__saturatef(v) * 255.0f + 0.5f); }
 __device__ __forceinline__ unsigned quant_texel(float4 t) {
     return quant1(t.x) | (quant1(t.y) << 8) | (quant1(t.z) << 16) | 0xFF000000u;
 }

@@ -258,3 +258,27 @@ def test_camera_script_matches_stepping_by_hand():
         want = rt.SceneCamera.from_settings(s, W, H, random_seed=seeds[f])
         assert cams[f].to_bytes() == want.to_bytes()
         assert cams[f].camera_has_moved == (0.0 if f == 5 else 1.0)
+
+
+def test_png_round_trip_and_diff_image(tmp_path):
+    """PNG writer (zlib only), its reader, and the diff-image report."""
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (37, 53, 4), dtype=np.uint8)
+    p = str(tmp_path / "x.png")
+    rt.write_png(p, img)
+    assert np.array_equal(rt.read_png(p), img[..., :3])
+    rt.write_png(p, img, alpha=True)
+    assert np.array_equal(rt.read_png(p), img)
+    a = rng.random((20, 30, 4), dtype=np.float32)
+    b = a.copy()
+    b[3, 4, 0] += 3.0 / 255.0          # over the tolerance
+    b[5, 6, 1] += 1.0 / 255.0          # one level: within it
+    pic, rep = rt.diff_image(a, b)
+    assert rep["pixels"] == 600 and rep["pixels_over_1_255"] == 1 and rep["pixels_differing"] == 2
+    assert tuple(pic[3, 4]) == (255, 0, 0, 255) and pic[0, 0, :3].sum() == 0
+
+
+def test_committed_scene_bytes_match_the_generator():
+    """tests/golden/random1024_seed1234.bin (what the CPU arms of bench.py read) == rt_create_random_spheres(1234, 1024)."""
+    raw = open(os.path.join(ROOT, "tests", "golden", "random1024_seed1234.bin"), "rb").read()
+    assert raw == rt.create_random_spheres(1024, 1234).to_bytes()
