@@ -15,6 +15,7 @@
 //                  (rtc::sphere_root), in sphere-index order with the shrinking t_max of
 //                  sphere_list_hit (compute_shader.wgsl:164-180).  Results are therefore
 //                  bit-identical to evaluating every sphere exactly.
+#include <cooperative_groups.h>
 #include <type_traits>
 
 #include "rt_kernels.cuh"
@@ -873,12 +874,14 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
             }
         }
     } else {
-        // fused epilogue: one rolled pass over the strip (rays and their nearest hits are in the slots)
+        // fused epilogue: one rolled pass over the strip (rays and their nearest hits are in the slots).  Tolerance modes:
+        // a ray whose scatter sits inside a decision margin (rtc::scatter_impl, *risky) is left alone by the first
+        // pass and finished with the exact arithmetic by a second one, which the hot loop so need not carry a call for
         const uint32_t sampling = L.alive | untraced;
-#pragma unroll 1
-        for (int p = 0; p < kPrimRays; ++p) {
+        auto shade_one = [&](int p, auto prec) -> bool {
+            constexpr int FF = decltype(prec)::value;
             const int row = row0 + p;
-            if (!((uint32_t)x < P.width && (uint32_t)row < P.row_count)) continue;
+            if (!((uint32_t)x < P.width && (uint32_t)row < P.row_count)) return false;
             float4* texel = &P.accum[(size_t)row * P.width + x];
             f3 mean = rtc::mk(0.0f, 0.0f, 0.0f);
             uint32_t n = 0;
@@ -901,21 +904,36 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                     best_t = hit.x;
                     best_i = __float_as_int(hit.y);
                 }
-                ++rays;
                 f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
                 bool black = false;
                 if (best_i >= 0) {
                     const GpuSphere sp = load_sphere(P.spheres, best_i);
                     const uint32_t seed = 1u + n + seed_bits;                       // compute_shader.wgsl:353
-                    black = !rtc::scatter<F>(&r, &factor, best_t, sp, rtc::hash(seed + 1u));   // :268 with i = 0
+                    bool risky = false;
+                    black = !rtc::scatter_impl<FF>(&r, &factor, best_t, sp, rtc::hash(seed + 1u), &risky);   // :268 with i = 0
+                    if (FF != 0 && risky) return true;   // texel untouched: the exact pass takes it
                 }
-                const f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times<F>(factor, r.d);
-                mean = running_mean<F>(mean, color, n);
+                ++rays;
+                const f3 color = black ? rtc::mk(0.0f, 0.0f, 0.0f) : rtc::sky_times<FF>(factor, r.d);
+                mean = running_mean<FF>(mean, color, n);
                 n += 1u;
             }
             *texel = make_float4(mean.x, mean.y, mean.z, (float)n);
             // the frame's RGBA8 image in the same pass when asked for (rt_set_rgba8_output): 128 B contiguous per warp row
             if (P.rgba8_out) P.rgba8_out[(size_t)row * P.width + x] = quant_texel(make_float4(mean.x, mean.y, mean.z, 0.0f));
+            return false;
+        };
+        uint32_t redo = 0;
+#pragma unroll 1
+        for (int p = 0; p < kPrimRays; ++p)
+            if (shade_one(p, std::integral_constant<int, F>())) redo |= 1u << p;
+        if constexpr (F != 0) {
+#pragma unroll 1
+            while (redo) {
+                const int p = __ffs((int)redo) - 1;
+                redo &= redo - 1u;
+                shade_one(p, std::integral_constant<int, 0>());
+            }
         }
     }
 }
@@ -1131,7 +1149,7 @@ __device__ __forceinline__ void wf_load_rays(const UpdateParams& P, const float4
     for (int p = 0; p < kPix; ++p) {
         const uint32_t j = j0 + (uint32_t)p;
         if (p < NR && j < count) {
-            const float4 A = qin[j], B = qin[(size_t)P.wf_capacity + j];
+            const float4 A = __ldcg(qin + j), B = __ldcg(qin + (size_t)P.wf_capacity + j);
             arm_ray<F>(L, p, rtc::mk(A.x, A.y, A.z), rtc::mk(A.w, B.x, B.y));
             ++rays;
         } else {
@@ -1151,7 +1169,7 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
         f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
         uint32_t texel_index = 0, bseed = 0, n = 0;
         if (j < count) {
-            const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+            const float4 B = __ldcg(qin + (size_t)P.wf_capacity + j), C = __ldcg(qin + 2 * (size_t)P.wf_capacity + j);
             factor = rtc::mk(B.z, B.w, C.x);
             texel_index = __float_as_uint(C.y);
             bseed = __float_as_uint(C.z);
@@ -1209,7 +1227,7 @@ __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const fl
         const uint32_t j = j0 + (uint32_t)p;
         push = false;
         if (j < count) {
-            const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+            const float4 B = __ldcg(qin + (size_t)P.wf_capacity + j), C = __ldcg(qin + 2 * (size_t)P.wf_capacity + j);
             factor = rtc::mk(B.z, B.w, C.x);
             texel_index = __float_as_uint(C.y);
             bseed = __float_as_uint(C.z);
@@ -1460,7 +1478,7 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
             factor[p] = rtc::mk(0.0f, 0.0f, 0.0f);
             texel_index[p] = bseed[p] = n_samples[p] = 0u;
             if (j < count) {
-                const float4 B = qin[(size_t)P.wf_capacity + j], C = qin[2 * (size_t)P.wf_capacity + j];
+                const float4 B = __ldcg(qin + (size_t)P.wf_capacity + j), C = __ldcg(qin + 2 * (size_t)P.wf_capacity + j);
                 factor[p] = rtc::mk(B.z, B.w, C.x);
                 texel_index[p] = __float_as_uint(C.y);
                 bseed[p] = __float_as_uint(C.z);
@@ -1510,15 +1528,14 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
 // per CTA; every WARP then pulls batches of 64 rays (2 per thread, one FFMA2 pair) on its own — no block barrier in
 // the loop, so a warp with deep stacks or long candidate queues delays nobody.  Two rays per thread rather than four:
 // the traversal runs as long as the busiest lane's, and a thread's work grows with its rays.
-// kFinish: the instantiation the later bounces use (launch_update), which may finish a short queue in one launch
-// (finish_paths).  The early bounces, where nearly all the rays are, run the instantiation without that code.
-// Three CTAs per SM for the full-queue instantiation (77 registers, ~60 KB of shared memory for 1024 spheres); the
-// finishing one would spill at that budget and runs when the machine is mostly idle anyway.
+// This kernel serves the early bounces, where nearly all the rays are: three CTAs per SM (80 registers, ~74 KB of shared
+// memory for 1024 spheres).  The late bounces, whose queues may be short enough to finish from registers, go to
+// bounce_tail_kernel, which carries the finishing code (it would spill at this kernel's register budget).
 // kGlobal: the instantiation for scenes whose image does not fit shared memory (cl_bytes == 0): the same traversal
 // reads the tree where it lies in global memory (L1 / L2; the upper levels stay hot), and the candidate codes are
 // 32 bits wide, so the sphere count is not limited by the code's 15 index bits either.
-template <bool kFinish, bool kGlobal, int F>
-__global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
+template <bool kGlobal, int F>
+__global__ void __launch_bounds__(kBlockThreads, 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
     using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
@@ -1554,24 +1571,85 @@ __global__ void __launch_bounds__(kBlockThreads, kFinish ? 2 : 3) bounce_cluster
     }
     const TreeView tv = tree_view(kGlobal ? P.cl_blob : (const void*)s_dyn, P.cl_n_nodes, P.cl_first_leaf, P.cl_n_entry, P.cl_entry_r,
                                   P.cl_stack_cap);
-    const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
-    if (!kFinish || count >= resident_warps * RT_WF_COMPLETE_BELOW) {
-        const uint32_t n_batches = (count + 63u) / 64u;
-        for (;;) {
-            uint32_t batch = 0;
-            if (lane == 0) batch = atomicAdd(ticket, 1u);
-            batch = __shfl_sync(kFull, batch, 0);
-            if (batch >= n_batches) break;
-            const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
-            Lanes L;
-            wf_load_rays<2, F>(P, qin, count, j0, L, rays);
-            trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
-            wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
-        }
-    } else {
-        finish_paths<F>(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+    const uint32_t n_batches = (count + 63u) / 64u;
+    for (;;) {
+        uint32_t batch = 0;
+        if (lane == 0) batch = atomicAdd(ticket, 1u);
+        batch = __shfl_sync(kFull, batch, 0);
+        if (batch >= n_batches) break;
+        const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
+        Lanes L;
+        wf_load_rays<2, F>(P, qin, count, j0, L, rays);
+        trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+        wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
     }
     wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
+}
+
+// Every bounce from P.wf_bounce to the end of the paths in ONE cooperative launch: the grid traces queue b exactly as
+// bounce_clustered_kernel does, meets at a grid barrier, reads the length of queue b + 1 and goes on — until a queue is
+// short enough to be finished from registers (finish_paths) or empty.  The late bounces of a frame are launch-bound, not
+// work-bound: at 1280x720 twenty-odd of the 29 bounce launches found a handful of rays or none, each costing a launch
+// and a drain.  Queue lengths come through ld.cg (the counters are bumped by atomics in L2; a plain load could be served
+// from an L1 line fetched for the neighbouring counter one bounce earlier), and so do the queue planes themselves
+// (wf_load_rays / wf_resolve_batch / finish_paths use __ldcg): queue b & 1 was read by this SM two bounces ago and has
+// been rewritten by others since.
+template <bool kGlobal, int F>
+__global__ void __launch_bounds__(kBlockThreads, 2) bounce_tail_kernel(const __grid_constant__ UpdateParams P) {
+    extern __shared__ float4 s_dyn[];
+    __shared__ __align__(8) uint64_t s_bar;
+    using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
+    const uint32_t image_slots = kGlobal ? 0u : (P.cl_bytes + 15u) / 16u;
+    CandT* s_cand = reinterpret_cast<CandT*>(s_dyn + image_slots) + threadIdx.x;
+    unsigned short* s_stack = reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads) + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    if constexpr (!kGlobal) {
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mbar_expect_tx(bar, P.cl_bytes);
+            bulk_copy_g2s((uint32_t)__cvta_generic_to_shared(s_dyn), P.cl_blob, P.cl_bytes, bar);
+        }
+        mbar_wait(bar, 0u);
+    }
+    const TreeView tv = tree_view(kGlobal ? P.cl_blob : (const void*)s_dyn, P.cl_n_nodes, P.cl_first_leaf, P.cl_n_entry, P.cl_entry_r,
+                                  P.cl_stack_cap);
+    const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
+    const bool reset = P.cam.camera_has_moved > 0.5f;
+    const uint32_t resident_warps = gridDim.x * (kBlockThreads / 32);
+    for (uint32_t bounce = P.wf_bounce; bounce < max_depth; ++bounce) {
+        const uint32_t count = __ldcg(&P.wf_counts[bounce]);   // grid-uniform: written before the barrier below
+        if (count == 0u) break;
+        const float4* qin = P.wf_queue[bounce & 1u];
+        unsigned int* ticket = &P.wf_counts[kWfMaxDepth + 1u + bounce];
+        const bool last = bounce + 1u >= max_depth;
+        uint32_t exact_tests = 0, rays = 0, rays_later = 0;
+        if (count >= resident_warps * RT_WF_COMPLETE_BELOW) {
+            const uint32_t n_batches = (count + 63u) / 64u;
+            for (;;) {
+                uint32_t batch = 0;
+                if (lane == 0) batch = atomicAdd(ticket, 1u);
+                batch = __shfl_sync(kFull, batch, 0);
+                if (batch >= n_batches) break;
+                const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
+                Lanes L;
+                wf_load_rays<2, F>(P, qin, count, j0, L, rays);
+                trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+                wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);
+            }
+        } else {
+            // short queue: every path to its end; nothing is queued, so the next length read is 0 for the whole grid
+            finish_paths<F>(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+        }
+        wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
+        if (last) break;
+        grid.sync();   // queue bounce + 1 and its length are complete (the barrier fences)
+    }
 }
 
 // Traces queue P.wf_bounce for scenes without a clustered image (more spheres than its shared-memory budget): 4 rays
@@ -1896,14 +1974,14 @@ cudaError_t configure_kernels() {
     if ((e = set_smem(primary_hits_kernel<kPrimQueue, 2>, prim)) != cudaSuccess) return e;
     if ((e = set_smem(bounce_streamed_kernel, bounce_smem_bytes())) != cudaSuccess) return e;
     const size_t cl = clustered_smem_bytes((uint32_t)kClusterImageMax, kTreeStackMax), clg = clustered_global_smem_bytes(kTreeStackMax);
-    if ((e = set_smem(bounce_clustered_kernel<false, false, 0>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, false, 0>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, true, 0>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, true, 0>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, false, 1>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, false, 1>, cl)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<false, true, 1>, clg)) != cudaSuccess) return e;
-    if ((e = set_smem(bounce_clustered_kernel<true, true, 1>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, 0>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_tail_kernel<false, 0>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, 0>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_tail_kernel<true, 0>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<false, 1>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_tail_kernel<false, 1>, cl)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_clustered_kernel<true, 1>, clg)) != cudaSuccess) return e;
+    if ((e = set_smem(bounce_tail_kernel<true, 1>, clg)) != cudaSuccess) return e;
     return set_smem(update_streamed_kernel, 2 * (kChunkSpheres + kGeomTail) * sizeof(float4));
 }
 
@@ -1919,18 +1997,24 @@ bool primary_pass_applies(const UpdateParams& p) {
 // One bounce launch of the wavefront: which instantiation depends on where the tree lives, whether this launch may finish
 // a short queue to the end, and the precision mode.
 template <int F>
-static void launch_bounce(const UpdateParams& p, bool finishing, uint32_t full_grid, uint32_t finish_grid, cudaStream_t stream) {
+static void launch_bounce(const UpdateParams& p, uint32_t full_grid, uint32_t finish_grid, cudaStream_t stream) {
     if (p.cl_bytes == 0u && p.cl_global != 0u) {   // the tree stays in global memory
-        const size_t smem = clustered_global_smem_bytes(p.cl_stack_cap);
-        if (!finishing) bounce_clustered_kernel<false, true, F><<<full_grid, kBlockThreads, smem, stream>>>(p);
-        else bounce_clustered_kernel<true, true, F><<<finish_grid, kBlockThreads, smem, stream>>>(p);
+        bounce_clustered_kernel<true, F><<<full_grid, kBlockThreads, clustered_global_smem_bytes(p.cl_stack_cap), stream>>>(p);
     } else if (p.cl_bytes == 0u) {   // no tree the bounce kernel can walk (node numbers beyond 16 bits): exact mode only
         bounce_streamed_kernel<<<finish_grid, kBlockThreads, bounce_smem_bytes(), stream>>>(p);
     } else {
-        const size_t smem = clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap);
-        if (!finishing) bounce_clustered_kernel<false, false, F><<<full_grid, kBlockThreads, smem, stream>>>(p);
-        else bounce_clustered_kernel<true, false, F><<<finish_grid, kBlockThreads, smem, stream>>>(p);
+        bounce_clustered_kernel<false, F><<<full_grid, kBlockThreads, clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream>>>(p);
     }
+}
+// Every remaining bounce in one cooperative launch (bounce_tail_kernel); grid = the co-resident CTAs.
+template <int F>
+static cudaError_t launch_bounce_tail(const UpdateParams& p, uint32_t grid, cudaStream_t stream) {
+    void* args[] = {const_cast<UpdateParams*>(&p)};
+    if (p.cl_bytes == 0u)
+        return cudaLaunchCooperativeKernel((const void*)bounce_tail_kernel<true, F>, dim3(grid), dim3(kBlockThreads), args,
+                                           clustered_global_smem_bytes(p.cl_stack_cap), stream);
+    return cudaLaunchCooperativeKernel((const void*)bounce_tail_kernel<false, F>, dim3(grid), dim3(kBlockThreads), args,
+                                       clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream);
 }
 
 cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
@@ -1990,10 +2074,18 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
             uint32_t finish_from = kWfFinishFrom;
             for (double q = (double)n_texels; q > 8.0 * short_queue && finish_from < depth; q *= 0.8) ++finish_from;
             finish_from = finish_from > kWfFinishFrom ? finish_from - 1 : kWfFinishFrom;
+            const bool walkable = p.cl_bytes != 0u || p.cl_global != 0u;
             for (uint32_t b = 1; b < depth; ++b) {
                 p.wf_bounce = b;
-                if (fast) launch_bounce<1>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);   // (bounce rays: one fast level)
-                else launch_bounce<0>(p, b >= finish_from, (uint32_t)sm_count * 3u, resident, stream);
+                if (walkable && b >= finish_from) {
+                    // from here on the queues can be short: the rest of the frame is one cooperative launch
+                    e = fast ? launch_bounce_tail<1>(p, resident, stream) : launch_bounce_tail<0>(p, resident, stream);
+                    if (e != cudaSuccess) return e;
+                    n_launch += 1;
+                    break;
+                }
+                if (fast) launch_bounce<1>(p, (uint32_t)sm_count * 3u, resident, stream);   // (bounce rays: one fast level)
+                else launch_bounce<0>(p, (uint32_t)sm_count * 3u, resident, stream);
                 n_launch += 1;
             }
             if (launches) *launches = n_launch;
