@@ -81,8 +81,9 @@ def workload_config(n_gpus):
         "workload": f"{N_SPHERES} random spheres (seed 1234) at {W}x{H}, max_depth 1, 1 sample/pixel, one frame per GPU per step",
         "spheres": N_SPHERES, "width": W, "height": H, "max_depth": 1, "frames_per_step": n_gpus,
         "parallelism": f"frames sharded over {n_gpus} GPU(s), scene replicated" + (
-            ", every frame's RGBA8 image stored into rank 0's device memory over NVLink by the shading pass itself "
-            "(rt_set_rgba8_target on a CUDA-IPC mapping; a release flag per frame behind the stores)" if n_gpus > 1 else ""),
+            ", every frame's RGBA8 image delivered into rank 0's device memory over NVLink (CUDA-IPC mapping): stored by the "
+            "shading pass itself with a release flag behind (N <= 4), or written locally and sent by a copy engine behind the "
+            "next frame (N >= 5, where rank 0's ingress runs near the link's bandwidth); weak_like_for_like.mode says which" if n_gpus > 1 else ""),
         "l2": "accumulation image (132.7 MB float4, stored once per step) exceeds the 126 MB L2; the 32 KB sphere buffer is shared-memory resident by design",
     }
 
@@ -333,39 +334,59 @@ def run_ours(args):
     # releases arrived[rank] = step + 1 behind them; rank 0 waits for the flags of the last step before the clock stops.
     gather = Gather(rt, dist, torch, rank, world, local_rank, world * frame_bytes) if (world > 1 or args.like_for_like) else None
 
-    def weak_step(i, deliver):
-        if deliver:
+    # Two ways to deliver a frame (args.deliver):
+    #   fused  the shading pass stores the RGBA8 texels into the slot itself (rt_set_rgba8_target) and a release flag follows;
+    #          nothing runs after the kernel, but the stores cross NVLink while the SMs compute
+    #   copy   the shading pass writes the frame into a local buffer (rt_set_rgba8_output) and a copy engine sends it on a copy
+    #          stream while the next frame renders (rt_read_rgba8_async): decoupled from the SMs, one frame of latency
+    # auto = fused while rank 0's ingress demand (N - 1 frames per step) stays under half the measured link bandwidth, copy
+    # beyond (N >= 5 here): near the link's limit the fused stores back-pressure the SMs that issue them.
+    demand_gbs = (world - 1) * frame_bytes / 0.29e-3 / 1e9
+    mode = args.deliver if args.deliver != "auto" else ("fused" if demand_gbs < 0.5 * 770.0 else "copy")
+
+    def weak_step(i, how):
+        if how == "fused":
             r.set_rgba8_target(gather.slot(i) + rank * frame_bytes)
         r.update(cam_for(i))
-        if deliver:
+        if how == "fused":
             r.stream_signal(gather.arrived(rank), i + 1)
+        elif how == "copy":
+            r.read_rgba8_async_into(gather.slot(i) + rank * frame_bytes)
 
-    def weak_region(n_steps, first, deliver):
+    def weak_region(n_steps, first, how):
         """n_steps headline steps, device-timed on the renderer's stream; returns (ms, wall window)."""
+        r.set_rgba8_target(None)
+        r.set_rgba8_output(how == "copy")
+        for i in range(3):
+            weak_step(i, how)
+        if how == "copy":
+            r.read_wait()
+        r.synchronize()
+        torch.cuda.synchronize()
+        r.reset_counters()
+        l0 = r.kernel_launches()
         barrier()
         t0 = time.perf_counter()
         r.timer_begin()
         for i in range(n_steps):
-            weak_step(first + i, deliver)
-        if deliver and rank == 0:
+            weak_step(first + i, how)
+        if how == "fused" and rank == 0:
             r.stream_wait(gather.arrived(0), world, first + n_steps, 5000)   # every rank's last frame is whole
+        if how == "copy":
+            r.read_wait()                                                   # ... has left this rank (host wait, then the end event)
         ms = r.timer_end()
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         barrier()
-        return ms, (t0, t1)
+        r.set_rgba8_target(None)
+        r.set_rgba8_output(False)
+        return ms, (t0, t1), r.rays_traced(), r.kernel_launches() - l0
 
-    deliver = world > 1
+    how = mode if world > 1 else "none"
     for i in range(Wm):
-        weak_step(i, deliver)
+        weak_step(i, "none")
     r.synchronize()
-    torch.cuda.synchronize()
-    r.reset_counters()
-    launches0 = r.kernel_launches()
-    ms, region = weak_region(K, Wm, deliver)
-    rays = r.rays_traced()
-    launches = r.kernel_launches() - launches0
-    r.set_rgba8_target(None)
+    ms, region, rays, launches = weak_region(K, Wm, how)
     timed_out = r.stream_wait_timed_out()
     mx = allreduce([ms], dist.ReduceOp.MAX)
     sm = allreduce([float(rays), float(launches)], dist.ReduceOp.SUM)
@@ -373,24 +394,27 @@ def run_ours(args):
     value = rays / (ms * 1e-3) / 1e6
     clocks = sampler.window(*region) if rank == 0 else None
 
-    # ---- the same step with the delivery at N = 1 too (what every rank does at N > 1): like-for-like basis for the
-    # scaling efficiency — the N = 1 headline above skips the RGBA8 stores because there is nothing to gather
+    # ---- like-for-like basis for the scaling efficiency: the N = 1 headline above skips the RGBA8 delivery because there is
+    # nothing to gather; here the same step WITH it — at N = 1 both ways (into a local buffer), at N > 1 the way not used above
     like = None
-    if world == 1 and args.like_for_like:
-        for i in range(3):
-            weak_step(i, True)
-        r.synchronize()
-        ms_l, _ = weak_region(K, Wm, True)
-        r.set_rgba8_target(None)
-        like = {"value": K * W * H / (ms_l * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": ms_l / K,
-                "what": "headline step + the frame's RGBA8 image stored by the shading pass into the gather buffer + completion flag, "
-                        "i.e. the per-GPU work of every rank at N > 1"}
-    elif world > 1:
-        inbound = (world - 1) * frame_bytes * K / (ms * 1e-3) / 1e9
-        like = {"value": value, "unit": "Mrays/s", "ms_per_step": ms / K, "rank0_ingress_gbs": inbound,
-                "nvlink_ingress_peak_gbs": 900.0,
-                "what": "same work per GPU as weak_like_for_like of the N = 1 run; rank 0 takes in (N-1) x 33.2 MB per step over NVLink "
-                        "(900 GB/s per direction nominal)"}
+    if args.like_for_like:
+        def timed(how_):
+            ms_ = weak_region(K, Wm, how_)[0]
+            ms_ = allreduce([ms_], dist.ReduceOp.MAX)[0]
+            return {"ms_per_step": ms_ / K, "value": world * K * W * H / (ms_ * 1e-3) / 1e6}
+        if world == 1:
+            like = {"unit": "Mrays/s", "fused": timed("fused"), "copy": timed("copy"),
+                    "what": "the headline step + the delivery of the frame's RGBA8 image every rank performs at N > 1 (into a local "
+                            "buffer here): `fused` = stored by the shading pass + completion flag, `copy` = written locally and sent "
+                            "by a copy engine behind the next frame.  Efficiency at N compares value(N) with N x the figure of the "
+                            "mode that run reports in weak_like_for_like.mode"}
+        else:
+            other = "copy" if mode == "fused" else "fused"
+            like = {"unit": "Mrays/s", "mode": mode, mode: {"ms_per_step": ms / K, "value": value}, other: timed(other),
+                    "rank0_ingress_gbs": (world - 1) * frame_bytes * K / (ms * 1e-3) / 1e9, "nvlink_ingress_peak_gbs": 770.0,
+                    "what": "same work per GPU as weak_like_for_like[mode] of the N = 1 run; rank 0 takes in (N-1) x 33.2 MB per step over "
+                            "NVLink (770 GB/s per direction measured for a peer copy on this pool, 900 nominal): gather-to-one-GPU is "
+                            "the ceiling of this leg"}
 
     # ---- the gathered frames are the frames: rank 0 re-renders rank 1's last frame and compares it with its slot ---
     gather_check = None
@@ -598,9 +622,10 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
     Time = rank 0's device time for K whole frames.  Afterwards rank 0 renders the same frame alone (t1) and compares."""
     K = max(5, min(args.steps, 20))
     frame8 = W8K * H8K * 4
-    row_begin, rows = rt.shard_rows(H8K, world, rank)
+    band_rows = 16
     g = Gather(rt, dist, torch, rank, world, local_rank, frame8)
-    rs = rt.Renderer(W8K, H8K, device=local_rank, row_begin=row_begin, row_count=rows)
+    # interleaved 16-row bands, not contiguous blocks: rows that hold geometry cost more than sky rows
+    rs = rt.Renderer(W8K, H8K, device=local_rank, bands=(band_rows, world, rank))
     rs.set_scene(scene)
     rs.init()
 
@@ -610,7 +635,7 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
     def frame(f):
         if f >= 2:
             rs.stream_wait(g.consumed(), 1, f - 1, 5000)
-        rs.set_rgba8_target(g.slot(f) + row_begin * W8K * 4)
+        rs.set_rgba8_target(g.slot(f))
         rs.update(cam8(f))
         rs.stream_signal(g.arrived(rank), f + 1)
         if rank == 0:
@@ -661,8 +686,8 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
             t1 = r1.timer_end() / K
             want = device_bytes(torch, g.slot(0), frame8).reshape(H8K, W8K, 4)
             identical = bool(np.array_equal(got, want))
-        out = {"workload": f"one {W8K}x{H8K} frame / {N_SPHERES} spheres / depth 1 per step, rows split over {world} rank(s) "
-                           "(rt_shard_rows), RGBA8 row blocks stored into rank 0's frame by the shading pass over NVLink, "
+        out = {"workload": f"one {W8K}x{H8K} frame / {N_SPHERES} spheres / depth 1 per step, interleaved {band_rows}-row bands dealt over "
+                           f"{world} rank(s) (rt_create_bands), RGBA8 rows stored into rank 0's frame by the shading pass over NVLink, "
                            "arrived / consumed flags per frame",
                "ms": ms, "mrays_s": W8K * H8K / ms / 1e3, "ms_without_gather": ms_nog,
                "t1_ms_same_run": t1, "speedup_vs_1": t1 / ms, "speedup_vs_1_without_gather": t1 / ms_nog,
@@ -853,6 +878,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the sustained leg (0 = skip)")
+    ap.add_argument("--deliver", choices=["auto", "fused", "copy"], default="auto",
+                    help="N > 1: how a finished frame reaches rank 0 (see run_ours)")
     ap.add_argument("--no-like-for-like", dest="like_for_like", action="store_false",
                     help="N = 1: skip the second timing of the headline step with the RGBA8 delivery of the N > 1 ranks")
     args = ap.parse_args()

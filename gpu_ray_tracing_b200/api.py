@@ -112,6 +112,9 @@ _SIGNATURES = {
     "rt_device_count": (C.c_int, [C.POINTER(C.c_int)]),
     "rt_create": (C.c_int, [C.c_int, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
     "rt_create_window": (C.c_int, [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_create_bands": (C.c_int, [C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_shard_bands": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "rt_bands": (C.c_int, [_P, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "rt_destroy": (C.c_int, [_P]),
     "rt_set_scene": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32]),
     "rt_init": (C.c_int, [_P]),
@@ -154,6 +157,7 @@ _SIGNATURES = {
     "rt_render_frames": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
     "rt_shard_rows": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "rt_multi_create": (C.c_int, [C.POINTER(C.c_int), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
+    "rt_multi_create_bands": (C.c_int, [C.POINTER(C.c_int), C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(_P)]),
     "rt_multi_destroy": (C.c_int, [_P]),
     "rt_multi_set_scene": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32]),
     "rt_multi_init": (C.c_int, [_P]),
@@ -312,12 +316,27 @@ def camera_script(settings: CameraSettings, keys, dt: float, width: int, height:
 class Renderer:
     """One device, one accumulation image (or a row window of it)."""
 
-    def __init__(self, width: int, height: int, device: int = 0, row_begin: int = 0, row_count: int = None):
+    def __init__(self, width: int, height: int, device: int = 0, row_begin: int = 0, row_count: int = None, bands=None):
+        """bands = (band_rows, n_shards, index): an interleaved shard (rt_create_bands) instead of a contiguous window."""
         self._h = C.c_void_p()
-        if row_count is None:
-            row_count = height - row_begin
-        _check(lib().rt_create_window(device, width, height, row_begin, row_count, C.byref(self._h)))
+        self.bands = bands
+        if bands is not None:
+            band_rows, n_shards, index = bands
+            row_begin, row_count = index * band_rows, shard_bands(height, band_rows, n_shards, index)
+            _check(lib().rt_create_bands(device, width, height, band_rows, n_shards, index, C.byref(self._h)))
+        else:
+            if row_count is None:
+                row_count = height - row_begin
+            _check(lib().rt_create_window(device, width, height, row_begin, row_count, C.byref(self._h)))
         self.width, self.height, self.row_begin, self.row_count, self.device = width, height, row_begin, row_count, device
+
+    def image_rows(self) -> np.ndarray:
+        """Image row of every window row, in window order (what read_accum / read_rgba8 return)."""
+        r = np.arange(self.row_count)
+        if self.bands is None:
+            return self.row_begin + r
+        band_rows, n_shards, index = self.bands
+        return (r // band_rows * n_shards + index) * band_rows + r % band_rows
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -476,6 +495,13 @@ class Renderer:
         return p.value or 0
 
 
+def shard_bands(height: int, band_rows: int, n_shards: int, index: int) -> int:
+    """Rows an interleaved shard owns — rt_shard_bands."""
+    c = C.c_uint32(0)
+    _check(lib().rt_shard_bands(height, band_rows, n_shards, index, C.byref(c)))
+    return c.value
+
+
 def shard_rows(height: int, n_shards: int, index: int):
     """(row_begin, row_count) of shard `index` — rt_shard_rows."""
     b, c = C.c_uint32(0), C.c_uint32(0)
@@ -486,10 +512,14 @@ def shard_rows(height: int, n_shards: int, index: int):
 class MultiRenderer:
     """One image sharded by row blocks over several devices of this host (rt_multi_*)."""
 
-    def __init__(self, devices, width: int, height: int):
+    def __init__(self, devices, width: int, height: int, band_rows: int = 0):
+        """band_rows > 0: interleaved bands of that many rows (balanced), else contiguous row blocks."""
         self._h = C.c_void_p()
         arr = (C.c_int * len(devices))(*devices)
-        _check(lib().rt_multi_create(arr, len(devices), width, height, C.byref(self._h)))
+        if band_rows:
+            _check(lib().rt_multi_create_bands(arr, len(devices), width, height, band_rows, C.byref(self._h)))
+        else:
+            _check(lib().rt_multi_create(arr, len(devices), width, height, C.byref(self._h)))
         self.width, self.height, self.devices = width, height, list(devices)
 
     def close(self):

@@ -124,6 +124,45 @@ int rt_create(int device, uint32_t width, uint32_t height, RtRenderer** out) {
     return rt_create_window(device, width, height, 0, height, out);
 }
 
+int rt_shard_bands(uint32_t height, uint32_t band_rows, uint32_t n_shards, uint32_t index, uint32_t* row_count) {
+    if (!row_count) return fail(RT_ERR_INVALID_ARG, "null argument");
+    if (band_rows == 0 || band_rows % 8u != 0u) return fail(RT_ERR_INVALID_ARG, "band_rows %u is not a positive multiple of 8", band_rows);
+    if (n_shards == 0 || index >= n_shards) return fail(RT_ERR_INVALID_ARG, "shard %u of %u", index, n_shards);
+    const uint32_t bands = (height + band_rows - 1) / band_rows;
+    if (bands <= index) { *row_count = 0; return RT_OK; }
+    const uint32_t mine = (bands - index + n_shards - 1) / n_shards;        // bands index, index + n, ...
+    uint32_t rows = mine * band_rows;
+    const uint32_t last_band = index + (mine - 1) * n_shards;
+    if (last_band == bands - 1) rows -= bands * band_rows - height;         // the image's last band may be short
+    *row_count = rows;
+    return RT_OK;
+}
+
+int rt_create_bands(int device, uint32_t width, uint32_t height, uint32_t band_rows, uint32_t n_shards, uint32_t index,
+                    RtRenderer** out) {
+    if (!out) return fail(RT_ERR_INVALID_ARG, "out is null");
+    *out = nullptr;
+    uint32_t rows = 0;
+    int rc = rt_shard_bands(height, band_rows, n_shards, index, &rows);
+    if (rc != RT_OK) return rc;
+    if (rows == 0) return fail(RT_ERR_INVALID_ARG, "shard %u of %u owns no band of a %u-row image", index, n_shards, height);
+    // created as a window of `rows` rows at the top, then re-labelled: the kernels map window rows to image rows (abs_row)
+    rc = rt_create_window(device, width, height, 0, rows, out);
+    if (rc != RT_OK) return rc;
+    (*out)->row_begin = index * band_rows;
+    (*out)->band_rows = band_rows;
+    (*out)->band_stride = n_shards * band_rows;
+    return RT_OK;
+}
+
+int rt_bands(RtRenderer* r, uint32_t* band_rows, uint32_t* n_shards, uint32_t* index) {
+    if (!r) return fail(RT_ERR_INVALID_ARG, "null renderer");
+    if (band_rows) *band_rows = r->band_rows;
+    if (n_shards) *n_shards = r->band_rows ? r->band_stride / r->band_rows : 1u;
+    if (index) *index = r->band_rows ? r->row_begin / r->band_rows : 0u;
+    return RT_OK;
+}
+
 int rt_destroy(RtRenderer* r) {
     if (!r) return RT_OK;
     cudaSetDevice(r->device);
@@ -213,6 +252,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.n_spheres = r->n_spheres;
     p.width = r->width; p.height = r->height;
     p.row_begin = r->row_begin; p.row_count = r->row_count;
+    p.band_rows = r->band_rows; p.band_stride = r->band_stride;
     p.tiles_x = (r->width + rtk::kWarpTileW - 1) / rtk::kWarpTileW;
     p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
     p.tile_counter = r->tile_counter;
@@ -276,11 +316,13 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.wf_capacity = (uint32_t)r->n_texels;
     p.wf_bounce = 0;
     p.rgba8_out = nullptr;
+    p.rgba8_abs = 0u;
     p.precision = (uint32_t)r->precision;
     r->rgba8_fresh = false;
     r->target_fresh = false;
     if (r->rgba8_target && rtk::fused_shade_applies(p, r->variant)) {
-        p.rgba8_out = r->rgba8_target;   // fused gather: the texels go where the caller wants them, possibly a peer GPU
+        p.rgba8_out = r->rgba8_target;   // fused gather: the texels go into the caller's full image, possibly on a peer GPU
+        p.rgba8_abs = 1u;
         r->target_fresh = true;
     } else if (r->rgba8_output && rtk::fused_shade_applies(p, r->variant)) {
         // the slot the next rt_read_rgba8_async will send: its previous copy must have left it

@@ -11,6 +11,7 @@ struct RtRenderer {
     int device = 0;
     int sm_count = 0;
     uint32_t width = 0, height = 0, row_begin = 0, row_count = 0;
+    uint32_t band_rows = 0, band_stride = 0;   // interleaved window (rt_create_bands); 0 = contiguous
     uint64_t n_texels = 0;
     cudaStream_t stream = nullptr;
     float4* accum = nullptr;              // (mean.rgb, n) per texel of the window

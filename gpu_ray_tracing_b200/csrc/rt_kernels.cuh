@@ -66,7 +66,9 @@ struct UpdateParams {
     const GpuSphere* spheres;   // the caller's buffer as uploaded (32 B stride)
     uint32_t n_spheres;
     uint32_t width, height;     // full image
-    uint32_t row_begin, row_count;  // window
+    uint32_t row_begin, row_count;  // window: rows [row_begin, row_begin + row_count) of the image, or (band_rows != 0) the
+                                    // bands row_begin / band_rows + k * band_stride / band_rows, row_count rows in all
+    uint32_t band_rows, band_stride;
     uint32_t tiles_x, n_tiles;  // warp tiles over the window
     unsigned int* tile_counter; // dynamic tile schedulers, zeroed before the launch: [0] update, [1] primary pass
     const float4* prim_tree;    // per-frame common-origin records (oc, -q) of the tree's child slots (cl_n_nodes * kTreeStride);
@@ -87,6 +89,7 @@ struct UpdateParams {
     float cl_entry_r;
     uint32_t* rgba8_out;            // non-null: the fused shading pass (max_depth 1) also stores the texel's RGBA8 here:
                                     // window-relative texel index, in this device's memory or in a peer's (NVLink stores)
+    uint32_t rgba8_abs;             // rgba8_out holds the full image (gather target): index by absolute row
     uint32_t precision;             // RT_PRECISION_* (rt_set_precision)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
 };

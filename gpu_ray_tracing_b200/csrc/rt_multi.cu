@@ -20,6 +20,7 @@ struct RtMultiRenderer {
     std::vector<RtRenderer*> shards;
     std::vector<char> direct;        // shard i can store into devices[0]'s memory (same device or peer access)
     uint32_t width = 0, height = 0;
+    uint32_t band_rows = 0;          // 0: contiguous row blocks (rt_shard_rows); else interleaved bands (rt_create_bands)
     uchar4* full_rgba8 = nullptr;    // on devices[0]
     float4* full_accum = nullptr;    // on devices[0], allocated on first use
 };
@@ -63,19 +64,59 @@ int rt_multi_destroy(RtMultiRenderer* m) {
     return RT_OK;
 }
 
+// One shard's rows (window order) into its places in a full image on devices[0]: one copy for a contiguous block, one
+// strided 2-D copy over the whole bands (+ one for a short last band) for an interleaved shard.  elem = bytes per texel.
+static cudaError_t scatter_rows(const RtMultiRenderer* m, const RtRenderer* s, void* full, const void* src, size_t elem) {
+    const size_t row_bytes = (size_t)m->width * elem;
+    unsigned char* dst = static_cast<unsigned char*>(full);
+    const unsigned char* from = static_cast<const unsigned char*>(src);
+    if (s->band_rows == 0)
+        return cudaMemcpyAsync(dst + (size_t)s->row_begin * row_bytes, from, (size_t)s->row_count * row_bytes, cudaMemcpyDefault, s->stream);
+    const size_t band_bytes = (size_t)s->band_rows * row_bytes;
+    const uint32_t whole = s->row_count / s->band_rows, rest = s->row_count % s->band_rows;
+    cudaError_t e = cudaSuccess;
+    if (whole)
+        e = cudaMemcpy2DAsync(dst + (size_t)s->row_begin * row_bytes, (size_t)s->band_stride * row_bytes, from, band_bytes, band_bytes,
+                              whole, cudaMemcpyDefault, s->stream);
+    if (e == cudaSuccess && rest)
+        e = cudaMemcpyAsync(dst + ((size_t)s->row_begin + (size_t)whole * s->band_stride) * row_bytes, from + (size_t)whole * band_bytes,
+                            (size_t)rest * row_bytes, cudaMemcpyDefault, s->stream);
+    return e;
+}
+
+static int multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height, uint32_t band_rows,
+                        RtMultiRenderer** out);
+
 int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height, RtMultiRenderer** out) {
+    return multi_create(devices, n_devices, width, height, 0, out);
+}
+
+int rt_multi_create_bands(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height, uint32_t band_rows,
+                          RtMultiRenderer** out) {
+    if (band_rows == 0 || band_rows % 8u != 0u) return fail(RT_ERR_INVALID_ARG, "band_rows %u is not a positive multiple of 8", band_rows);
+    return multi_create(devices, n_devices, width, height, band_rows, out);
+}
+
+static int multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height, uint32_t band_rows,
+                        RtMultiRenderer** out) {
     if (!out) return fail(RT_ERR_INVALID_ARG, "out is null");
     *out = nullptr;
     if (!devices || n_devices == 0) return fail(RT_ERR_INVALID_ARG, "no devices");
     if (height < n_devices) return fail(RT_ERR_INVALID_ARG, "fewer rows (%u) than devices (%u)", height, n_devices);
     RtMultiRenderer* m = new (std::nothrow) RtMultiRenderer();
     if (!m) return fail(RT_ERR_OUT_OF_MEMORY, "host allocation failed");
-    m->width = width; m->height = height;
+    m->width = width; m->height = height; m->band_rows = band_rows;
+    if (band_rows && (height + band_rows - 1) / band_rows < n_devices) { delete m; return fail(RT_ERR_INVALID_ARG, "fewer bands than devices"); }
     for (uint32_t i = 0; i < n_devices; ++i) {
         uint32_t r0 = 0, rows = 0;
-        int rc = rt_shard_rows(height, n_devices, i, &r0, &rows);
+        int rc = RT_OK;
         RtRenderer* s = nullptr;
-        if (rc == RT_OK) rc = rt_create_window(devices[i], width, height, r0, rows, &s);
+        if (band_rows) {
+            rc = rt_create_bands(devices[i], width, height, band_rows, n_devices, i, &s);
+        } else {
+            rc = rt_shard_rows(height, n_devices, i, &r0, &rows);
+            if (rc == RT_OK) rc = rt_create_window(devices[i], width, height, r0, rows, &s);
+        }
         if (rc != RT_OK) { rt_multi_destroy(m); return rc; }
         m->shards.push_back(s);
     }
@@ -103,7 +144,7 @@ int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint
     if (e != cudaSuccess) { rt_multi_destroy(m); return fail_cuda(e, "rt_multi_create"); }
     // fused gather: the shading pass of a depth-1 update stores the shard's rows straight into the full frame
     for (uint32_t i = 0; i < n_devices; ++i)
-        if (m->direct[i]) rt_set_rgba8_target(m->shards[i], m->full_rgba8 + (size_t)m->shards[i]->row_begin * width);
+        if (m->direct[i]) rt_set_rgba8_target(m->shards[i], m->full_rgba8);
     *out = m;
     return RT_OK;
 }
@@ -143,8 +184,7 @@ int rt_multi_gather_rgba8(RtMultiRenderer* m, uint8_t* host) {
         int rc = rt_quantize(s);
         if (rc != RT_OK) return rc;
         RTM_CUDA(cudaSetDevice(s->device));
-        RTM_CUDA(cudaMemcpyPeerAsync(m->full_rgba8 + (size_t)s->row_begin * m->width, dev0, s->rgba8, s->device,
-                                     s->n_texels * sizeof(uchar4), s->stream));
+        RTM_CUDA(scatter_rows(m, s, m->full_rgba8, s->rgba8, sizeof(uchar4)));
     }
     for (RtRenderer* s : m->shards) {
         RTM_CUDA(cudaSetDevice(s->device));
@@ -166,8 +206,7 @@ int rt_multi_gather_accum(RtMultiRenderer* m, float* host) {
     }
     for (RtRenderer* s : m->shards) {
         RTM_CUDA(cudaSetDevice(s->device));
-        RTM_CUDA(cudaMemcpyPeerAsync(m->full_accum + (size_t)s->row_begin * m->width, dev0, s->accum, s->device,
-                                     s->n_texels * sizeof(float4), s->stream));
+        RTM_CUDA(scatter_rows(m, s, m->full_accum, s->accum, sizeof(float4)));
     }
     for (RtRenderer* s : m->shards) {
         RTM_CUDA(cudaSetDevice(s->device));

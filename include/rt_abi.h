@@ -130,6 +130,16 @@ RT_API int rt_device_count(int* count);              /* RT_ERR_NO_DEVICE when CU
 RT_API int rt_create(int device, uint32_t width, uint32_t height, RtRenderer** out);
 RT_API int rt_create_window(int device, uint32_t width, uint32_t height,
                             uint32_t row_begin, uint32_t row_count, RtRenderer** out);
+/* An INTERLEAVED shard: the renderer owns bands index, index + n_shards, index + 2 n_shards, ... of band_rows rows each
+ * (band_rows: a positive multiple of 8).  Contiguous row blocks balance only while every row costs the same; the culled
+ * kernels spend more on rows that hold geometry than on sky, and bounce rays (max_depth > 1) cluster on the lower rows,
+ * so a sharded image is balanced by dealing narrow bands round-robin.  Window row r is image row
+ * (r / band_rows * n_shards + index) * band_rows + r % band_rows; rt_read_accum / rt_read_rgba8 return the window's rows
+ * in window order (rt_shard_bands gives their number).  Everything else behaves as for rt_create_window. */
+RT_API int rt_create_bands(int device, uint32_t width, uint32_t height, uint32_t band_rows, uint32_t n_shards,
+                           uint32_t index, RtRenderer** out);
+RT_API int rt_shard_bands(uint32_t height, uint32_t band_rows, uint32_t n_shards, uint32_t index, uint32_t* row_count);
+RT_API int rt_bands(RtRenderer* r, uint32_t* band_rows, uint32_t* n_shards, uint32_t* index);   /* band_rows 0: contiguous */
 RT_API int rt_destroy(RtRenderer* r);
 
 /* prepare_sphere_buffer (src/lib.rs:177-207): `spheres` points at `buffer_len` structs of which
@@ -168,11 +178,12 @@ RT_API int rt_read_wait(RtRenderer* r);   /* every asynchronous read issued so f
  * image, into the buffer the next rt_read_rgba8_async sends, so that read needs no quantise pass of its own (one kernel
  * less per frame, 166 MB less HBM traffic at 4K).  Other updates and reads behave as before.  Off by default. */
 RT_API int rt_set_rgba8_output(RtRenderer* r, int enable);
-/* Fused gather.  device_rgba8 != NULL: updates whose shading is finished inside the primary pass (max_depth == 1) store
- * the window's RGBA8 texels straight to device_rgba8[window-relative texel index] — device memory of this GPU or of a
- * peer (mapped with rt_ipc_open, or any pointer of a peer with access enabled): the row block of a sharded image lands in
- * the owner's frame WHILE the kernel computes, 128 contiguous bytes per warp row over NVLink, and no copy follows the
- * kernel ("the final image is gathered by peer copy over NVLink", fused into the producing pass).  NULL: off.
+/* Fused gather.  device_rgba8 != NULL names texel (0, 0) of a FULL width x height RGBA8 image in device memory of this
+ * GPU or of a peer (mapped with rt_ipc_open, or any pointer of a peer with access enabled): updates whose shading is
+ * finished inside the primary pass (max_depth == 1) store every texel of the renderer's window straight to its place
+ * there, device_rgba8[y * width + x] with y the image row.  The rows of a sharded image so land in the owner's frame
+ * WHILE the kernel computes, 128 contiguous bytes per warp row over NVLink, and no copy follows the kernel ("the final
+ * image is gathered by peer copy over NVLink", fused into the producing pass).  NULL: off.
  * rt_read_rgba8* keep working (they quantise into the renderer's own buffers). */
 RT_API int rt_set_rgba8_target(RtRenderer* r, void* device_rgba8);
 /* Completion protocol of such a gather, enqueued on the renderer's stream (no host synchronisation):
@@ -276,6 +287,10 @@ RT_API int rt_render_frames(int device, const GpuSphere* spheres, uint32_t count
 RT_API int rt_shard_rows(uint32_t height, uint32_t n_shards, uint32_t index, uint32_t* row_begin, uint32_t* row_count);
 RT_API int rt_multi_create(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height,
                            RtMultiRenderer** out);
+/* The same with interleaved bands of band_rows rows (rt_create_bands) instead of contiguous blocks: balanced whatever
+ * the image holds where. */
+RT_API int rt_multi_create_bands(const int* devices, uint32_t n_devices, uint32_t width, uint32_t height,
+                                 uint32_t band_rows, RtMultiRenderer** out);
 RT_API int rt_multi_destroy(RtMultiRenderer* m);
 RT_API int rt_multi_set_scene(RtMultiRenderer* m, const GpuSphere* spheres, uint32_t buffer_len, uint32_t count);
 RT_API int rt_multi_init(RtMultiRenderer* m);

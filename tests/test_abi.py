@@ -282,3 +282,14 @@ def test_committed_scene_bytes_match_the_generator():
     """tests/golden/random1024_seed1234.bin (what the CPU arms of bench.py read) == rt_create_random_spheres(1234, 1024)."""
     raw = open(os.path.join(ROOT, "tests", "golden", "random1024_seed1234.bin"), "rb").read()
     assert raw == rt.create_random_spheres(1024, 1234).to_bytes()
+
+
+def test_band_shards_partition_the_rows():
+    """rt_shard_bands: interleaved shards own every row exactly once, for ragged heights and more shards than bands."""
+    for H, band, n in ((4320, 16, 8), (203, 8, 3), (64, 8, 8), (17, 8, 2), (100, 24, 5)):
+        total = sum(rt.shard_bands(H, band, n, i) for i in range(n))
+        assert total == H, (H, band, n, total)
+    assert rt.shard_bands(16, 8, 4, 3) == 0
+    c = C.c_uint32()
+    assert rt.lib().rt_shard_bands(100, 12, 2, 0, C.byref(c)) == api.RT_ERR_INVALID_ARG      # not a multiple of 8
+    assert rt.lib().rt_shard_bands(100, 8, 2, 2, C.byref(c)) == api.RT_ERR_INVALID_ARG

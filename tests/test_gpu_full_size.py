@@ -251,7 +251,7 @@ def test_fused_rgba8_target_and_stream_flags():
         with rt.Renderer(W, H, row_begin=r0, row_count=rows) as r:
             r.set_scene(scene)
             r.init()
-            r.set_rgba8_target(full + r0 * W * 4)
+            r.set_rgba8_target(full)                             # texel (0, 0) of the FULL image
             before = r.kernel_launches()
             r.update(cam)
             assert r.kernel_launches() - before == 2            # records + primary pass: no quantise, no copy
@@ -296,3 +296,47 @@ def test_multi_renderer_on_distinct_devices():
             accum = m.gather_accum()
         assert np.array_equal(accum.view(np.uint32), single.view(np.uint32))
         assert np.array_equal(rgba, ol.quantize(single))
+
+
+@pytest.mark.parametrize("depth", [1, 6])
+def test_interleaved_band_shards_equal_the_whole_image(depth):
+    """rt_create_bands: three shards owning every third 8-row band (ragged height: the last band is short) render exactly
+    the texels of the single renderer; at depth 1 their fused stores assemble the RGBA8 image in one full-frame buffer."""
+    W, H, band, n = 500, 203, 8, 3
+    scene, cam = scenes.random_scene(400), scenes.camera(W, H, depth, 4)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        r.update(cam)
+        whole, rays_whole = r.read_accum(), r.rays_traced()
+    full = rt.device_alloc(0, W * H * 4)
+    try:
+        device_fill(full, 0, W * H * 4)
+        got = np.zeros_like(whole)
+        rays = 0
+        rows_seen = []
+        for idx in range(n):
+            with rt.Renderer(W, H, bands=(band, n, idx)) as r:
+                assert r.row_count == rt.shard_bands(H, band, n, idx)
+                r.set_scene(scene)
+                r.init()
+                r.set_rgba8_target(full)
+                r.update(cam)
+                rows = r.image_rows()
+                got[rows] = r.read_accum()
+                rays += r.rays_traced()
+                rows_seen.append(rows)
+        assert sorted(np.concatenate(rows_seen).tolist()) == list(range(H))
+        assert rays == rays_whole
+        assert np.array_equal(got.view(np.uint32), whole.view(np.uint32))
+        if depth == 1:
+            assert np.array_equal(device_bytes(full, W * H * 4).reshape(H, W, 4), ol.quantize(whole))
+    finally:
+        rt.device_free(0, full)
+    have = rt.device_count()
+    with rt.MultiRenderer([i % have for i in range(n)], W, H, band_rows=band) as m:
+        m.set_scene(scene)
+        m.init()
+        m.update(cam)
+        assert np.array_equal(m.gather_rgba8(), ol.quantize(whole))
+        assert np.array_equal(m.gather_accum().view(np.uint32), whole.view(np.uint32))
