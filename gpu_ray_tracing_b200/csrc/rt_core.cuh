@@ -473,39 +473,6 @@ RT_DEV void primary_record(const GpuSphere& s, f3 o, double rho, float out[4]) {
     out[3] = -rt_double2float_rd(q);
 }
 
-// The same record evaluated in binary32, for a GROUP of the tree and a common origin found at run time: the bounce
-// rays of one warp batch start on neighbouring surface points, all within `rho` of the centre `o` of their bounding
-// box, so the entry list of the tree can be met with the 3-FFMA half-line test as well (rt_kernels.cu, trace_tree).
-// Every intermediate is padded in the safe direction by 2^-18 ... 2^-20 relative, several times the 2^-24 per
-// operation it covers (cc, S and R are sums of non-negative terms: no cancellation before the one subtraction that
-// forms cp, which is padded on both operands); q so comes out BELOW primary_record's value for the same inputs,
-// i.e. the test is at most more permissive.  radius: the group's bounding radius, already inflated by the batch's
-// share of the members' kappa S terms (warp_origin_margin, the counterpart of primary_m_cam).
-RT_DEV void warp_origin_record(float cx, float cy, float cz, float radius, f3 o, float rho, float out[4]) {
-    const float ocx = cx - o.x, ocy = cy - o.y, ocz = cz - o.z, r = fabsf(radius);
-    const float cc = fmaf(ocx, ocx, fmaf(ocy, ocy, ocz * ocz)), rr = r * r;
-    const float S = fmaf(rho, rho, cc + rr) * 1.00000095367431640625f;                                      // >= |oc|^2 + r^2 + rho^2
-    const float R = (sqrtf(fmaf((float)RT_KAPPA, S, rr)) * 1.00000095367431640625f + rho) * 1.00000095367431640625f;   // >= sqrt(r^2 + kappa S) + rho
-    const float cp = cc * 0.99999904632568359375f - (R * R) * 1.000003814697265625f;                        // <= |oc|^2 - R^2 (1 + 2^-20)
-    const float m = fmaxf(fmaxf(fabsf(ocx), fabsf(ocy)), fmaxf(fabsf(ocz), r));
-    bool ok = (m <= (float)RT_PRIMARY_MAG) && (S >= 8.673617379884035e-19f) && (cp > 0.0f) && (rho <= (float)RT_PRIMARY_MAG);
-    float q = 0.0f;
-    if (ok) {
-        q = sqrtf(cp) * 0.999996185302734375f - 7.62939453125e-06f /* 2^-17 */ * sqrtf(S);
-        ok = q > 0.0f;
-    }
-    if (!ok) {   // also taken by any NaN above
-        out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = 1.0f;
-        return;
-    }
-    out[0] = ocx; out[1] = ocy; out[2] = ocz;
-    out[3] = -(q * 0.99999904632568359375f);
-}
-// The batch's share of a group's bounding radius: 2^-7 (|o| + rho), rounded up with room to spare (primary_m_cam).
-RT_DEV float warp_origin_margin(f3 o, float rho) {
-    return (sqrtf(dot(o, o)) * 1.0000009537f + rho) * 0.00782012939453125f;   // 2^-7 (1 + 2^-10)
-}
-
 // Record of a padding slot: never a candidate.
 RT_DEV void primary_record_pad(float out[4]) { out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f; out[3] = -1.0f; }
 

@@ -1309,8 +1309,7 @@ struct TreeView {
     const uint32_t* link;
     const float* node_r;
     const float4* entry_rec;            // the entry list (rt_tree.h): records ...
-    const uint32_t* entry_node;         // ... the nodes they stand for ...
-    const float* entry_rad;             // ... and their bounding radii (< 0: none, always descended into)
+    const uint32_t* entry_node;         // ... and the nodes they stand for
     int first_leaf, n_entry_pad, stack_cap;
     float entry_r;
 };
@@ -1325,7 +1324,6 @@ __device__ __forceinline__ TreeView tree_view(const void* blob, uint32_t n_nodes
     tv.node_r = reinterpret_cast<const float*>(b + lay.off_r);
     tv.entry_rec = reinterpret_cast<const float4*>(b + lay.off_entry_rec);
     tv.entry_node = reinterpret_cast<const uint32_t*>(b + lay.off_entry_node);
-    tv.entry_rad = reinterpret_cast<const float*>(b + lay.off_entry_rad);
     tv.first_leaf = (int)first_leaf;
     tv.n_entry_pad = (int)lay.n_entry_pad;
     tv.stack_cap = (int)stack_cap;
@@ -1425,128 +1423,24 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
         if (__any_sync(kFull, n_cand > kWfCand - 2 * kTreeWide)) drain_candidates(s_cand, n_cand, spheres, L, exact_tests, nan_rays);
     }
     };
-    // The entry list.  The 64 rays of a batch leave neighbouring pixels' hit points, so their origins usually sit in a
-    // small ball (centre ow, radius rho) — and then the entry records can be met as the primary pass meets its records:
-    // one common-origin record per entry for THIS batch (rtc::warp_origin_record, 4 entries per lane, parked in the
-    // warp's idle candidate columns) and the 3-FFMA half-line sign test per (ray, entry) instead of the 7-FFMA line
-    // test — which also drops every group BEHIND the rays, where the line test sends half of the visits.  (An entry the
-    // ball touches has an always-record.)  A batch whose origins are spread out (a silhouette in the block, the later
-    // bounces of finish_paths) would have mostly always-records: it takes the line test of the tree's own records.
-    const float e0 = rtc::cluster_thr(thr0, m0, tv.entry_r), e1 = rtc::cluster_thr(thr1, m1, tv.entry_r);
-    bool common = false;
-    constexpr int kRecPerRow = (int)(32 * sizeof(CandT) / 16);   // float4 records per row of the warp's candidate columns
-    static_assert(kWfCand * kRecPerRow >= 128, "a chunk of 128 entry records fits the warp's candidate columns");
-    const int lane = threadIdx.x & 31;
-    char* warp_rows = reinterpret_cast<char*>(s_cand - lane);
-    auto rec_slot = [&](int i) -> float4* {
-        return reinterpret_cast<float4*>(warp_rows + (size_t)(i / kRecPerRow) * (kBlockThreads * sizeof(CandT)) + (size_t)(i % kRecPerRow) * 16);
-    };
-    f3 ow = rtc::mk(0.0f, 0.0f, 0.0f);
-    float rho = 0.0f;
-    if (tv.n_entry_pad >= 32) {
-        f3 lo = rtc::mk(inf, inf, inf), hi = rtc::mk(-inf, -inf, -inf);
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            if (L.alive[p]) {
-                lo = rtc::mk(fminf(lo.x, L.ox[p]), fminf(lo.y, L.oy[p]), fminf(lo.z, L.oz[p]));
-                hi = rtc::mk(fmaxf(hi.x, L.ox[p]), fmaxf(hi.y, L.oy[p]), fmaxf(hi.z, L.oz[p]));
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            lo = rtc::mk(fminf(lo.x, __shfl_xor_sync(kFull, lo.x, o)), fminf(lo.y, __shfl_xor_sync(kFull, lo.y, o)),
-                         fminf(lo.z, __shfl_xor_sync(kFull, lo.z, o)));
-            hi = rtc::mk(fmaxf(hi.x, __shfl_xor_sync(kFull, hi.x, o)), fmaxf(hi.y, __shfl_xor_sync(kFull, hi.y, o)),
-                         fmaxf(hi.z, __shfl_xor_sync(kFull, hi.z, o)));
-        }
-        ow = rtc::mk(0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z));
-        float r2 = 0.0f;
-        bool wide = false;   // |d|^2 outside the window of the unit direction (rtc::primary_arm)
-#pragma unroll
-        for (int p = 0; p < 2; ++p) {
-            if (L.alive[p]) {
-                const float dx = L.ox[p] - ow.x, dy = L.oy[p] - ow.y, dz = L.oz[p] - ow.z;
-                r2 = fmaxf(r2, fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
-                wide |= !(L.a[p] >= 9.094947017729282e-13f && L.a[p] <= 1099511627776.0f);
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) r2 = fmaxf(r2, __shfl_xor_sync(kFull, r2, o));
-        // >= max |o_i - ow|: the float evaluation of r2 is good to 2^-22 relative
-        rho = fmaf(sqrtf(r2), 1.0009765625f, 9.5367431640625e-07f * (fabsf(ow.x) + fabsf(ow.y) + fabsf(ow.z)));
-        // worth it only while the ball is small against the scene: entries within ~rho of it get always-records
-        common = !__any_sync(kFull, wide) && hi.x >= lo.x && rho <= 0.125f * tv.entry_r;
-    }
-    // pass 1: which entries either ray passes, one bit per entry — by the half-line test against this batch's records, or
-    // (spread-out batch) by the line test against the tree's own.  All lanes walk the same records: no divergence here.
-    // (Loops rolled and the five mask words addressed through selects: this kernel lives on its instruction footprint.)
-    uint32_t w_0 = 0u, w_1 = 0u, w_2 = 0u, w_3 = 0u, w_4 = 0u;   // rtt::kMaxEntry = 160 entries
-    auto put_word = [&](int w, uint32_t b) {
-        if (w == 0) w_0 = b; else if (w == 1) w_1 = b; else if (w == 2) w_2 = b; else if (w == 3) w_3 = b; else w_4 = b;
-    };
-    auto get_word = [&](int w) -> uint32_t { return w == 0 ? w_0 : w == 1 ? w_1 : w == 2 ? w_2 : w == 3 ? w_3 : w_4; };
-    const int n_words = (tv.n_entry_pad + 31) >> 5;
-    const float m_w = rtc::warp_origin_margin(ow, rho);
-    const int dead0 = L.alive[0] ? 0 : (int)0x80000000, dead1 = L.alive[1] ? 0 : (int)0x80000000;
-#pragma unroll 1
-    for (int w = 0; w < n_words; ++w) {
-        const int w0 = w * 32, wn = min(32, tv.n_entry_pad - w0);   // (a multiple of 4)
-        uint32_t bits = 0u;
-        if (common) {
-            if ((w & 3) == 0) {   // the next chunk of up to 128 records into the warp's candidate columns
-                const int cn = min(128, tv.n_entry_pad - w0);
-                __syncwarp();
-#pragma unroll 1
-                for (int i = lane; i < cn; i += 32) {
-                    const float4 g = tv.entry_rec[w0 + i];
-                    const float rad = tv.entry_rad[w0 + i];
-                    float r4[4];
-                    if (tv.entry_node[w0 + i] == 0xFFFFFFFFu) rtc::primary_record_pad(r4);
-                    else if (!(rad >= 0.0f) || g.w < -1.0e38f) { r4[0] = 0.0f; r4[1] = 0.0f; r4[2] = 0.0f; r4[3] = 1.0f; }
-                    else rtc::warp_origin_record(g.x, g.y, g.z, rad + m_w, ow, rho, r4);
-                    *rec_slot(i) = make_float4(r4[0], r4[1], r4[2], r4[3]);
-                }
-                __syncwarp();
-            }
-            const int base = w0 & 127;
-#pragma unroll 4
-            for (int i = 0; i < wn; ++i) {
-                const float4 r = *rec_slot(base + i);
-                const float2 h = __ffma2_rn(make_float2(r.x, r.x), L.ux[0],
-                                            __ffma2_rn(make_float2(r.y, r.y), L.uy[0],
-                                                       __ffma2_rn(make_float2(r.z, r.z), L.uz[0], make_float2(r.w, r.w))));
-                // passes unless both rays' sign bits are set (a dead ray's is forced)
-                const int both = (__float_as_int(h.x) | dead0) & (__float_as_int(h.y) | dead1);
-                bits = (bits >> 1) | ((uint32_t)~both & 0x80000000u);
-            }
-        } else {
-#pragma unroll 4
-            for (int i = 0; i < wn; ++i) {
-                const float2 g = broad_g2(tv.entry_rec[w0 + i], L, 0);
-                bits = (bits >> 1) | ((!(g.x < e0) || !(g.y < e1)) ? 0x80000000u : 0u);
-            }
-        }
-        put_word(w, bits >> (32 - wn));
-    }
-    __syncwarp();   // the candidate columns go back to the traversal
-    // pass 2: the nodes behind the set bits start the lane's stack (an empty slot of the padded list holds no node); the
-    // traversal runs whenever a lane's backlog fills.  ONE loop for all the words: the traversal below is inlined per call.
+    // the entry list, all lanes on the same record: the nodes either ray passes start the lane's stack
     {
-        int w = 0;
-        uint32_t bits = w_0;
-        for (;;) {
-            while (bits == 0u && w + 1 < n_words) bits = get_word(++w);
-            if (!__any_sync(kFull, bits != 0u)) break;
-            if (bits) {
-                const int e = w * 32 + __ffs((int)bits) - 1;
-                bits &= bits - 1u;
-                const uint32_t node = tv.entry_node[e];
-                if (node != 0xFFFFFFFFu) {
-                    s_stack[n_stack * kBlockThreads] = (unsigned short)node;
-                    ++n_stack;
-                }
+        const float e0 = rtc::cluster_thr(thr0, m0, tv.entry_r), e1 = rtc::cluster_thr(thr1, m1, tv.entry_r);
+#pragma unroll 1
+        for (int c0 = 0; c0 < tv.n_entry_pad; c0 += 4) {
+            float4 rec[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) rec[u] = tv.entry_rec[c0 + u];
+            const uint4 nodes4 = *reinterpret_cast<const uint4*>(tv.entry_node + c0);
+            const uint32_t node_of[4] = {nodes4.x, nodes4.y, nodes4.z, nodes4.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const float2 g = broad_g2(rec[u], L, 0);
+                const bool pass = !(g.x < e0) || !(g.y < e1);
+                s_stack[n_stack * kBlockThreads] = (unsigned short)node_of[u];   // slot n_stack is free; kept only if `pass`
+                n_stack += (pass && node_of[u] != 0xFFFFFFFFu) ? 1 : 0;
             }
-            // the stack keeps room for the growth of the traversal below the backlog (rt_api.cu)
+            // the stack keeps room for 4 more entries and for the growth of the traversal below them (rt_api.cu)
             if (__any_sync(kFull, n_stack > kTreeBacklog)) traverse();
         }
     }

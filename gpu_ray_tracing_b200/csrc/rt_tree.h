@@ -56,10 +56,8 @@ struct Tree {
     std::vector<float> entry_rec;            // n_entry_pad x (C.xyz, k)
     std::vector<uint32_t> entry_node;        // n_entry_pad
     std::vector<uint32_t> entry_slot;        // n_entry_pad: the child slot (node * kStride + k) the entry's record came from
-    std::vector<float> entry_rad;            // n_entry_pad: the entry's bounding radius (child_r of that slot); < 0 = no bound
-                                             // (the root, children under always-records, padding): always descended into
 
-    // Device image: [rec | link | node_r | entry_rec | entry_node | entry_rad | child_r | entry_slot], every part padded to 16 bytes.  The
+    // Device image: [rec | link | node_r | entry_rec | entry_node | child_r | entry_slot], every part padded to 16 bytes.  The
     // bounce kernel copies the image up to child_r (bounce_bytes) into shared memory.
     // offsets: rt_tree_layout.h, the one definition the kernels use as well
     ImageLayout layout() const { return image_layout(n_nodes, n_entry); }
@@ -78,7 +76,6 @@ struct Tree {
         memcpy(blob + off_r(), node_r.data(), node_r.size() * 4);
         memcpy(blob + off_entry_rec(), entry_rec.data(), entry_rec.size() * 4);
         memcpy(blob + off_entry_node(), entry_node.data(), entry_node.size() * 4);
-        memcpy(blob + layout().off_entry_rad, entry_rad.data(), entry_rad.size() * 4);
         memcpy(blob + off_child_r(), child_r.data(), child_r.size() * 4);
         memcpy(blob + off_entry_slot(), entry_slot.data(), entry_slot.size() * 4);
     }
@@ -336,14 +333,11 @@ inline bool build(const GpuSphere* s, uint32_t n, Tree& out) {
     out.entry_rec.assign((size_t)out.n_entry_pad * 4, 0.0f);
     out.entry_node.assign(out.n_entry_pad, kNone);
     out.entry_slot.assign(out.n_entry_pad, kNone);
-    out.entry_rad.assign(out.n_entry_pad, -1.0f);
     for (uint32_t j = 0; j < out.n_entry_pad; ++j) out.entry_rec[(size_t)j * 4 + 3] = kNever;
     for (uint32_t j = 0; j < out.n_entry; ++j) {
         memcpy(&out.entry_rec[(size_t)j * 4], frontier[j].rec.data(), 16);
         out.entry_node[j] = frontier[j].node;
         out.entry_slot[j] = frontier[j].slot;
-        if (frontier[j].slot != kNone && frontier[j].rec[3] != kAlways)
-            out.entry_rad[j] = out.child_r[(size_t)(frontier[j].slot / kStride) * kWide + frontier[j].slot % kStride];
         out.entry_r = std::max(out.entry_r, frontier[j].r);
     }
     return true;

@@ -6,8 +6,7 @@
 //   |node_r     n_nodes           f32      largest bounding radius among the node's children
 //   |entry_rec  n_entry_pad       float4   the entry list's records ...
 //   |entry_node n_entry_pad       u32      ... and the nodes they stand for
-//   |entry_rad  n_entry_pad       f32      ... and their bounding radii (< 0: always descend)  <- bounce_bytes ends here
-//   |child_r    n_nodes * kWide   f32      bounding radius per child slot (primary pass)
+//   |child_r    n_nodes * kWide   f32      bounding radius per child slot (primary pass)       <- bounce_bytes ends here
 //   |entry_slot n_entry_pad       u32]     child slot an entry's record came from (primary pass)
 // every part padded to 16 bytes.
 #pragma once
@@ -26,7 +25,7 @@ constexpr int kWide = 8;                // children per node
 constexpr int kStride = kWide + 1;      // record slots per node in the image: the odd stride spreads the nodes over the banks
 
 struct ImageLayout {
-    size_t off_link, off_r, off_entry_rec, off_entry_node, off_entry_rad, off_child_r, off_entry_slot, bytes;
+    size_t off_link, off_r, off_entry_rec, off_entry_node, off_child_r, off_entry_slot, bytes;
     uint32_t n_entry_pad;
 };
 
@@ -39,8 +38,7 @@ RTT_HD ImageLayout image_layout(uint32_t n_nodes, uint32_t n_entry) {
     l.off_r = l.off_link + pad16((size_t)n_nodes * kWide * 4);
     l.off_entry_rec = l.off_r + pad16((size_t)n_nodes * 4);
     l.off_entry_node = l.off_entry_rec + (size_t)l.n_entry_pad * 16;
-    l.off_entry_rad = l.off_entry_node + pad16((size_t)l.n_entry_pad * 4);
-    l.off_child_r = l.off_entry_rad + pad16((size_t)l.n_entry_pad * 4);
+    l.off_child_r = l.off_entry_node + pad16((size_t)l.n_entry_pad * 4);
     l.off_entry_slot = l.off_child_r + pad16((size_t)n_nodes * kWide * 4);
     l.bytes = l.off_entry_slot + pad16((size_t)l.n_entry_pad * 4);
     return l;
