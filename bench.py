@@ -615,11 +615,17 @@ def device_bytes(torch, ptr, nbytes):
 
 
 def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barrier, allreduce, args):
-    """One 7680x4320 / 1024-sphere frame per step, rows split over the ranks with rt_shard_rows, every rank's shading pass
-    storing its RGBA8 row block into rank 0's frame (fused gather over NVLink).  Protocol per frame f and rank i:
-    wait consumed >= f - 1 (the slot's previous frame has been seen whole) -> update -> release arrived[i] = f + 1;
-    rank 0 then waits for every arrived[*] >= f + 1 — the frame is whole in its memory — and releases consumed = f + 1.
-    Time = rank 0's device time for K whole frames.  Afterwards rank 0 renders the same frame alone (t1) and compares."""
+    """One 7680x4320 / 1024-sphere frame per step, dealt over the ranks as interleaved 16-row bands (rt_create_bands), the
+    RGBA8 rows gathered into rank 0's full frame over NVLink.  Two gathers are timed:
+      pipelined  the shading pass writes the rows locally, a copy engine scatters them into rank 0's frame on the copy
+                 stream while the next frame renders (rt_send_rgba8_async): the link carries frame f behind the kernels of
+                 f + 1 — the `ms` of this leg
+      fused      the shading pass stores the rows straight into rank 0's frame (rt_set_rgba8_target): no frame of latency,
+                 but the stores share NVLink with the kernel that issues them
+    Protocol per frame f and rank i, both ways: wait consumed >= f - 1 (the slot's previous frame has been seen whole) ->
+    deliver -> release arrived[i] = f + 1; rank 0 waits for every arrived[*] >= f + 1 — the frame is whole in its memory —
+    and releases consumed = f + 1.  Time = device time, max over ranks, for K whole frames.  Afterwards rank 0 renders the
+    same frames alone (t1) and compares."""
     K = max(5, min(args.steps, 20))
     frame8 = W8K * H8K * 4
     band_rows = 16
@@ -632,7 +638,7 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
     def cam8(f):
         return scenes.camera(W8K, H8K, 1, 1, random_seed=((f + 1) * 2654435761 % (1 << 24)) / float(1 << 24))
 
-    def frame(f):
+    def frame_fused(f):
         if f >= 2:
             rs.stream_wait(g.consumed(), 1, f - 1, 5000)
         rs.set_rgba8_target(g.slot(f))
@@ -642,20 +648,43 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
             rs.stream_wait(g.arrived(0), world, f + 1, 5000)
             rs.stream_signal(g.consumed(), f + 1)
 
-    for f in range(3):
-        frame(f)
-    rs.synchronize()
-    torch.cuda.synchronize()
-    barrier()
-    rs.timer_begin()
-    for f in range(3, 3 + K):
-        frame(f)
-    ms = rs.timer_end()
-    torch.cuda.synchronize()
-    barrier()
+    def frame_pipelined(f):
+        rs.update(cam8(f))                                   # (rt_set_rgba8_output: the rows land in a local buffer)
+        if f >= 2:
+            rs.copy_wait(g.consumed(), 1, f - 1, 5000)
+        rs.send_rgba8_async(g.slot(f))
+        rs.copy_signal(g.arrived(rank), f + 1)
+        if rank == 0:
+            rs.copy_wait(g.arrived(0), world, f + 1, 5000)
+            rs.copy_signal(g.consumed(), f + 1)
+
+    def timed(frame_fn, first, pipelined):
+        rs.set_rgba8_target(None)
+        rs.set_rgba8_output(pipelined)
+        for f in range(first, first + 3):
+            frame_fn(f)
+        rs.read_wait()
+        rs.synchronize()
+        torch.cuda.synchronize()
+        barrier()
+        rs.timer_begin()
+        for f in range(first + 3, first + 3 + K):
+            frame_fn(f)
+        if pipelined:
+            rs.read_wait()                                   # the copy stream has delivered (and rank 0 has seen) the last frame
+        ms_ = rs.timer_end()
+        torch.cuda.synchronize()
+        barrier()
+        got_ = device_bytes(torch, g.slot(first + 3 + K - 1), frame8).reshape(H8K, W8K, 4).copy() if rank == 0 else None
+        barrier()
+        return ms_, got_, first + 3 + K - 1
+
+    ms_p, got_p, last_p = timed(frame_pipelined, 0, True)
+    ms_f, got_f, last_f = timed(frame_fused, 3 + K, False)
     timed_out = rs.stream_wait_timed_out()
-    # without the gather: the row blocks stay where they are rendered
+    # without the gather: the rows stay where they are rendered
     rs.set_rgba8_target(None)
+    rs.set_rgba8_output(False)
     rs.update(cam8(0))
     rs.synchronize()
     barrier()
@@ -664,35 +693,39 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
         rs.update(cam8(f))
     ms_nog = rs.timer_end()
     barrier()
-    mx = allreduce([ms, ms_nog, float(timed_out)], dist.ReduceOp.MAX)
-    ms, ms_nog, timed_out = mx[0] / K, mx[1] / K, int(mx[2])
-    out = None
-    if rank == 0:
-        last = 3 + K - 1
-        got = device_bytes(torch, g.slot(last), frame8).reshape(H8K, W8K, 4).copy()
+    mx = allreduce([ms_p, ms_f, ms_nog, float(timed_out)], dist.ReduceOp.MAX)
+    ms_p, ms_f, ms_nog, timed_out = mx[0] / K, mx[1] / K, mx[2] / K, int(mx[3])
     rs.close()
     barrier()
+    out = None
     if rank == 0:
-        # the same frame on this GPU alone: t1, and the image the gathered one must equal
+        # the same frames on this GPU alone: t1, and the images the gathered ones must equal
         with rt.Renderer(W8K, H8K, device=local_rank) as r1:
             r1.set_scene(scene)
             r1.init()
             r1.set_rgba8_target(g.slot(0))
-            r1.update(cam8(last))
+            r1.update(cam8(last_p))
             r1.synchronize()
+            same_p = bool(np.array_equal(got_p, device_bytes(torch, g.slot(0), frame8).reshape(H8K, W8K, 4)))
+            r1.update(cam8(last_f))
+            r1.synchronize()
+            same_f = bool(np.array_equal(got_f, device_bytes(torch, g.slot(0), frame8).reshape(H8K, W8K, 4)))
             r1.timer_begin()
             for f in range(K):
-                r1.update(cam8(last))
+                r1.update(cam8(last_f))
             t1 = r1.timer_end() / K
-            want = device_bytes(torch, g.slot(0), frame8).reshape(H8K, W8K, 4)
-            identical = bool(np.array_equal(got, want))
+        inbound = (world - 1) / world * frame8
         out = {"workload": f"one {W8K}x{H8K} frame / {N_SPHERES} spheres / depth 1 per step, interleaved {band_rows}-row bands dealt over "
-                           f"{world} rank(s) (rt_create_bands), RGBA8 rows stored into rank 0's frame by the shading pass over NVLink, "
-                           "arrived / consumed flags per frame",
-               "ms": ms, "mrays_s": W8K * H8K / ms / 1e3, "ms_without_gather": ms_nog,
-               "t1_ms_same_run": t1, "speedup_vs_1": t1 / ms, "speedup_vs_1_without_gather": t1 / ms_nog,
-               "rank0_ingress_gbs": (world - 1) / world * frame8 / (ms * 1e-3) / 1e9 if world > 1 else 0.0,
-               "identical_to_single_gpu_frame": identical, "frames": K, "waits_timed_out": timed_out}
+                           f"{world} rank(s) (rt_create_bands), RGBA8 rows gathered into rank 0's frame over NVLink, arrived / consumed "
+                           "flags per frame; `ms` = the pipelined gather (copy engines behind the next frame), `fused` = stores out of "
+                           "the shading pass",
+               "ms": ms_p, "mrays_s": W8K * H8K / ms_p / 1e3, "t1_ms_same_run": t1, "speedup_vs_1": t1 / ms_p,
+               "rank0_ingress_gbs": inbound / (ms_p * 1e-3) / 1e9 if world > 1 else 0.0, "nvlink_ingress_peak_gbs": 770.0,
+               "fused": {"ms": ms_f, "speedup_vs_1": t1 / ms_f, "rank0_ingress_gbs": inbound / (ms_f * 1e-3) / 1e9 if world > 1 else 0.0,
+                         "identical_to_single_gpu_frame": same_f},
+               "ms_without_gather": ms_nog, "speedup_vs_1_without_gather": t1 / ms_nog,
+               "link_floor_ms": inbound / 770e9 * 1e3,
+               "identical_to_single_gpu_frame": same_p, "frames": K, "waits_timed_out": timed_out}
     barrier()
     return out
 

@@ -133,6 +133,9 @@ _SIGNATURES = {
     "rt_stream_signal": (C.c_int, [_P, _P, C.c_uint32]),
     "rt_stream_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rt_stream_wait_timed_out": (C.c_int, [_P, C.POINTER(C.c_uint32)]),
+    "rt_send_rgba8_async": (C.c_int, [_P, _P]),
+    "rt_copy_signal": (C.c_int, [_P, _P, C.c_uint32]),
+    "rt_copy_wait": (C.c_int, [_P, _P, C.c_uint32, C.c_uint32, C.c_uint32]),
     "rt_set_precision": (C.c_int, [_P, C.c_int]),
     "rt_tree_build_ms": (C.c_int, [_P, C.POINTER(C.c_double)]),
     "rt_device_alloc": (C.c_int, [C.c_int, C.c_uint64, C.POINTER(_P)]),
@@ -437,6 +440,17 @@ class Renderer:
 
     def stream_wait(self, device_flags: int, n: int, value: int, timeout_ms: int = 2000):
         _check(lib().rt_stream_wait(self._h, C.c_void_p(device_flags), n, value, timeout_ms))
+
+    def send_rgba8_async(self, device_full_rgba8: int):
+        """Pipelined gather: the window's RGBA8 rows into their places in a full image (this GPU's memory or a peer's) by a
+        copy engine on the copy stream; pair with copy_signal / copy_wait and read_wait()."""
+        _check(lib().rt_send_rgba8_async(self._h, C.c_void_p(device_full_rgba8)))
+
+    def copy_signal(self, device_flag: int, value: int):
+        _check(lib().rt_copy_signal(self._h, C.c_void_p(device_flag), value))
+
+    def copy_wait(self, device_flags: int, n: int, value: int, timeout_ms: int = 2000):
+        _check(lib().rt_copy_wait(self._h, C.c_void_p(device_flags), n, value, timeout_ms))
 
     def stream_wait_timed_out(self) -> int:
         v = C.c_uint32(0)

@@ -409,6 +409,75 @@ int rt_read_rgba8(RtRenderer* r, uint8_t* host) {
     return RT_OK;
 }
 
+// The window's rows (window order, `elem` bytes per texel) to their places in a full image: one copy for a contiguous
+// window, a strided 2-D copy over the whole bands (+ one for a short last band) for an interleaved one.
+static cudaError_t scatter_window(const RtRenderer* r, void* full, const void* src, size_t elem, cudaStream_t stream) {
+    const size_t row_bytes = (size_t)r->width * elem;
+    unsigned char* dst = static_cast<unsigned char*>(full);
+    const unsigned char* from = static_cast<const unsigned char*>(src);
+    if (r->band_rows == 0)
+        return cudaMemcpyAsync(dst + (size_t)r->row_begin * row_bytes, from, (size_t)r->row_count * row_bytes, cudaMemcpyDefault, stream);
+    const size_t band_bytes = (size_t)r->band_rows * row_bytes;
+    const uint32_t whole = r->row_count / r->band_rows, rest = r->row_count % r->band_rows;
+    cudaError_t e = cudaSuccess;
+    if (whole)
+        e = cudaMemcpy2DAsync(dst + (size_t)r->row_begin * row_bytes, (size_t)r->band_stride * row_bytes, from, band_bytes, band_bytes,
+                              whole, cudaMemcpyDefault, stream);
+    if (e == cudaSuccess && rest)
+        e = cudaMemcpyAsync(dst + ((size_t)r->row_begin + (size_t)whole * r->band_stride) * row_bytes, from + (size_t)whole * band_bytes,
+                            (size_t)rest * row_bytes, cudaMemcpyDefault, stream);
+    return e;
+}
+
+// Common part of the asynchronous reads: the frame as it stands into device slot b (unless a fused update wrote it
+// already), the copy stream ordered behind it.  Returns the slot's buffer.
+static int stage_async_slot(RtRenderer* r, uchar4** dev_out, int* slot_out) {
+    if (!r->rgba8_alt) RT_CUDA(cudaMalloc(&r->rgba8_alt, r->n_texels * sizeof(uchar4)));
+    const int b = (int)(r->async_reads & 1u);
+    uchar4* dev = b ? r->rgba8_alt : r->rgba8;
+    // slot b was last used two reads ago: its copy must have left the buffer before it is overwritten
+    if (!r->rgba8_fresh) {   // (a fused update has already written slot b, after the same wait)
+        if (r->async_reads >= 2) RT_CUDA(cudaStreamWaitEvent(r->stream, r->ev_copied[b], 0));
+        RT_CUDA(rtk::launch_quantize(r->accum, dev, r->n_texels, r->stream));
+        r->launches += 1;
+    }
+    r->rgba8_fresh = false;
+    RT_CUDA(cudaEventRecord(r->ev_quantized[b], r->stream));
+    RT_CUDA(cudaStreamWaitEvent(r->copy_stream, r->ev_quantized[b], 0));
+    *dev_out = dev;
+    *slot_out = b;
+    return RT_OK;
+}
+
+int rt_send_rgba8_async(RtRenderer* r, void* device_full_rgba8) {
+    RT_CHECK_HANDLE(r);
+    if (!device_full_rgba8) return fail(RT_ERR_INVALID_ARG, "destination is null");
+    uchar4* dev = nullptr;
+    int b = 0;
+    int rc = stage_async_slot(r, &dev, &b);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(scatter_window(r, device_full_rgba8, dev, sizeof(uchar4), r->copy_stream));
+    RT_CUDA(cudaEventRecord(r->ev_copied[b], r->copy_stream));
+    r->async_reads += 1;
+    return RT_OK;
+}
+
+int rt_copy_signal(RtRenderer* r, void* device_flag, uint32_t value) {
+    RT_CHECK_HANDLE(r);
+    if (!device_flag) return fail(RT_ERR_INVALID_ARG, "flag is null");
+    RT_CUDA(rtk::launch_signal(device_flag, value, r->copy_stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
+int rt_copy_wait(RtRenderer* r, const void* device_flags, uint32_t n, uint32_t value, uint32_t timeout_ms) {
+    RT_CHECK_HANDLE(r);
+    if (!device_flags || n == 0) return fail(RT_ERR_INVALID_ARG, "no flags");
+    RT_CUDA(rtk::launch_wait_flags(device_flags, n, value, timeout_ms ? timeout_ms : 1u, r->wait_status, r->copy_stream));
+    r->launches += 1;
+    return RT_OK;
+}
+
 int rt_read_rgba8_async(RtRenderer* r, uint8_t* host) {
     RT_CHECK_HANDLE(r);
     if (!host) return fail(RT_ERR_INVALID_ARG, "host buffer is null");

@@ -195,6 +195,16 @@ RT_API int rt_set_rgba8_target(RtRenderer* r, void* device_rgba8);
 RT_API int rt_stream_signal(RtRenderer* r, void* device_flag, uint32_t value);
 RT_API int rt_stream_wait(RtRenderer* r, const void* device_flags, uint32_t n, uint32_t value, uint32_t timeout_ms);
 RT_API int rt_stream_wait_timed_out(RtRenderer* r, uint32_t* count);   /* synchronises; number of waits that gave up */
+/* The PIPELINED gather: rt_send_rgba8_async puts the window's RGBA8 rows (as rt_read_rgba8_async would read them: the frame
+ * as it stands after the work queued so far, from one of two device buffers) into their places in a FULL width x height
+ * image at device_full_rgba8 — this GPU's memory or a peer's — with a copy engine on the renderer's copy stream: one copy
+ * for a contiguous window, one strided 2-D copy for an interleaved one.  The next update overlaps the transfer, so the
+ * link carries frame f while the SMs render f + 1 (one frame of latency; the fused target above has none but its stores
+ * share the link with the kernel that issues them).  rt_copy_signal / rt_copy_wait are rt_stream_signal / rt_stream_wait
+ * on that copy stream: a flag behind the transfer, and back-pressure before it.  rt_read_wait drains the copy stream. */
+RT_API int rt_send_rgba8_async(RtRenderer* r, void* device_full_rgba8);
+RT_API int rt_copy_signal(RtRenderer* r, void* device_flag, uint32_t value);
+RT_API int rt_copy_wait(RtRenderer* r, const void* device_flags, uint32_t n, uint32_t value, uint32_t timeout_ms);
 /* Device buffers that other processes can write into.  A multi-process run (one process per GPU) keeps its gather
  * target in one process (rt_device_alloc + rt_ipc_export), the others map it (rt_ipc_open, peer access enabled
  * lazily) and hand the mapped address to rt_read_rgba8_async, whose destination may be pinned host memory or device

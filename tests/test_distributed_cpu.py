@@ -27,6 +27,10 @@ def _worker(rank, world, port, out_dir):
     b, c = sharding.rows_for_rank(H, rank, world)
     block, _ = ol.oracle_update(cam, scene, W, H, row_begin=b, row_count=c)
     full = sharding.gather_row_blocks(dist, torch.from_numpy(block), H, rank, world)
+    # bands plan: 8-row bands dealt round-robin; the oracle renders each band of this rank as a row window
+    mine_rows = sharding.band_rows_for_rank(H, 8, rank, world)
+    parts = [ol.oracle_update(cam, scene, W, H, row_begin=int(r0), row_count=int(min(8, H - r0)))[0] for r0 in mine_rows[::8]]
+    banded = sharding.gather_bands(dist, torch.from_numpy(np.concatenate(parts)), H, 8, rank, world)
     # frames plan: 5 frames, frame k = random_seed k/8
     mine = sharding.frames_for_rank(5, rank, world)
     frames = {k: ol.oracle_update(scenes.camera(W, H, max_depth=2, spp=1, random_seed=k / 8.0), scene, W, H)[0] for k in mine}
@@ -34,6 +38,7 @@ def _worker(rank, world, port, out_dir):
     dist.all_gather_object(gathered, {k: v.tobytes() for k, v in frames.items()})
     if rank == 0:
         np.save(os.path.join(out_dir, "rows.npy"), full.numpy())
+        np.save(os.path.join(out_dir, "bands.npy"), banded.numpy())
         merged = {}
         for g in gathered:
             merged.update(g)
@@ -54,6 +59,8 @@ def test_two_rank_sharding_reassembles_the_single_process_result(tmp_path):
     want, _ = ol.oracle_update(cam, scene, W, H)
     got = np.load(os.path.join(tmp_path, "rows.npy"))
     assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    got = np.load(os.path.join(tmp_path, "bands.npy"))
+    assert got.shape == want.shape and np.array_equal(got.view(np.uint32), want.view(np.uint32))
     frames = np.load(os.path.join(tmp_path, "frames.npy"))
     for k in range(5):
         ref, _ = ol.oracle_update(scenes.camera(W, H, max_depth=2, spp=1, random_seed=k / 8.0), scene, W, H)
@@ -69,3 +76,5 @@ def test_plans_cover_everything_once():
         rows = [sharding.rows_for_rank(4320, r, world) for r in range(world)]
         assert rows[0][0] == 0 and sum(c for _, c in rows) == 4320
         assert all(rows[i][0] + rows[i][1] == rows[i + 1][0] for i in range(world - 1))
+        banded = np.concatenate([sharding.band_rows_for_rank(4320, 16, r, world) for r in range(world)])
+        assert sorted(banded.tolist()) == list(range(4320))

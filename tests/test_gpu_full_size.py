@@ -309,9 +309,10 @@ def test_interleaved_band_shards_equal_the_whole_image(depth):
         r.init()
         r.update(cam)
         whole, rays_whole = r.read_accum(), r.rays_traced()
-    full = rt.device_alloc(0, W * H * 4)
+    full = rt.device_alloc(0, 2 * W * H * 4 + 256)
+    full2 = full + W * H * 4
     try:
-        device_fill(full, 0, W * H * 4)
+        device_fill(full, 0, 2 * W * H * 4 + 256)
         got = np.zeros_like(whole)
         rays = 0
         rows_seen = []
@@ -326,11 +327,18 @@ def test_interleaved_band_shards_equal_the_whole_image(depth):
                 got[rows] = r.read_accum()
                 rays += r.rays_traced()
                 rows_seen.append(rows)
+                # the pipelined gather: the same rows scattered into a second full image by a copy engine, flag behind
+                r.send_rgba8_async(full2)
+                r.copy_signal(full2 + W * H * 4, idx + 1)
+                r.copy_wait(full2 + W * H * 4, 1, idx + 1, 1000)
+                r.read_wait()
+                assert r.stream_wait_timed_out() == 0
         assert sorted(np.concatenate(rows_seen).tolist()) == list(range(H))
         assert rays == rays_whole
         assert np.array_equal(got.view(np.uint32), whole.view(np.uint32))
         if depth == 1:
             assert np.array_equal(device_bytes(full, W * H * 4).reshape(H, W, 4), ol.quantize(whole))
+        assert np.array_equal(device_bytes(full2, W * H * 4).reshape(H, W, 4), ol.quantize(whole))
     finally:
         rt.device_free(0, full)
     have = rt.device_count()
