@@ -649,18 +649,25 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
             rs.stream_signal(g.consumed(), f + 1)
 
     def frame_pipelined(f):
+        if rank == 0:
+            # the owner's rows need no link: stored in place by the shading pass; its copy stream only keeps the books
+            if f >= 2:
+                rs.stream_wait(g.consumed(), 1, f - 1, 5000)
+            rs.set_rgba8_target(g.slot(f))
+            rs.update(cam8(f))
+            rs.stream_signal(g.arrived(0), f + 1)
+            rs.copy_wait(g.arrived(0), world, f + 1, 5000)
+            rs.copy_signal(g.consumed(), f + 1)
+            return
         rs.update(cam8(f))                                   # (rt_set_rgba8_output: the rows land in a local buffer)
         if f >= 2:
             rs.copy_wait(g.consumed(), 1, f - 1, 5000)
         rs.send_rgba8_async(g.slot(f))
         rs.copy_signal(g.arrived(rank), f + 1)
-        if rank == 0:
-            rs.copy_wait(g.arrived(0), world, f + 1, 5000)
-            rs.copy_signal(g.consumed(), f + 1)
 
     def timed(frame_fn, first, pipelined):
         rs.set_rgba8_target(None)
-        rs.set_rgba8_output(pipelined)
+        rs.set_rgba8_output(pipelined and rank != 0)
         for f in range(first, first + 3):
             frame_fn(f)
         rs.read_wait()
