@@ -156,6 +156,7 @@ _SIGNATURES = {
     "rt_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "rt_window": (C.c_int, [_P] + [C.POINTER(C.c_uint32)] * 4),
     "rt_set_kernel_variant": (C.c_int, [_P, C.c_int]),
+    "rt_update_static": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, _P, _P]),
     "rt_render": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
     "rt_render_frames": (C.c_int, [C.c_int, _P, C.c_uint32, C.POINTER(SceneCamera), C.c_uint32, C.c_uint32, C.c_uint32, _P]),
     "rt_shard_rows": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
@@ -607,6 +608,18 @@ class ComputeShaderNode:
             self.renderer.init()
         elif self.state is ComputeShaderState.Update:
             self.renderer.update(camera)
+
+
+RT_STATIC_MAX_SPHERES = 4096
+
+
+def update_static(device: int, device_spheres: int, n_spheres: int, camera: SceneCamera, width: int, height: int,
+                  device_accum: int, stream: int = 0) -> None:
+    """rt_update_static: one `update` over a whole image with DEVICE pointers for spheres and accumulation image, no
+    renderer handle and no allocation (scratch in a static device array; at most RT_STATIC_MAX_SPHERES spheres; calls that
+    overlap on one GPU race on that array).  Asynchronous on `stream` (0 = default stream)."""
+    _check(lib().rt_update_static(device, C.c_void_p(device_spheres), n_spheres, C.byref(camera), width, height,
+                                  C.c_void_p(device_accum), C.c_void_p(stream)))
 
 
 def render(scene: SphereCollection, camera: SceneCamera, width: int, height: int, samples: int = 1,

@@ -688,6 +688,25 @@ int rt_set_kernel_variant(RtRenderer* r, int variant) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// rt_update_static: one `update` without a renderer handle and without any allocation (include/rt_abi.h).  Calls no
+// cudaMalloc / cudaFree / allocating library routine: the kernel's scratch is a file-scope device array in rt_kernels.cu.
+// ---------------------------------------------------------------------------------------------
+int rt_update_static(int device, const GpuSphere* device_spheres, uint32_t n_spheres, const SceneCamera* camera,
+                     uint32_t width, uint32_t height, float* device_accum_rgba32f, void* cuda_stream) {
+    if (!camera || !device_accum_rgba32f) return fail(RT_ERR_INVALID_ARG, "null camera or accumulation image");
+    if (n_spheres > 0 && !device_spheres) return fail(RT_ERR_INVALID_ARG, "spheres is null");
+    if (n_spheres > RT_STATIC_MAX_SPHERES)
+        return fail(RT_ERR_INVALID_ARG, "rt_update_static: %u spheres exceed the static scratch's maximum of %u (use a renderer handle)",
+                    n_spheres, (unsigned)RT_STATIC_MAX_SPHERES);
+    if (width == 0 || height == 0 || width > (1u << 20) || height > (1u << 20)) return fail(RT_ERR_INVALID_ARG, "image %ux%u", width, height);
+    if (device < 0 || device >= 64) return fail(RT_ERR_INVALID_ARG, "device %d out of range", device);
+    RT_CUDA(cudaSetDevice(device));
+    RT_CUDA(rtk::launch_update_static(device, device_spheres, n_spheres, *camera, width, height,
+                                      reinterpret_cast<float4*>(device_accum_rgba32f), static_cast<cudaStream_t>(cuda_stream)));
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Headless one-shot entries
 // ---------------------------------------------------------------------------------------------
 int rt_render(int device, const GpuSphere* spheres, uint32_t count, const SceneCamera* camera, uint32_t width,

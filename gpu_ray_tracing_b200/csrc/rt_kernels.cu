@@ -2177,6 +2177,80 @@ cudaError_t launch_wait_flags(const void* flags, uint32_t n, uint32_t value, uin
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// rt_update_static (include/rt_abi.h): `update` for callers that may not allocate — code under CUDA graph capture, tight
+// serving loops.  It is update_resident_kernel (variant 2: every sphere's broad-phase record resident in shared memory, any
+// max_depth in the kernel's own bounce loop) with its scratch — the tile ticket, the ray / test counters and the
+// per-sphere records prep_geometry_kernel derives from the caller's sphere buffer — in ONE file-scope device array
+// instead of cudaMalloc'ed buffers of a renderer handle.  Every GPU that loads the library holds the array (66,048
+// bytes) until the process exits; every call on a device shares it.
+//   [0, 8)    tile ticket (2 x u32)   cleared per call (must start at zero)
+//   [16, 32)  rays, exact tests (2 x u64)   cleared per call
+//   [256, ..) float4 records for kStaticMaxSpheres + padding + prefetch tail, rewritten per call up to the length the
+//             kernel reads (prep_geometry_kernel writes the padding and the tail as never-candidates)
+// In host code the array's NAME is a host-side stand-in, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device with that device current, and that pointer is what the kernels get.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kStaticGeomOffset = 256;
+constexpr size_t kStaticScratchBytes = kStaticGeomOffset + (size_t)(kStaticMaxSpheres + kGeomPad + kGeomTail) * sizeof(float4);
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+static_assert(kStaticMaxSpheres <= kResidentMaxSpheres, "the records must fit the resident kernel's shared memory");
+
+constexpr int kStaticMaxDevices = 64;
+static unsigned char* g_static_ptr[kStaticMaxDevices];   // device address of g_static_scratch, per device
+static int g_static_sms[kStaticMaxDevices];
+
+// Set-up of the calling device (current): symbol address, SM count, shared-memory opt-in of the kernel.  No allocation.
+static cudaError_t static_setup(int device) {
+    if (g_static_ptr[device] != nullptr) return cudaSuccess;
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess) return e;
+    int sms = 0;
+    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) return e;
+    e = set_smem(update_resident_kernel, (kResidentMaxSpheres + kGeomTail) * sizeof(float4));
+    if (e != cudaSuccess) return e;
+    g_static_sms[device] = sms;
+    g_static_ptr[device] = static_cast<unsigned char*>(ptr);
+    return cudaSuccess;
+}
+
+cudaError_t launch_update_static(int device, const GpuSphere* device_spheres, uint32_t n_spheres, const SceneCamera& cam,
+                                 uint32_t width, uint32_t height, float4* device_accum, cudaStream_t stream) {
+    if (device < 0 || device >= kStaticMaxDevices || n_spheres > kStaticMaxSpheres) return cudaErrorInvalidValue;
+    cudaError_t e = static_setup(device);
+    if (e != cudaSuccess) return e;
+    unsigned char* scratch = g_static_ptr[device];
+    UpdateParams p;
+    memset(&p, 0, sizeof(p));   // no primary pass, no wavefront, no tree, no RGBA8 output: null pointers and zero counts
+    p.cam = cam;
+    p.accum = device_accum;
+    p.geom = reinterpret_cast<const float4*>(scratch + kStaticGeomOffset);
+    p.spheres = device_spheres;
+    p.n_spheres = n_spheres;
+    p.width = width; p.height = height;
+    p.row_begin = 0; p.row_count = height;
+    p.tiles_x = (width + kWarpTileW - 1) / kWarpTileW;
+    p.n_tiles = p.tiles_x * ((height + kWarpTileH - 1) / kWarpTileH);
+    p.tile_counter = reinterpret_cast<unsigned int*>(scratch);
+    p.counters = reinterpret_cast<unsigned long long*>(scratch + 16);
+    // the array keeps the last call's contents: ticket and counters must start at zero
+    e = cudaMemsetAsync(scratch, 0, 32, stream);
+    if (e != cudaSuccess) return e;
+    const uint32_t n_pad = (n_spheres + kGeomPad - 1) / kGeomPad * kGeomPad;
+    prep_geometry_kernel<<<(n_pad + kGeomTail + 255) / 256, 256, 0, stream>>>(device_spheres, reinterpret_cast<float4*>(scratch + kStaticGeomOffset),
+                                                                               n_spheres, n_pad + kGeomTail);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    uint32_t blocks = (p.n_tiles + 7) / 8;
+    const uint32_t resident = (uint32_t)g_static_sms[device] * 2u;
+    if (blocks > resident) blocks = resident;
+    if (blocks == 0) blocks = 1;
+    update_resident_kernel<<<blocks, kBlockThreads, (n_pad + kGeomTail) * sizeof(float4), stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream) {
     const uint32_t n_pad = (n + kGeomPad - 1) / kGeomPad * kGeomPad + kGeomTail;
     prep_geometry_kernel<<<(n_pad + 255) / 256, 256, 0, stream>>>(spheres, geom, n, n_pad);

@@ -109,6 +109,10 @@ cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texel
 cudaError_t launch_signal(void* flag, uint32_t value, cudaStream_t stream);
 cudaError_t launch_wait_flags(const void* flags, uint32_t n, uint32_t value, uint32_t timeout_ms, unsigned int* status,
                               cudaStream_t stream);
+// rt_update_static: variant 2 with its scratch in a file-scope device array (rt_kernels.cu); allocates nothing
+constexpr uint32_t kStaticMaxSpheres = 4096;   // == RT_STATIC_MAX_SPHERES of include/rt_abi.h
+cudaError_t launch_update_static(int device, const GpuSphere* device_spheres, uint32_t n_spheres, const SceneCamera& cam,
+                                 uint32_t width, uint32_t height, float4* device_accum, cudaStream_t stream);
 cudaError_t configure_kernels();   // one-off cudaFuncSetAttribute calls
 
 }  // namespace rtk

@@ -275,6 +275,27 @@ enum { RT_PRECISION_EXACT = 0, RT_PRECISION_FAST_SHADING = 1, RT_PRECISION_FAST_
 RT_API int rt_set_precision(RtRenderer* r, int precision);
 
 /* ---------------------------------------------------------------------------------------
+ * `update` for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ *
+ * One `update` dispatch (compute_shader.wgsl:333-364) over a whole width x height image, in place, without a renderer
+ * handle: the caller passes DEVICE pointers for the input (n_spheres GpuSphere structs as the reference lays them out)
+ * and for the input / output accumulation image (width*height float4 texels (mean.rgb, n); zero it for `init`), the
+ * 176-byte camera uniform by host pointer (read during the call) and the CUDA stream to enqueue on (NULL = the default
+ * stream).  Asynchronous on that stream.  The call performs no cudaMalloc, cudaFree or other allocating routine: the
+ * kernel's scratch (per-sphere broad-phase records, tile ticket, counters) lives in a file-scope device array of 66,048
+ * bytes that every GPU which loads the library holds until the process exits.
+ * LIMIT: n_spheres <= RT_STATIC_MAX_SPHERES (4096); more is rejected with RT_ERR_INVALID_ARG and a message.
+ * SHARING: every call on a device uses the same array, which keeps the previous call's contents (what must start at zero is
+ * cleared by each call).  Calls that OVERLAP on one GPU — different streams, or different threads — race on it: serialise
+ * them (one stream, or events).  Calls on different GPUs are independent.
+ * The kernel is the resident-scene variant (rt_set_kernel_variant 2: every sphere's record in shared memory, any max_depth
+ * in the kernel's own bounce loop); results are bit-identical to rt_update's. */
+#define RT_STATIC_MAX_SPHERES 4096u
+RT_API int rt_update_static(int device, const GpuSphere* device_spheres, uint32_t n_spheres, const SceneCamera* camera,
+                            uint32_t width, uint32_t height, float* device_accum_rgba32f, void* cuda_stream);
+
+/* ---------------------------------------------------------------------------------------
  * Headless one-shot entries (new surface asked for by the port target; the reference has
  * only the windowed app, src/lib.rs:28-58)
  * ------------------------------------------------------------------------------------- */
