@@ -560,6 +560,10 @@ def run_ours(args):
                 "cascade; the other N - that many pairs are discarded by conservative tests with identical results",
         "from_capture": capture,
     }
+    if capture and capture.get("executed_fp32_flop_per_launch"):
+        executed["fp32_tflops"] = capture["executed_fp32_flop_per_launch"] / (kernel_ms * 1e-3) / 1e12
+        executed["fp32_frac_of_peak"] = executed["fp32_tflops"] / peak_tf
+        executed["fp32_note"] = "captured FADD + FMUL + 2 x FFMA thread instructions / kernel_ms of this run / FFMA peak of this run: the kernel is issue-bound, not FMA-bound"
     if capture and capture.get("warp_instructions_per_launch") and clocks and clocks.get("sm_mhz"):
         slots = sms * 4 * clocks["sm_mhz"] * 1e6 * kernel_ms * 1e-3
         executed["issue_slot_frac"] = capture["warp_instructions_per_launch"] / slots
