@@ -1032,6 +1032,15 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
         if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
         tile = __shfl_sync(kFull, tile, 0);
         if (tile >= n_tiles) break;
+#if RT_PRIM_TILE_ORDER == 1
+        tile = n_tiles - 1u - tile;   // bottom-up: see RT_PRIM_TILE_ORDER
+#elif RT_PRIM_TILE_ORDER == 2
+        {   // middle-out by tile rows: mid, mid - 1, mid + 1, mid - 2, ... (a bijection of the rows for any count)
+            const uint32_t k = tile / tiles_x, mid = (n_tiles / tiles_x) / 2u;
+            const uint32_t row_of = (k & 1u) ? mid - (k + 1u) / 2u : mid + k / 2u;
+            tile = row_of * tiles_x + tile % tiles_x;
+        }
+#endif
         const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
         const int row0 = (int)((tile / tiles_x) * kPrimTileH);
         PrimLanes L;
@@ -1211,19 +1220,38 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 // and let other warps' appends fall between.)  Ray 0's outcome waits in `s_park`, 12 words of the thread's idle candidate
 // column (its OWN column: a wider view of the area would land in other warps' cells, which are in use), while the
 // rolled loop resolves ray 1.
+// Per-thread columns of the bounce kernels (node stack, candidate codes): row k of thread t.  Plain layout: element
+// k * kBlockThreads + t — for 16-bit entries lanes 2j and 2j + 1 share a bank, and once their rows differ (divergent
+// stack depths) every access is a 2-way conflict (16 % of the shared-memory wavefronts of a bounce launch).  Paired
+// layout (RT_WF_PAIR_ROWS): rows 2m and 2m + 1 of a thread share ONE 32-bit word, element (m * kBlockThreads + t) * 2 +
+// (k & 1), so lane t always hits bank t whatever its row.
+#ifndef RT_WF_PAIR_ROWS
+#define RT_WF_PAIR_ROWS 0
+#endif
+template <typename T>
+__device__ __forceinline__ int col_at(int k) {
+    if constexpr (sizeof(T) == 2 && RT_WF_PAIR_ROWS) return (k >> 1) * (2 * kBlockThreads) + (k & 1);
+    else return k * kBlockThreads;
+}
+template <typename T>
+__device__ __forceinline__ T* col_base(T* block_base) {
+    if constexpr (sizeof(T) == 2 && RT_WF_PAIR_ROWS) return block_base + 2 * threadIdx.x;
+    else return block_base + threadIdx.x;
+}
+
 template <typename CandT>
 __device__ __forceinline__ void park_word(CandT* s_cand, int k, uint32_t v) {
     if constexpr (sizeof(CandT) == 4) {
         s_cand[k * kBlockThreads] = v;
     } else {
-        s_cand[(2 * k) * kBlockThreads] = (CandT)(v & 0xffffu);
-        s_cand[(2 * k + 1) * kBlockThreads] = (CandT)(v >> 16);
+        s_cand[col_at<CandT>(2 * k)] = (CandT)(v & 0xffffu);
+        s_cand[col_at<CandT>(2 * k + 1)] = (CandT)(v >> 16);
     }
 }
 template <typename CandT>
 __device__ __forceinline__ uint32_t parked_word(const CandT* s_cand, int k) {
     if constexpr (sizeof(CandT) == 4) return s_cand[k * kBlockThreads];
-    else return (uint32_t)s_cand[(2 * k) * kBlockThreads] | ((uint32_t)s_cand[(2 * k + 1) * kBlockThreads] << 16);
+    else return (uint32_t)s_cand[col_at<CandT>(2 * k)] | ((uint32_t)s_cand[col_at<CandT>(2 * k + 1)] << 16);
 }
 template <int F, typename CandT>
 __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count, uint32_t j0,
@@ -1340,7 +1368,7 @@ __device__ __forceinline__ void drain_candidates(const CandT* __restrict__ s_can
     for (int e = 0; __any_sync(kFull, e < n_cand); ++e) {
         if (e < n_cand) {
             constexpr int kRayBit = (int)sizeof(CandT) * 8 - 1;   // top bit: the thread's second ray
-            const uint32_t code = (uint32_t)s_cand[e * kBlockThreads];
+            const uint32_t code = (uint32_t)s_cand[col_at<CandT>(e)];
             const int idx = (int)(code & ((1u << kRayBit) - 1u));
             const bool second = (code >> kRayBit) != 0u;
             const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
@@ -1379,7 +1407,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
     auto traverse = [&]() {   // empties every lane's stack
     while (__any_sync(kFull, n_stack > 0)) {
         if (n_stack > 0) {
-            const int node = (int)s_stack[(--n_stack) * kBlockThreads];
+            const int node = (int)s_stack[col_at<unsigned short>(--n_stack)];
             const bool leaf = node >= tv.first_leaf;
             float t0 = thr0, t1 = thr1;
             if (!leaf) {
@@ -1402,7 +1430,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
                     pass &= pass - 1u;
                     const unsigned idx = link[bit >> 1];
                     if (idx != 0xFFFFFFFFu) {   // (an empty slot can only get here through a NaN threshold)
-                        s_cand[n_cand * kBlockThreads] = (CandT)(idx | ((unsigned)(bit & 1) << ((int)sizeof(CandT) * 8 - 1)));
+                        s_cand[col_at<CandT>(n_cand)] = (CandT)(idx | ((unsigned)(bit & 1) << ((int)sizeof(CandT) * 8 - 1)));
                         ++n_cand;
                     }
                 }
@@ -1413,7 +1441,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
                     pass &= pass - 1u;
                     const unsigned child = link[bit >> 1];
                     if (child != 0xFFFFFFFFu) {
-                        s_stack[n_stack * kBlockThreads] = (unsigned short)child;
+                        s_stack[col_at<unsigned short>(n_stack)] = (unsigned short)child;
                         ++n_stack;
                     }
                 }
@@ -1437,7 +1465,7 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
             for (int u = 0; u < 4; ++u) {
                 const float2 g = broad_g2(rec[u], L, 0);
                 const bool pass = !(g.x < e0) || !(g.y < e1);
-                s_stack[n_stack * kBlockThreads] = (unsigned short)node_of[u];   // slot n_stack is free; kept only if `pass`
+                s_stack[col_at<unsigned short>(n_stack)] = (unsigned short)node_of[u];   // slot n_stack is free; kept only if `pass`
                 n_stack += (pass && node_of[u] != 0xFFFFFFFFu) ? 1 : 0;
             }
             // the stack keeps room for 4 more entries and for the growth of the traversal below them (rt_api.cu)
@@ -1553,9 +1581,9 @@ __global__ void __launch_bounds__(kBlockThreads, 3) bounce_clustered_kernel(cons
     using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
     const uint32_t image_slots = kGlobal ? 0u : (P.cl_bytes + 15u) / 16u;
     // [kWfCand][kBlockThreads] candidate codes, then [cl_stack_cap][kBlockThreads] node numbers
-    CandT* s_cand = reinterpret_cast<CandT*>(s_dyn + image_slots) + threadIdx.x;
+    CandT* s_cand = col_base(reinterpret_cast<CandT*>(s_dyn + image_slots));
 
-    unsigned short* s_stack = reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads) + threadIdx.x;
+    unsigned short* s_stack = col_base(reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads));
     const int lane = threadIdx.x & 31;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) {
@@ -1612,8 +1640,8 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_tail_kernel(const __g
     __shared__ __align__(8) uint64_t s_bar;
     using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
     const uint32_t image_slots = kGlobal ? 0u : (P.cl_bytes + 15u) / 16u;
-    CandT* s_cand = reinterpret_cast<CandT*>(s_dyn + image_slots) + threadIdx.x;
-    unsigned short* s_stack = reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads) + threadIdx.x;
+    CandT* s_cand = col_base(reinterpret_cast<CandT*>(s_dyn + image_slots));
+    unsigned short* s_stack = col_base(reinterpret_cast<unsigned short*>(reinterpret_cast<CandT*>(s_dyn + image_slots) + kWfCand * kBlockThreads));
     const int lane = threadIdx.x & 31;
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     if constexpr (!kGlobal) {
@@ -1962,10 +1990,10 @@ static size_t bounce_smem_bytes() {
     return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
 }
 static size_t clustered_smem_bytes(uint32_t image_bytes, uint32_t stack_cap) {
-    return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(stack_cap + kWfCand) * kBlockThreads * sizeof(unsigned short);
+    return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(((stack_cap + 1u) & ~1u) + kWfCand) * kBlockThreads * sizeof(unsigned short);
 }
 static size_t clustered_global_smem_bytes(uint32_t stack_cap) {   // tree in global memory, 32-bit candidate codes
-    return (size_t)kWfCand * kBlockThreads * sizeof(uint32_t) + (size_t)stack_cap * kBlockThreads * sizeof(unsigned short);
+    return (size_t)kWfCand * kBlockThreads * sizeof(uint32_t) + (size_t)((stack_cap + 1u) & ~1u) * kBlockThreads * sizeof(unsigned short);
 }
 
 template <typename K>

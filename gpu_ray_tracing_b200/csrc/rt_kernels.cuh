@@ -38,6 +38,14 @@ constexpr int kPrimTileH = 8;
 #ifndef RT_PRIM_SORT_MAX
 #define RT_PRIM_SORT_MAX 16
 #endif
+// Order in which the dynamic tile tickets walk the window: 0 = top-down (row-major), 1 = bottom-up, 2 = middle-out by
+// tile rows (the window's edges last: sky above and the near ground below are the cheapest tiles of most frames).  A warp's last
+// tile decides the kernel's tail; tiles that hold geometry cost several times a sky tile, and with the horizon in the
+// upper part of the frame (the reference's default camera looks slightly down, camera.rs:38-40) top-down hands out the
+// expensive tiles LAST.
+#ifndef RT_PRIM_TILE_ORDER
+#define RT_PRIM_TILE_ORDER 0
+#endif
 #ifndef RT_PRIM_WORK
 #define RT_PRIM_WORK 224
 #endif
