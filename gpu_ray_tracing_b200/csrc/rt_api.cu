@@ -291,7 +291,8 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
                               r->cl_stack_cap <= rtk::kTreeStackMax;
             r->cl_bytes = fits ? (uint32_t)tree.bounce_bytes() : 0u;
             // too large for shared memory: the bounce kernel walks the tree where it lies (16-bit node numbers on its stack)
-            r->cl_global = (!fits && tree.n_nodes < 65536u && r->n_spheres < 0x80000000u && r->cl_stack_cap <= rtk::kTreeStackMax) ? 1u : 0u;
+            // (sphere indices travel in 26 bits of the cooperative traversal's candidate codes)
+            r->cl_global = (!fits && tree.n_nodes < 65536u && r->n_spheres < (1u << 26) && r->cl_stack_cap <= rtk::kTreeStackMax) ? 1u : 0u;
         }
         r->tree_build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build).count();
     }

@@ -1228,9 +1228,15 @@ __device__ __forceinline__ void wf_resolve(const UpdateParams& P, const float4* 
 #ifndef RT_WF_PAIR_ROWS
 #define RT_WF_PAIR_ROWS 0
 #endif
+#ifndef RT_WF_COOP_GLOBAL
+#define RT_WF_COOP_GLOBAL 1   /* trees walked in GLOBAL memory use the warp-cooperative traversal (trace_tree_coop) */
+#endif
+// A word of a warp's cooperative queue area used as parking space by wf_resolve_batch: column stride 32, not a CTA's.
+enum CoopWord : uint32_t {};
 template <typename T>
 __device__ __forceinline__ int col_at(int k) {
-    if constexpr (sizeof(T) == 2 && RT_WF_PAIR_ROWS) return (k >> 1) * (2 * kBlockThreads) + (k & 1);
+    if constexpr (std::is_same<T, CoopWord>::value) return k * 32;   // a column of the WARP's queue area
+    else if constexpr (sizeof(T) == 2 && RT_WF_PAIR_ROWS) return (k >> 1) * (2 * kBlockThreads) + (k & 1);
     else return k * kBlockThreads;
 }
 template <typename T>
@@ -1242,7 +1248,7 @@ __device__ __forceinline__ T* col_base(T* block_base) {
 template <typename CandT>
 __device__ __forceinline__ void park_word(CandT* s_cand, int k, uint32_t v) {
     if constexpr (sizeof(CandT) == 4) {
-        s_cand[k * kBlockThreads] = v;
+        s_cand[col_at<CandT>(k)] = (CandT)v;
     } else {
         s_cand[col_at<CandT>(2 * k)] = (CandT)(v & 0xffffu);
         s_cand[col_at<CandT>(2 * k + 1)] = (CandT)(v >> 16);
@@ -1250,7 +1256,7 @@ __device__ __forceinline__ void park_word(CandT* s_cand, int k, uint32_t v) {
 }
 template <typename CandT>
 __device__ __forceinline__ uint32_t parked_word(const CandT* s_cand, int k) {
-    if constexpr (sizeof(CandT) == 4) return s_cand[k * kBlockThreads];
+    if constexpr (sizeof(CandT) == 4) return (uint32_t)s_cand[col_at<CandT>(k)];
     else return (uint32_t)s_cand[col_at<CandT>(2 * k)] | ((uint32_t)s_cand[col_at<CandT>(2 * k + 1)] << 16);
 }
 template <int F, typename CandT>
@@ -1487,6 +1493,214 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Warp-cooperative traversal (trees walked in GLOBAL memory, RT_WF_COOP_GLOBAL).  trace_tree above keeps a stack per THREAD, and the warp runs as long as its
+// busiest lane: from the second bounce on the 64 rays of a batch come from all over the image and 15-17 of 32 lanes are
+// active per instruction (profiles/r2_bounce_ncu.md).  Here the work belongs to the WARP: the entry scan (coherent, all
+// lanes on the same record, two rays per lane in an FFMA2 pair — unchanged) emits (ray, node) items into a queue in the
+// warp's shared memory; each step the 32 top items go one to a lane, which tests the node's 8 child records for THAT ray
+// (scalar FFMA: the ray's parameters come from shared memory) and pushes (ray, child) items or, under a leaf node,
+// (ray, sphere) candidates through a warp prefix sum; candidates are drained 32 at a time, one reference quadratic per
+// lane.  A lane is busy whenever the warp has 32 items, whatever ray they belong to, and rays that ended (to-completion
+// batches of finish_paths) cost nothing.  The nearest hit per ray is the 64-bit minimum of (bits of t, sphere index) —
+// t > tmin > 0, so the float's bits order as the value does — kept with atomicMin in shared memory: the lexicographic
+// (t, index) minimum of rtc::nearest_update, whatever the order of the tests.  A NaN root flags its ray for the
+// sequential retrace as before.  Same candidate set, same exact test, same result as trace_tree, bit for bit.
+// Measured (B200, depth-8 frames): where the tree image sits in SHARED memory the per-thread traversal wins — 1,024
+// spheres at 4K: 2.55 ms against 3.60 cooperative, depth 30: 3.78 against 4.65 (an FFMA2 serves two rays per
+// instruction there and a step's queue bookkeeping costs as much as its 56 FMAs) — so that path keeps trace_tree.  Where
+// the tree is walked in GLOBAL memory the walk is latency-bound and full lanes hide it: 65,536 spheres at 1080p,
+// 8.0 -> 5.3 ms.  The kGlobal instantiations use this traversal.
+//   per warp: 64 rays x 4 float4 (u, h0 | -2o, thr | o, a | d, m), 64 x u64 nearest keys, kCoopItems node items
+//   (ray << 16 | node), kCoopCands candidates (ray << 26 | sphere), 2 words of NaN flags.
+// ---------------------------------------------------------------------------------------------
+constexpr int kCoopItems = 768, kCoopCands = 512;
+constexpr int kCoopStepGrowth = 32 * (kTreeWide - 1);   // a full step pops 32 items and pushes at most 32 x 8
+constexpr int kCoopDfsReserve = 7 * 16;                 // one-node-at-a-time descent: + 7 items per level
+constexpr size_t kCoopWarpBytes = 64 * 4 * sizeof(float4) + 64 * sizeof(unsigned long long) + (kCoopItems + kCoopCands) * sizeof(uint32_t) + 16;
+static_assert(kCoopWarpBytes % 16 == 0, "warp regions stay 16-byte aligned");
+
+struct CoopWarp {
+    float4* ray;
+    unsigned long long* best;
+    uint32_t* items;
+    uint32_t* cands;
+    uint32_t* nan;
+};
+__device__ __forceinline__ CoopWarp coop_warp(void* cta_base, int warp) {
+    unsigned char* b = static_cast<unsigned char*>(cta_base) + (size_t)warp * kCoopWarpBytes;
+    CoopWarp w;
+    w.ray = reinterpret_cast<float4*>(b);
+    w.best = reinterpret_cast<unsigned long long*>(b + 64 * 4 * sizeof(float4));
+    w.items = reinterpret_cast<uint32_t*>(b + 64 * 4 * sizeof(float4) + 64 * sizeof(unsigned long long));
+    w.cands = w.items + kCoopItems;
+    w.nan = w.cands + kCoopCands;
+    return w;
+}
+
+// Inclusive warp prefix sum of a packed pair of counts (low 16 bits | high 16 bits; sums stay below 2^16).
+__device__ __forceinline__ uint32_t warp_scan_incl(uint32_t v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+__device__ __forceinline__ void coop_drain(const CoopWarp& w, int& n_cand, int keep_below, const GpuSphere* __restrict__ spheres,
+                                           uint32_t n_spheres, uint32_t& exact_tests, int lane) {
+    // full steps of 32 while more than `keep_below` candidates wait (0: everything)
+    while (n_cand > keep_below) {
+        const int take = min(32, n_cand);
+        n_cand -= take;
+        if (lane < take) {
+            const uint32_t c = w.cands[n_cand + lane];
+            const uint32_t ray = c >> 26, idx = c & 0x3FFFFFFu;
+            if (idx < n_spheres) {   // (an empty slot can only get here through a NaN threshold)
+                const float4 q2 = w.ray[ray * 4 + 2], q3 = w.ray[ray * 4 + 3];
+                const float4 gs = __ldg(reinterpret_cast<const float4*>(spheres + idx));   // centre, radius as uploaded
+                float bt = kTMax;
+                int bi = -1;
+                ++exact_tests;
+                if (!rtc::nearest_update_from_inside(rtc::mk(q2.x, q2.y, q2.z), rtc::mk(q3.x, q3.y, q3.z), q2.w, rtc::mk(gs.x, gs.y, gs.z),
+                                                     gs.w, kTMin, kTMax, (int)idx, &bt, &bi))
+                    atomicOr(&w.nan[ray >> 5], 1u << (ray & 31u));
+                else if (bi >= 0)
+                    atomicMin(&w.best[ray], ((unsigned long long)__float_as_uint(bt) << 32) | (unsigned long long)idx);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// Works the node queue down to `keep_below` items (0: empty).
+__device__ __forceinline__ void coop_nodes(const TreeView& tv, const CoopWarp& w, int& n_items, int& n_cand, int keep_below,
+                                           const GpuSphere* __restrict__ spheres, uint32_t n_spheres, uint32_t& exact_tests, int lane) {
+    while (n_items > keep_below) {
+        if (n_cand > kCoopCands - 32 * kTreeWide) coop_drain(w, n_cand, 31, spheres, n_spheres, exact_tests, lane);
+        // a nearly full queue is worked off one node at a time, depth first: it then grows by at most 7 per level
+        const int take = (n_items + kCoopStepGrowth + kCoopDfsReserve <= kCoopItems) ? min(32, n_items) : 1;
+        n_items -= take;
+        uint32_t pass = 0, ray = 0, node = 0;
+        bool leaf = false;
+        if (lane < take) {
+            const uint32_t it = w.items[n_items + lane];
+            ray = it >> 16;
+            node = it & 0xFFFFu;
+            if (node != 0xFFFFu) {   // (the link of an empty slot)
+                leaf = (int)node >= tv.first_leaf;
+                const float4 q0 = w.ray[ray * 4], q1 = w.ray[ray * 4 + 1];
+                float thr = q1.w;
+                if (!leaf) thr = rtc::cluster_thr(thr, w.ray[ray * 4 + 3].w, tv.node_r[node]);
+                const float4* rec = tv.rec + node * kTreeStride;
+#pragma unroll
+                for (int k = 0; k < kTreeWide; ++k) {
+                    const float4 r = rec[k];
+                    const float g = rtc::broad_g(r.x, r.y, r.z, r.w, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z);
+                    pass |= (!(g < thr) ? 1u : 0u) << k;
+                }
+            }
+        }
+        __syncwarp();   // the taken items have been read before their slots are reused
+        const uint32_t c = (uint32_t)__popc(pass);
+        const uint32_t mine = leaf ? (c << 16) : c;
+        const uint32_t incl = warp_scan_incl(mine, lane);
+        const uint32_t total = __shfl_sync(kFull, incl, 31);
+        const uint32_t excl = incl - mine;
+        const uint32_t* link = tv.link + node * kTreeWide;
+        if (leaf) {
+            uint32_t pos = (uint32_t)n_cand + (excl >> 16);
+            while (pass) {
+                const int k = __ffs((int)pass) - 1;
+                pass &= pass - 1u;
+                w.cands[pos++] = (ray << 26) | (link[k] & 0x3FFFFFFu);
+            }
+        } else {
+            uint32_t pos = (uint32_t)n_items + (excl & 0xFFFFu);
+            while (pass) {
+                const int k = __ffs((int)pass) - 1;
+                pass &= pass - 1u;
+                w.items[pos++] = (ray << 16) | (link[k] & 0xFFFFu);
+            }
+        }
+        n_items += (int)(total & 0xFFFFu);
+        n_cand += (int)(total >> 16);
+        __syncwarp();
+    }
+}
+
+// Nearest hits of the thread's rays 0 and 1 (rays 2 lane and 2 lane + 1 of the warp's batch), cooperatively.
+__device__ __forceinline__ void trace_tree_coop(const TreeView& tv, const CoopWarp& w, const GpuSphere* __restrict__ spheres,
+                                                uint32_t n_spheres, Lanes& L, uint32_t& exact_tests) {
+    const int lane = threadIdx.x & 31;
+    const float inf = __int_as_float(0x7f800000);
+    const float thr0 = L.alive[0] ? L.thr[0] : inf, thr1 = L.alive[1] ? L.thr[1] : inf;
+    const f3 o0 = origin_of(L, 0), o1 = origin_of(L, 1);
+    const float m0 = rtc::cluster_m(rtc::dot(o0, o0)), m1 = rtc::cluster_m(rtc::dot(o1, o1));
+    __syncwarp();   // (the queue area may have held the previous batch's parked words)
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        float4* q = w.ray + (2 * lane + p) * 4;
+        q[0] = make_float4(half(L.ux[0], p), half(L.uy[0], p), half(L.uz[0], p), half(L.h0[0], p));
+        q[1] = make_float4(half(L.mox[0], p), half(L.moy[0], p), half(L.moz[0], p), p ? thr1 : thr0);
+        q[2] = make_float4(L.ox[p], L.oy[p], L.oz[p], L.a[p]);
+        q[3] = make_float4(L.dx[p], L.dy[p], L.dz[p], p ? m1 : m0);
+        w.best[2 * lane + p] = ((unsigned long long)__float_as_uint(kTMax) << 32) | 0xFFFFFFFFull;
+    }
+    if (lane < 2) w.nan[lane] = 0u;
+    __syncwarp();
+    int n_items = 0, n_cand = 0;
+    // the entry list, all lanes on the same record: one pass bit per (ray, entry), 32 entries at a time, then the set
+    // bits become (ray, node) items, one per lane and round
+    const float e0 = rtc::cluster_thr(thr0, m0, tv.entry_r), e1 = rtc::cluster_thr(thr1, m1, tv.entry_r);
+#pragma unroll 1
+    for (int w0 = 0; w0 < tv.n_entry_pad; w0 += 32) {
+        const int wn = min(32, tv.n_entry_pad - w0);   // (a multiple of 4)
+        uint32_t bits0 = 0u, bits1 = 0u;
+#pragma unroll 4
+        for (int i = 0; i < wn; ++i) {
+            const float2 g = broad_g2(tv.entry_rec[w0 + i], L, 0);
+            bits0 = (bits0 >> 1) | (!(g.x < e0) ? 0x80000000u : 0u);
+            bits1 = (bits1 >> 1) | (!(g.y < e1) ? 0x80000000u : 0u);
+        }
+        bits0 >>= (32 - wn);
+        bits1 >>= (32 - wn);
+        while (__any_sync(kFull, (bits0 | bits1) != 0u)) {
+            if (n_items > kCoopItems - kCoopStepGrowth - kCoopDfsReserve - 32)
+                coop_nodes(tv, w, n_items, n_cand, 31, spheres, n_spheres, exact_tests, lane);
+            const bool first = bits0 != 0u;
+            const uint32_t bits = first ? bits0 : bits1;
+            const bool has = bits != 0u;
+            const int e = __ffs((int)bits) - 1;
+            if (first) bits0 &= bits0 - 1u; else bits1 &= bits1 - 1u;
+            const unsigned m = __ballot_sync(kFull, has);
+            if (has) {
+                const uint32_t node = tv.entry_node[w0 + e];
+                w.items[n_items + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)(2 * lane + (first ? 0 : 1)) << 16) | (node & 0xFFFFu);
+            }
+            n_items += __popc(m);
+            __syncwarp();
+        }
+    }
+    coop_nodes(tv, w, n_items, n_cand, 0, spheres, n_spheres, exact_tests, lane);
+    coop_drain(w, n_cand, 0, spheres, n_spheres, exact_tests, lane);
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const unsigned long long key = w.best[2 * lane + p];
+        L.best_t[p] = __uint_as_float((uint32_t)(key >> 32));
+        L.best_i[p] = (int)(uint32_t)(key & 0xFFFFFFFFull);
+        if ((w.nan[(2 * lane + p) >> 5] >> ((2 * lane + p) & 31)) & 1u) {
+            const float2 hit = retrace_sequential(spheres, n_spheres, L.ox[p], L.oy[p], L.oz[p], L.dx[p], L.dy[p], L.dz[p], L.a[p]);
+            L.best_t[p] = hit.x;
+            L.best_i[p] = __float_as_int(hit.y);
+            exact_tests += n_spheres;
+        }
+    }
+    __syncwarp();   // the queues may become parking space (wf_resolve_batch)
+}
+
 // Few paths left (less than RT_WF_COMPLETE_BELOW rays per resident warp): finish them inside ONE launch, every
 // remaining bounce, instead of paying a launch and a pass latency per bounce for a nearly empty machine.  Nothing is
 // queued, so the later bounce launches find empty queues and return.  Kept out of line: inlined, its live state
@@ -1494,10 +1708,10 @@ __device__ __forceinline__ void trace_tree(const TreeView& tv, unsigned short* _
 #ifndef RT_WF_COMPLETE_BELOW
 #define RT_WF_COMPLETE_BELOW 64u   /* one 64-ray batch per resident warp (A/B on B200: 16 / 32 / 48 / 64 / 80 -> 4.52 / 4.49 / 4.41 / 4.31 / 4.60 ms per depth-30 4K frame) */
 #endif
-template <int F, typename CandT>
+template <int F, bool kCoop, typename CandT>
 __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* __restrict__ qin, uint32_t count,
                                           const TreeView& tv, unsigned short* __restrict__ s_stack, CandT* __restrict__ s_cand,
-                                          unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
+                                          void* coop_base, unsigned int* ticket, uint32_t bounce, uint32_t max_depth, bool reset, int lane,
                                           uint32_t& exact_tests_out, uint32_t& rays_out, uint32_t& rays_later_out) {
     const uint32_t n_batches = (count + 63u) / 64u;
     unsigned int* traced = &P.wf_counts[2u * (kWfMaxDepth + 1u)];
@@ -1526,7 +1740,8 @@ __device__ __noinline__ void finish_paths(const UpdateParams& P, const float4* _
             }
         }
         for (uint32_t b = bounce;; ++b) {
-            trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+            if constexpr (kCoop) trace_tree_coop(tv, coop_warp(coop_base, threadIdx.x >> 5), P.spheres, P.n_spheres, L, exact_tests);
+            else trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
 #pragma unroll
             for (int p = 0; p < 2; ++p) {
                 if (!L.alive[p]) continue;
@@ -1575,7 +1790,7 @@ __device__ __forceinline__ void wf_flush(const UpdateParams& P, uint32_t bounce,
 // reads the tree where it lies in global memory (L1 / L2; the upper levels stay hot), and the candidate codes are
 // 32 bits wide, so the sphere count is not limited by the code's 15 index bits either.
 template <bool kGlobal, int F>
-__global__ void __launch_bounds__(kBlockThreads, 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
+__global__ void __launch_bounds__(kBlockThreads, (kGlobal && RT_WF_COOP_GLOBAL) ? 2 : 3) bounce_clustered_kernel(const __grid_constant__ UpdateParams P) {
     extern __shared__ float4 s_dyn[];
     __shared__ __align__(8) uint64_t s_bar;
     using CandT = typename std::conditional<kGlobal, uint32_t, unsigned short>::type;
@@ -1620,8 +1835,14 @@ __global__ void __launch_bounds__(kBlockThreads, 3) bounce_clustered_kernel(cons
         const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
         Lanes L;
         wf_load_rays<2, F>(P, qin, count, j0, L, rays);
-        trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
-        wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
+        if constexpr (kGlobal && RT_WF_COOP_GLOBAL) {
+            const CoopWarp cw = coop_warp(s_dyn + image_slots, threadIdx.x >> 5);
+            trace_tree_coop(tv, cw, P.spheres, P.n_spheres, L, exact_tests);
+            wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, reinterpret_cast<CoopWord*>(cw.items) + lane);   // (the queue is idle here)
+        } else {
+            trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+            wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);   // (the thread's candidate column is idle here)
+        }
     }
     wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
 }
@@ -1679,12 +1900,18 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_tail_kernel(const __g
                 const uint32_t j0 = batch * 64u + 2u * (uint32_t)lane;
                 Lanes L;
                 wf_load_rays<2, F>(P, qin, count, j0, L, rays);
-                trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
-                wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);
+                if constexpr (kGlobal && RT_WF_COOP_GLOBAL) {
+                    const CoopWarp cw = coop_warp(s_dyn + image_slots, threadIdx.x >> 5);
+                    trace_tree_coop(tv, cw, P.spheres, P.n_spheres, L, exact_tests);
+                    wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, reinterpret_cast<CoopWord*>(cw.items) + lane);
+                } else {
+                    trace_tree(tv, s_stack, s_cand, P.spheres, P.n_spheres, L, exact_tests);
+                    wf_resolve_batch<F>(P, qin, count, j0, L, bounce, last, reset, lane, s_cand);
+                }
             }
         } else {
             // short queue: every path to its end; nothing is queued, so the next length read is 0 for the whole grid
-            finish_paths<F>(P, qin, count, tv, s_stack, s_cand, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
+            finish_paths<F, (kGlobal && RT_WF_COOP_GLOBAL)>(P, qin, count, tv, s_stack, s_cand, s_dyn + image_slots, ticket, bounce, max_depth, reset, lane, exact_tests, rays, rays_later);
         }
         wf_flush(P, bounce, exact_tests, rays, rays_later, lane);
         if (last) break;
@@ -1990,9 +2217,11 @@ static size_t bounce_smem_bytes() {
     return (size_t)2 * (kWfChunk + kGeomTail) * sizeof(float4) + (size_t)kWfDefer * kBlockThreads * sizeof(unsigned short);
 }
 static size_t clustered_smem_bytes(uint32_t image_bytes, uint32_t stack_cap) {
+
     return (size_t)(image_bytes + 15u) / 16u * 16u + (size_t)(((stack_cap + 1u) & ~1u) + kWfCand) * kBlockThreads * sizeof(unsigned short);
 }
 static size_t clustered_global_smem_bytes(uint32_t stack_cap) {   // tree in global memory, 32-bit candidate codes
+    if (RT_WF_COOP_GLOBAL) return (size_t)(kBlockThreads / 32) * kCoopWarpBytes;
     return (size_t)kWfCand * kBlockThreads * sizeof(uint32_t) + (size_t)((stack_cap + 1u) & ~1u) * kBlockThreads * sizeof(unsigned short);
 }
 
