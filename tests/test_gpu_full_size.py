@@ -348,3 +348,30 @@ def test_interleaved_band_shards_equal_the_whole_image(depth):
         m.update(cam)
         assert np.array_equal(m.gather_rgba8(), ol.quantize(whole))
         assert np.array_equal(m.gather_accum().view(np.uint32), whole.view(np.uint32))
+
+
+def test_converged_default_image_500_spp():
+    """The application's working point (camera.rs:33-34: 500 samples per pixel, max_depth 30; default scene) at reduced
+    size: 500 progressive frames through rt_update_n — random_seed re-rolled per frame (camera.rs:346), reset flag on the
+    first only — against the oracle looped 500 times.  Every texel holds n = 500 and the running means agree bit for bit
+    (the running-mean order is the frames' order on both sides)."""
+    W, H, S = 128, 72, 500
+    scene = scenes.default_scene()
+    cams = [scenes.camera(W, H, 30, S, random_seed=((i + 1) * 2654435761 % (1 << 24)) / float(1 << 24), moved=1 if i == 0 else 0)
+            for i in range(S)]
+    cpu = None
+    for cam in cams:
+        cpu, _ = ol.oracle_update(cam, scene, W, H, accum=cpu)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene)
+        r.init()
+        r.update_n(cams)
+        gpu = r.read_accum()
+        # one more frame changes nothing: the sample cap is reached (compute_shader.wgsl:343, 352)
+        r.update(scenes.camera(W, H, 30, S, random_seed=0.123, moved=0))
+        capped = r.read_accum()
+    assert (gpu[..., 3] == float(S)).all()
+    assert_bit_identical(gpu, cpu, "default scene 128x72, depth 30, 500 spp")
+    assert np.array_equal(capped.view(np.uint32), gpu.view(np.uint32))
+    # converged: neighbouring sky pixels are smooth (a 1-spp frame is not) — the mean of 500 samples, not the last one
+    assert float(np.abs(np.diff(gpu[0, :, :3], axis=0)).max()) < 0.02
