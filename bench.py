@@ -632,7 +632,7 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
     same frames alone (t1) and compares."""
     K = max(5, min(args.steps, 20))
     frame8 = W8K * H8K * 4
-    band_rows = 16
+    band_rows = int(os.environ.get("RT_BENCH_BAND_ROWS", "16"))   # (a multiple of 8; A/B knob)
     g = Gather(rt, dist, torch, rank, world, local_rank, frame8)
     # interleaved 16-row bands, not contiguous blocks: rows that hold geometry cost more than sky rows
     rs = rt.Renderer(W8K, H8K, device=local_rank, bands=(band_rows, world, rank))

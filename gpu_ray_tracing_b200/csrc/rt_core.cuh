@@ -162,6 +162,27 @@ RT_DEV f3 random_unit_vector(uint32_t seed) {
     }
 }
 
+// ray_color's seed does not depend on the pixel (compute_shader.wgsl:268, 353: hash(seed + i * 1000) with seed = 1 + n +
+// u32(random_seed * 2^32)), so every path of a frame with the same sample count n draws the SAME random unit vector at
+// bounce i.  A caller that shades several rays in a row (a thread's strip of the primary pass) keeps the last one: two
+// hashes, a square root and a sin / cos per thread instead of per ray.  Pure memoisation: same bits.  One cache per
+// precision level (the levels' values differ).
+struct UnitVecCache {
+    uint32_t seed;
+    f3 v;
+    bool valid;
+};
+template <int F>
+RT_DEV f3 random_unit_vector_cached(uint32_t seed, UnitVecCache* c) {
+    if (c == nullptr) return random_unit_vector<F>(seed);
+    if (!(c->valid && c->seed == seed)) {
+        c->v = random_unit_vector<F>(seed);
+        c->seed = seed;
+        c->valid = true;
+    }
+    return c->v;
+}
+
 struct Ray {
     f3 o, d;
 };
@@ -247,7 +268,8 @@ RT_DEV f3 sky_times(f3 factor, f3 dir) {
 // with the exact arithmetic (one shared out-of-line copy).  The tolerance modes so make the reference's decisions, ray
 // for ray, and differ from the exact mode by the rounding of the values only.
 template <int F>
-RT_DEV bool scatter_impl(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed, bool* risky) {
+RT_DEV bool scatter_impl(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed, bool* risky,
+                         UnitVecCache* ruv_cache = nullptr) {
     f3 o = ray->o, d = ray->d;
     f3 center = mk(sp.position);
     f3 p, outward;
@@ -274,7 +296,7 @@ RT_DEV bool scatter_impl(Ray* ray, f3* factor, float t, const GpuSphere& sp, uin
     out.o = p;
     if (w < -1.0f) {
         // lambertian_scatter, compute_shader.wgsl:84-93
-        f3 dir = add(n, random_unit_vector<F>(bounce_seed));
+        f3 dir = add(n, random_unit_vector_cached<F>(bounce_seed, ruv_cache));
         if constexpr (F) *risky |= !(dot_t<1>(dir, dir) > 1e-3f);   // nearly opposite vectors: the direction is ill-conditioned
         if (dot_t<F>(dir, dir) < 1e-6f) dir = n;
         out.d = dir;
@@ -284,7 +306,7 @@ RT_DEV bool scatter_impl(Ray* ray, f3* factor, float t, const GpuSphere& sp, uin
     } else if (w <= 1.0f) {
         // metal_scatter, compute_shader.wgsl:95-100; reflect(e1,e2) = e1 - 2 dot(e2,e1) e2
         f3 refl = sub(d, scale(2.0f * dot_t<F>(n, d), n));
-        f3 reflected = add(normalize_branch<F>(refl), scale(w, random_unit_vector<F>(bounce_seed)));
+        f3 reflected = add(normalize_branch<F>(refl), scale(w, random_unit_vector_cached<F>(bounce_seed, ruv_cache)));
         out.d = normalize_branch<F>(reflected);
         *factor = mul(*factor, albedo);
         *ray = out;
@@ -336,14 +358,14 @@ RT_DEV_SHARED bool scatter_exact_shared(Ray* ray, f3* factor, float t, const Gpu
     return scatter_impl<0>(ray, factor, t, sp, bounce_seed, &unused);
 }
 template <int F = 0>
-RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed) {
+RT_DEV bool scatter(Ray* ray, f3* factor, float t, const GpuSphere& sp, uint32_t bounce_seed, UnitVecCache* ruv_cache = nullptr) {
     bool risky = false;
     if constexpr (F == 0) {
-        return scatter_impl<0>(ray, factor, t, sp, bounce_seed, &risky);
+        return scatter_impl<0>(ray, factor, t, sp, bounce_seed, &risky, ruv_cache);
     } else {
         Ray r = *ray;
         f3 f = *factor;
-        const bool ok = scatter_impl<F>(&r, &f, t, sp, bounce_seed, &risky);
+        const bool ok = scatter_impl<F>(&r, &f, t, sp, bounce_seed, &risky, ruv_cache);
         if (risky) return scatter_exact_shared(ray, factor, t, sp, bounce_seed);
         *ray = r;
         *factor = f;

@@ -766,7 +766,7 @@ __device__ __forceinline__ void push_path(const UpdateParams& P, uint32_t next_b
 template <int F = 0>
 __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t bounce, bool last, int best_i, float best_t,
                                             f3& o, f3& d, f3& factor, uint32_t texel_index, uint32_t bseed, uint32_t n,
-                                            bool reset) {
+                                            bool reset, rtc::UnitVecCache* ruv = nullptr) {
     if (best_i < 0) {
         finalize_texel<F>(P, texel_index, n, rtc::sky_times<F>(factor, d), reset);
         return false;
@@ -775,7 +775,7 @@ __device__ __forceinline__ bool resolve_hit(const UpdateParams& P, uint32_t boun
     rtc::Ray r;
     r.o = o;
     r.d = d;
-    const bool ok = rtc::scatter<F>(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u));   // compute_shader.wgsl:268
+    const bool ok = rtc::scatter<F>(&r, &factor, best_t, sp, rtc::hash(bseed + bounce * 1000u), ruv);   // compute_shader.wgsl:268
     if (!ok) {
         finalize_texel<F>(P, texel_index, n, rtc::mk(0.0f, 0.0f, 0.0f), reset);
         return false;
@@ -806,6 +806,8 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         const uint32_t sampling = L.alive | untraced;
         const uint32_t max_depth = rtc::f2u(P.cam.max_depth);
         const int lane = threadIdx.x & 31;
+        rtc::UnitVecCache ruv_queue;   // the strip's rays share their bounce seed (rtc::UnitVecCache)
+        ruv_queue.valid = false;
         // pass A: resolve every ray's first hit; a continuing path parks its scattered ray in the ray's own slots
         // (d, o; n in the best_t slot, the sphere index stays: the factor after one hit is that sphere's attenuation)
         uint32_t pmask = 0;
@@ -831,7 +833,7 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                 ++rays;
                 f3 factor = rtc::mk(1.0f, 1.0f, 1.0f);
                 const uint32_t bseed = 2u + n + seed_bits;   // hash seed of bounce 0 (compute_shader.wgsl:353, 268)
-                if (resolve_hit<F>(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset)) {
+                if (resolve_hit<F>(P, 0u, max_depth <= 1u, best_i, best_t, o, d, factor, texel_index, bseed, n, reset, &ruv_queue)) {
                     dp[0] = d.x; dp[kPrimThreads] = d.y; dp[2 * kPrimThreads] = d.z;
                     dp[3 * kPrimThreads] = o.x; dp[4 * kPrimThreads] = o.y; dp[5 * kPrimThreads] = o.z;
                     dp[6 * kPrimThreads] = __uint_as_float(n);
@@ -888,7 +890,10 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         // a ray whose scatter sits inside a decision margin (rtc::scatter_impl, *risky) is left alone by the first
         // pass and finished with the exact arithmetic by a second one, which the hot loop so need not carry a call for
         const uint32_t sampling = L.alive | untraced;
-        auto shade_one = [&](int p, auto prec) -> bool {
+        rtc::UnitVecCache ruv_main, ruv_redo;   // (the redo pass is exact arithmetic: its own cache)
+        ruv_main.valid = false;
+        ruv_redo.valid = false;
+        auto shade_one = [&](int p, auto prec, rtc::UnitVecCache* ruv) -> bool {
             constexpr int FF = decltype(prec)::value;
             const int row = row0 + p;
             if (!((uint32_t)x < P.width && (uint32_t)row < P.row_count)) return false;
@@ -920,7 +925,7 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
                     const GpuSphere sp = load_sphere(P.spheres, best_i);
                     const uint32_t seed = 1u + n + seed_bits;                       // compute_shader.wgsl:353
                     bool risky = false;
-                    black = !rtc::scatter_impl<FF>(&r, &factor, best_t, sp, rtc::hash(seed + 1u), &risky);   // :268 with i = 0
+                    black = !rtc::scatter_impl<FF>(&r, &factor, best_t, sp, rtc::hash(seed + 1u), &risky, ruv);   // :268 with i = 0
                     if (FF != 0 && risky) return true;   // texel untouched: the exact pass takes it
                 }
                 ++rays;
@@ -938,13 +943,13 @@ __device__ __forceinline__ void prim_finish(const UpdateParams& P, int x, int ro
         uint32_t redo = 0;
 #pragma unroll 1
         for (int p = 0; p < kPrimRays; ++p)
-            if (shade_one(p, std::integral_constant<int, F>())) redo |= 1u << p;
+            if (shade_one(p, std::integral_constant<int, F>(), &ruv_main)) redo |= 1u << p;
         if constexpr (F != 0) {
 #pragma unroll 1
             while (redo) {
                 const int p = __ffs((int)redo) - 1;
                 redo &= redo - 1u;
-                shade_one(p, std::integral_constant<int, 0>());
+                shade_one(p, std::integral_constant<int, 0>(), &ruv_redo);
             }
         }
     }
@@ -1267,6 +1272,8 @@ __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const fl
     bool push = false, push0 = false;
     f3 o = rtc::mk(0.0f, 0.0f, 0.0f), d = o, factor = o;
     uint32_t texel_index = 0, bseed = 0, n = 0;
+    rtc::UnitVecCache ruv_batch;   // the thread's two paths usually share their bounce seed
+    ruv_batch.valid = false;
     __syncwarp();
 #pragma unroll 1
     for (int p = 0; p < 2; ++p) {
@@ -1283,7 +1290,7 @@ __device__ __forceinline__ void wf_resolve_batch(const UpdateParams& P, const fl
             d = second ? rtc::mk(L.dx[1], L.dy[1], L.dz[1]) : rtc::mk(L.dx[0], L.dy[0], L.dz[0]);
             const float best_t = second ? L.best_t[1] : L.best_t[0];
             const int best_i = second ? L.best_i[1] : L.best_i[0];
-            push = resolve_hit<F>(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset);
+            push = resolve_hit<F>(P, bounce, last, best_i, best_t, o, d, factor, texel_index, bseed, n, reset, &ruv_batch);
         }
         if (p == 0) {
             push0 = push;
