@@ -97,7 +97,13 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     if (e == cudaSuccess) e = cudaMalloc(&r->accum, r->n_texels * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&r->rgba8, r->n_texels * sizeof(uchar4));
     if (e == cudaSuccess) e = cudaMalloc(&r->first_hit, r->n_texels * sizeof(float2));
-    if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, 2 * sizeof(unsigned int));
+    {   // the tile tickets and, behind them, the primary pass's per-tile-row costs (two frames) and row order
+        const uint32_t tile_rows = (row_count + rtk::kPrimTileH - 1) / rtk::kPrimTileH;
+        r->order_rows = (RT_PRIM_ROW_ORDER && tile_rows <= rtk::kOrderMaxRows) ? tile_rows : 0u;
+        const size_t words = 2 + 3 * (size_t)r->order_rows;
+        if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, words * sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaMemsetAsync(r->tile_counter, 0, words * sizeof(unsigned int), r->stream);
+    }
     if (e == cudaSuccess) e = cudaMalloc(&r->counters, 2 * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&r->wait_status, sizeof(unsigned int));
     if (e == cudaSuccess) e = cudaMemsetAsync(r->wait_status, 0, sizeof(unsigned int), r->stream);
@@ -256,6 +262,13 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.tiles_x = (r->width + rtk::kWarpTileW - 1) / rtk::kWarpTileW;
     p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
     p.tile_counter = r->tile_counter;
+    if (r->order_rows) {
+        unsigned int* cost = r->tile_counter + 2;
+        p.row_cost_cur = cost + (r->order_frame & 1u) * r->order_rows;
+        p.row_cost_prev = cost + ((r->order_frame & 1u) ^ 1u) * r->order_rows;
+        p.row_order = cost + 2 * (size_t)r->order_rows;
+        r->order_frame += 1;
+    }
     p.counters = r->counters;
     p.first_hit = r->first_hit;
     if (r->clusters_stale && (r->variant == 0 || r->variant >= 4) && r->n_spheres > 0) {

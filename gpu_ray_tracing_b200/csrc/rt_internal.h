@@ -35,7 +35,9 @@ struct RtRenderer {
     float cl_entry_r = 0.0f;
     uint32_t n_spheres = 0;
     bool has_scene = false;
-    unsigned int* tile_counter = nullptr;
+    unsigned int* tile_counter = nullptr;  // [2] tickets, then (tile_rows <= rtk::kOrderMaxRows) [2][tile_rows] costs, [tile_rows] order
+    uint32_t order_rows = 0;               // tile rows of the primary pass with a cost / order record; 0 = none
+    uint32_t order_frame = 0;              // parity of the cost buffer the next frame fills
     unsigned long long* counters = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     // asynchronous read-back (rt_read_rgba8_async): second RGBA8 buffer, copy stream, per-slot events

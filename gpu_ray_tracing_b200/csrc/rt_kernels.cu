@@ -1031,6 +1031,9 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
         T.entry_rec = P.prim_tree + (size_t)P.cl_n_nodes * kTreeStride;
     }
     uint32_t exact_tests = 0, rays = 0;
+#if RT_PRIM_PROBE
+    uint32_t probe_busy = 0;
+#endif
 
     for (;;) {
         uint32_t tile = 0;
@@ -1046,8 +1049,12 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
             tile = row_of * tiles_x + tile % tiles_x;
         }
 #endif
+        // ticket -> tile: the ticket's tile row goes through the frame's row order (dearest rows of the last frame first)
+        uint32_t tile_row = tile / tiles_x;
+        if (P.row_order != nullptr) tile_row = P.row_order[tile_row];
+        const long long t_begin = clock64();
         const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
-        const int row0 = (int)((tile / tiles_x) * kPrimTileH);
+        const int row0 = (int)(tile_row * kPrimTileH);
         PrimLanes L;
         uint32_t untraced;
         prim_setup<F>(P, x, row0, s_d, reinterpret_cast<float*>(s_rec) + lane, seed_bits, spp, reset, L, untraced);
@@ -1058,7 +1065,14 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
             prim_tree_walk(T, s_work, s_rec, s_idx, s_near, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
         prim_finish<kMode, F>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
+        if (lane == 0 && P.row_cost_cur != nullptr) atomicAdd(P.row_cost_cur + tile_row, (unsigned int)((clock64() - t_begin) >> 6));
+#if RT_PRIM_PROBE
+        probe_busy += (uint32_t)(clock64() - t_begin);
+#endif
     }
+#if RT_PRIM_PROBE
+    exact_tests = lane == 0 ? probe_busy : 0u;   // developer probe: the counter reports the warps' busy cycles instead
+#endif
     prim_flush(P, exact_tests, rays, lane);
 }
 
@@ -2003,7 +2017,28 @@ __global__ void prep_primary_tree_kernel(const float4* __restrict__ tree_rec, co
                                          const uint32_t* __restrict__ entry_slot, uint32_t n_entry,
                                          float4* __restrict__ out, uint32_t n_nodes, uint32_t first_leaf, float ox, float oy,
                                          float oz, double rho, float m_cam, unsigned int* __restrict__ tile_counter,
-                                         unsigned int* __restrict__ wf_counts) {
+                                         unsigned int* __restrict__ wf_counts, uint32_t record_blocks,
+                                         const unsigned int* __restrict__ row_cost_prev, unsigned int* __restrict__ row_cost_cur,
+                                         uint32_t* __restrict__ row_order, uint32_t tile_rows) {
+    if (blockIdx.x >= record_blocks) {
+        // The blocks behind the record blocks rank the tile rows by what they cost in the last frame, dearest first
+        // (ties: top-down, so a first frame is handed out top-down), and clear the record this frame adds to.  A
+        // thread per row counts the rows that go before its own: tile_rows <= kOrderMaxRows broadcast reads.
+        __shared__ unsigned int s_cost[kOrderMaxRows];
+        for (uint32_t j = threadIdx.x; j < tile_rows; j += blockDim.x) s_cost[j] = row_cost_prev[j];
+        __syncthreads();
+        const uint32_t i = (blockIdx.x - record_blocks) * blockDim.x + threadIdx.x;
+        if (i >= tile_rows) return;
+        const unsigned int mine = s_cost[i];
+        uint32_t before = 0;
+        for (uint32_t j = 0; j < tile_rows; ++j) {
+            const unsigned int c = s_cost[j];
+            before += (c > mine || (c == mine && j < i)) ? 1u : 0u;
+        }
+        row_order[before] = i;
+        row_cost_cur[i] = 0u;
+        return;
+    }
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     // the frame's tile tickets and (deep frames) queue lengths, batch tickets and per-bounce counters start at zero:
     // done here rather than by memset nodes of their own, the kernels that use them are ordered behind this one
@@ -2390,12 +2425,14 @@ cudaError_t launch_prep_primary_tree(const UpdateParams& p, bool zero_wavefront,
     const float m_cam = rtc::primary_m_cam(p.cam, rho);
     uint32_t n_threads = p.cl_n_nodes * kTreeStride + p.cl_n_entry;
     if (n_threads < kWfWords) n_threads = kWfWords;
-    prep_primary_tree_kernel<<<(n_threads + 255) / 256, 256, 0, stream>>>(
+    const uint32_t record_blocks = (n_threads + 255) / 256;
+    const uint32_t tile_rows = p.row_order != nullptr ? (p.row_count + kPrimTileH - 1) / kPrimTileH : 0u;
+    prep_primary_tree_kernel<<<record_blocks + (tile_rows + 255) / 256, 256, 0, stream>>>(
         reinterpret_cast<const float4*>(blob), reinterpret_cast<const uint32_t*>(blob + lay.off_link),
         reinterpret_cast<const float*>(blob + lay.off_child_r), p.spheres, reinterpret_cast<const uint32_t*>(blob + lay.off_entry_slot),
         p.cl_n_entry, const_cast<float4*>(p.prim_tree), p.cl_n_nodes,
         p.cl_first_leaf, p.cam.center.x, p.cam.center.y, p.cam.center.z, rho, m_cam, p.tile_counter,
-        zero_wavefront ? p.wf_counts : nullptr);
+        zero_wavefront ? p.wf_counts : nullptr, record_blocks, p.row_cost_prev, p.row_cost_cur, p.row_order, tile_rows);
     return cudaGetLastError();
 }
 

@@ -46,6 +46,14 @@ constexpr int kPrimTileH = 8;
 #ifndef RT_PRIM_TILE_ORDER
 #define RT_PRIM_TILE_ORDER 0
 #endif
+// 1: the primary pass hands out its tile rows dearest first, by the last frame's measured cost (UpdateParams::row_order);
+// 0: in RT_PRIM_TILE_ORDER's fixed order (the A/B arm)
+#ifndef RT_PRIM_ROW_ORDER
+#define RT_PRIM_ROW_ORDER 1
+#endif
+#ifndef RT_PRIM_PROBE
+#define RT_PRIM_PROBE 0   // developer probe: rt_exact_tests reports the primary pass's busy cycles summed over its warps
+#endif
 #ifndef RT_PRIM_WORK
 #define RT_PRIM_WORK 224
 #endif
@@ -100,7 +108,14 @@ struct UpdateParams {
     uint32_t rgba8_abs;             // rgba8_out holds the full image (gather target): index by absolute row
     uint32_t precision;             // RT_PRECISION_* (rt_set_precision)
     unsigned long long* counters;   // [0] rays (sphere_list_hit traversals), [1] narrow-phase tests
+    // Order in which the primary pass hands out its tile rows: every tile adds its duration to
+    // row_cost_cur[its tile row]; the next frame's prep kernel ranks the rows of row_cost_prev, dearest first, into
+    // row_order, so the frame ends on its cheapest tiles.  All three null (or tile_rows > kOrderMaxRows): top-down.
+    unsigned int* row_cost_cur = nullptr;
+    const unsigned int* row_cost_prev = nullptr;
+    uint32_t* row_order = nullptr;
 };
+constexpr uint32_t kOrderMaxRows = 2048;   // tile rows the prep kernel ranks (16,384 image rows); taller windows go top-down
 
 // variant: 1 = baseline (thread per pixel, exact test per sphere from global memory),
 //          2 = tiled broad phase with the scene resident in shared memory,
