@@ -100,7 +100,7 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     {   // the tile tickets and, behind them, the primary pass's per-tile-row costs (two frames) and row order
         const uint32_t tile_rows = (row_count + rtk::kPrimTileH - 1) / rtk::kPrimTileH;
         r->order_rows = (RT_PRIM_ROW_ORDER && tile_rows <= rtk::kOrderMaxRows) ? tile_rows : 0u;
-        const size_t words = 2 + 3 * (size_t)r->order_rows;
+        const size_t words = 4 + 5 * (size_t)r->order_rows;
         if (e == cudaSuccess) e = cudaMalloc(&r->tile_counter, words * sizeof(unsigned int));
         if (e == cudaSuccess) e = cudaMemsetAsync(r->tile_counter, 0, words * sizeof(unsigned int), r->stream);
     }
@@ -110,6 +110,11 @@ int rt_create_window(int device, uint32_t width, uint32_t height, uint32_t row_b
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_begin);
     if (e == cudaSuccess) e = cudaEventCreate(&r->ev_end);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->prep_stream, cudaStreamNonBlocking);
+    for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+        e = cudaEventCreateWithFlags(&r->ev_frame[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_prep[b], cudaEventDisableTiming);
+    }
     for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
         e = cudaEventCreateWithFlags(&r->ev_quantized[b], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&r->ev_copied[b], cudaEventDisableTiming);
@@ -174,7 +179,13 @@ int rt_destroy(RtRenderer* r) {
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
     if (r->copy_stream) cudaStreamSynchronize(r->copy_stream);
+    if (r->prep_stream) cudaStreamSynchronize(r->prep_stream);
     cudaFree(r->rgba8_alt);
+    for (int b = 0; b < 2; ++b) {
+        if (r->ev_frame[b]) cudaEventDestroy(r->ev_frame[b]);
+        if (r->ev_prep[b]) cudaEventDestroy(r->ev_prep[b]);
+    }
+    if (r->prep_stream) cudaStreamDestroy(r->prep_stream);
     for (int b = 0; b < 2; ++b) {
         if (r->ev_quantized[b]) cudaEventDestroy(r->ev_quantized[b]);
         if (r->ev_copied[b]) cudaEventDestroy(r->ev_copied[b]);
@@ -261,13 +272,14 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
     p.band_rows = r->band_rows; p.band_stride = r->band_stride;
     p.tiles_x = (r->width + rtk::kWarpTileW - 1) / rtk::kWarpTileW;
     p.n_tiles = p.tiles_x * ((r->row_count + rtk::kWarpTileH - 1) / rtk::kWarpTileH);
-    p.tile_counter = r->tile_counter;
+    const uint32_t frame = r->frame_index++;
+    const uint32_t parity = frame & 1u;
+    p.tile_counter = r->tile_counter + 2 * parity;
     if (r->order_rows) {
-        unsigned int* cost = r->tile_counter + 2;
-        p.row_cost_cur = cost + (r->order_frame & 1u) * r->order_rows;
-        p.row_cost_prev = cost + ((r->order_frame & 1u) ^ 1u) * r->order_rows;
-        p.row_order = cost + 2 * (size_t)r->order_rows;
-        r->order_frame += 1;
+        unsigned int* cost = r->tile_counter + 4;
+        p.row_cost_cur = cost + (size_t)(frame % 3u) * r->order_rows;
+        p.row_cost_prev = cost + (size_t)((frame + 1u) % 3u) * r->order_rows;   // the frame before the last one
+        p.row_order = cost + (size_t)(3u + parity) * r->order_rows;
     }
     p.counters = r->counters;
     p.first_hit = r->first_hit;
@@ -278,20 +290,22 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         rtt::Tree tree;
         const auto t_build = std::chrono::steady_clock::now();
         if (rtt::build(r->host_spheres.data(), r->n_spheres, tree)) {
-            const size_t rec_bytes = ((size_t)tree.n_nodes * rtk::kTreeStride + tree.n_entry_pad) * sizeof(float4);
+            const size_t rec_slots = (size_t)tree.n_nodes * rtk::kTreeStride + tree.n_entry_pad;
+            const size_t rec_bytes = rec_slots * sizeof(float4);
             if (tree.bytes() > r->cl_capacity || rec_bytes > r->prim_tree_capacity) {
                 RT_CUDA(cudaStreamSynchronize(r->stream));
                 cudaFree(r->cl_blob); r->cl_blob = nullptr; r->cl_capacity = 0;
                 cudaFree(r->prim_tree); r->prim_tree = nullptr; r->prim_tree_capacity = 0;
                 RT_CUDA(cudaMalloc(&r->cl_blob, tree.bytes()));
                 r->cl_capacity = tree.bytes();
-                RT_CUDA(cudaMalloc(&r->prim_tree, rec_bytes));
+                RT_CUDA(cudaMalloc(&r->prim_tree, 2 * rec_bytes));
                 r->prim_tree_capacity = rec_bytes;
             }
             std::vector<unsigned char> image(tree.bytes());
             tree.pack(image.data());
             RT_CUDA(cudaMemcpyAsync(r->cl_blob, image.data(), image.size(), cudaMemcpyHostToDevice, r->stream));
             RT_CUDA(cudaStreamSynchronize(r->stream));   // `image` is about to go away
+            r->prim_tree_slots = rec_slots;
             r->cl_n_nodes = tree.n_nodes;
             r->cl_first_leaf = tree.first_leaf;
             r->cl_n_entry = tree.n_entry;
@@ -309,7 +323,7 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         }
         r->tree_build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build).count();
     }
-    p.prim_tree = r->cl_n_nodes ? r->prim_tree : nullptr;
+    p.prim_tree = r->cl_n_nodes ? r->prim_tree + parity * r->prim_tree_slots : nullptr;
     p.cl_blob = r->cl_blob;
     p.cl_n_nodes = r->cl_n_nodes;
     p.cl_first_leaf = r->cl_first_leaf;
@@ -346,7 +360,14 @@ static int update_one(RtRenderer* r, const SceneCamera* camera) {
         p.rgba8_out = reinterpret_cast<uint32_t*>(b ? r->rgba8_alt : r->rgba8);
     }
     int launched = 0;
-    RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched));
+    // a depth-1 frame's prep kernel goes to prep_stream, behind the frame that last used this parity's buffers (two
+    // frames back) — and behind the last frame too if that one's prep kernel ran in line (it shares the cost records)
+    const rtk::PrepAsync prep_async{r->prep_stream, r->ev_frame[parity], r->last_prep_async ? nullptr : r->ev_frame[parity ^ 1u],
+                                    r->ev_prep[parity]};
+    bool was_async = false;
+    RT_CUDA(rtk::launch_update(p, r->variant, r->sm_count, r->stream, &launched, RT_PREP_ASYNC ? &prep_async : nullptr, &was_async));
+    r->last_prep_async = was_async;
+    RT_CUDA(cudaEventRecord(r->ev_frame[parity], r->stream));
     r->launches += (uint64_t)launched;
     r->rgba8_fresh = p.rgba8_out != nullptr && !r->target_fresh;
     return RT_OK;

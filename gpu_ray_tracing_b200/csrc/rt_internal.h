@@ -20,8 +20,9 @@ struct RtRenderer {
     uint32_t sphere_capacity = 0;
     float4* geom = nullptr;               // broad-phase records
     uint32_t geom_capacity = 0;
-    float4* prim_tree = nullptr;          // per-frame common-origin records of the tree's child slots
-    size_t prim_tree_capacity = 0;
+    float4* prim_tree = nullptr;          // per-frame common-origin records of the tree's child slots: two buffers of
+    size_t prim_tree_capacity = 0;        // prim_tree_slots records (capacity in bytes per buffer), by frame parity
+    size_t prim_tree_slots = 0;
     float2* first_hit = nullptr;          // (t, sphere index) per texel, written by the primary pass
     float4* wf_queue[2] = {nullptr, nullptr};   // wavefront path queues (3 planes of n_texels float4 each), on first deep frame
     unsigned int* wf_counts = nullptr;
@@ -35,9 +36,16 @@ struct RtRenderer {
     float cl_entry_r = 0.0f;
     uint32_t n_spheres = 0;
     bool has_scene = false;
-    unsigned int* tile_counter = nullptr;  // [2] tickets, then (tile_rows <= rtk::kOrderMaxRows) [2][tile_rows] costs, [tile_rows] order
+    // Per-frame records are double-buffered by frame parity so that a depth-1 frame's prep kernel can run on prep_stream
+    // while the frame before it still renders: tile_counter = [2][2] tickets, then
+    // (order_rows != 0) [3][order_rows] tile-row costs (frame g adds to g % 3, ranks (g - 2) % 3), [2][order_rows] order.
+    unsigned int* tile_counter = nullptr;
     uint32_t order_rows = 0;               // tile rows of the primary pass with a cost / order record; 0 = none
-    uint32_t order_frame = 0;              // parity of the cost buffer the next frame fills
+    uint32_t frame_index = 0;              // updates issued so far
+    bool last_prep_async = false;          // the last update's prep kernel ran on prep_stream
+    cudaStream_t prep_stream = nullptr;
+    cudaEvent_t ev_frame[2] = {nullptr, nullptr};   // recorded on `stream` behind the last kernel of a frame of that parity
+    cudaEvent_t ev_prep[2] = {nullptr, nullptr};    // recorded on prep_stream behind that parity's prep kernel
     unsigned long long* counters = nullptr;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     // asynchronous read-back (rt_read_rgba8_async): second RGBA8 buffer, copy stream, per-slot events

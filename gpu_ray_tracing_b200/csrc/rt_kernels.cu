@@ -2012,7 +2012,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) bounce_streamed_kernel(const
 // its own rtc::primary_record; a group gets the record of its bounding sphere, radius Rc' + m_cam (m_cam = 2^-7 (|Oc| +
 // rho): the camera's share of the members' kappa S inflation, so that every member's inflated sphere lies inside the
 // group's); children hanging under always-passing records stay always candidates; empty slots never are.
-__global__ void prep_primary_tree_kernel(const float4* __restrict__ tree_rec, const uint32_t* __restrict__ link,
+__global__ void __launch_bounds__(kPrepThreads) prep_primary_tree_kernel(const float4* __restrict__ tree_rec, const uint32_t* __restrict__ link,
                                          const float* __restrict__ child_r, const GpuSphere* __restrict__ spheres,
                                          const uint32_t* __restrict__ entry_slot, uint32_t n_entry,
                                          float4* __restrict__ out, uint32_t n_nodes, uint32_t first_leaf, float ox, float oy,
@@ -2023,16 +2023,15 @@ __global__ void prep_primary_tree_kernel(const float4* __restrict__ tree_rec, co
     if (blockIdx.x >= record_blocks) {
         // The blocks behind the record blocks rank the tile rows by what they cost in the last frame, dearest first
         // (ties: top-down, so a first frame is handed out top-down), and clear the record this frame adds to.  A
-        // thread per row counts the rows that go before its own: tile_rows <= kOrderMaxRows broadcast reads.
-        __shared__ unsigned int s_cost[kOrderMaxRows];
-        for (uint32_t j = threadIdx.x; j < tile_rows; j += blockDim.x) s_cost[j] = row_cost_prev[j];
-        __syncthreads();
+        // thread per row counts the rows that go before its own: tile_rows <= kOrderMaxRows broadcast reads of a record no
+        // kernel in flight writes (the frame that filled it is two frames back), so the ranks are a permutation.
         const uint32_t i = (blockIdx.x - record_blocks) * blockDim.x + threadIdx.x;
         if (i >= tile_rows) return;
-        const unsigned int mine = s_cost[i];
+        const unsigned int mine = __ldg(row_cost_prev + i);
         uint32_t before = 0;
+#pragma unroll 8
         for (uint32_t j = 0; j < tile_rows; ++j) {
-            const unsigned int c = s_cost[j];
+            const unsigned int c = __ldg(row_cost_prev + j);
             before += (c > mine || (c == mine && j < i)) ? 1u : 0u;
         }
         row_order[before] = i;
@@ -2328,8 +2327,10 @@ static cudaError_t launch_bounce_tail(const UpdateParams& p, uint32_t grid, cuda
                                        clustered_smem_bytes(p.cl_bytes, p.cl_stack_cap), stream);
 }
 
-cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches) {
+cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, cudaStream_t stream, int* launches,
+                          const PrepAsync* prep_async, bool* prep_was_async) {
     UpdateParams p = p_in;
+    if (prep_was_async) *prep_was_async = false;
     int n_launch = 0;
     const bool primary = (variant == 0 || variant >= 4) && primary_pass_applies(p);
     if (!primary) p.first_hit = nullptr;
@@ -2355,7 +2356,17 @@ cudaError_t launch_update(const UpdateParams& p_in, int variant, int sm_count, c
         // tolerance mode exists for the fused depth-1 pass and the wavefront; the other paths are exact whatever the mode
         const uint32_t fast = (shade || wavefront) ? p.precision : 0u;
         // per-frame records; the same launch zeroes the tile tickets and (wavefront) the frame's queue counters
-        e = launch_prep_primary_tree(p, wavefront, stream);
+        if (shade && prep_async != nullptr) {
+            // nothing the prep kernel reads or writes belongs to the frame before this one: it runs beside it
+            e = cudaStreamWaitEvent(prep_async->stream, prep_async->buffers_free, 0);
+            if (e == cudaSuccess && prep_async->also_wait != nullptr) e = cudaStreamWaitEvent(prep_async->stream, prep_async->also_wait, 0);
+            if (e == cudaSuccess) e = launch_prep_primary_tree(p, false, prep_async->stream);
+            if (e == cudaSuccess) e = cudaEventRecord(prep_async->prep_done, prep_async->stream);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, prep_async->prep_done, 0);
+            if (e == cudaSuccess && prep_was_async) *prep_was_async = true;
+        } else {
+            e = launch_prep_primary_tree(p, wavefront, stream);
+        }
         if (e != cudaSuccess) return e;
         if (shade) {
             if (fast >= 2u) primary_hits_kernel<kPrimShade, 2><<<blocks, kPrimThreads, prim_smem_bytes(), stream>>>(p);
@@ -2425,9 +2436,9 @@ cudaError_t launch_prep_primary_tree(const UpdateParams& p, bool zero_wavefront,
     const float m_cam = rtc::primary_m_cam(p.cam, rho);
     uint32_t n_threads = p.cl_n_nodes * kTreeStride + p.cl_n_entry;
     if (n_threads < kWfWords) n_threads = kWfWords;
-    const uint32_t record_blocks = (n_threads + 255) / 256;
+    const uint32_t record_blocks = (n_threads + kPrepThreads - 1) / kPrepThreads;
     const uint32_t tile_rows = p.row_order != nullptr ? (p.row_count + kPrimTileH - 1) / kPrimTileH : 0u;
-    prep_primary_tree_kernel<<<record_blocks + (tile_rows + 255) / 256, 256, 0, stream>>>(
+    prep_primary_tree_kernel<<<record_blocks + (tile_rows + kPrepThreads - 1) / kPrepThreads, kPrepThreads, 0, stream>>>(
         reinterpret_cast<const float4*>(blob), reinterpret_cast<const uint32_t*>(blob + lay.off_link),
         reinterpret_cast<const float*>(blob + lay.off_child_r), p.spheres, reinterpret_cast<const uint32_t*>(blob + lay.off_entry_slot),
         p.cl_n_entry, const_cast<float4*>(p.prim_tree), p.cl_n_nodes,

@@ -51,6 +51,10 @@ constexpr int kPrimTileH = 8;
 #ifndef RT_PRIM_ROW_ORDER
 #define RT_PRIM_ROW_ORDER 1
 #endif
+// 1: a depth-1 frame's prep kernel runs on a stream of its own, beside the frame before it (PrepAsync); 0: in line (A/B arm)
+#ifndef RT_PREP_ASYNC
+#define RT_PREP_ASYNC 1
+#endif
 #ifndef RT_PRIM_PROBE
 #define RT_PRIM_PROBE 0   // developer probe: rt_exact_tests reports the primary pass's busy cycles summed over its warps
 #endif
@@ -120,13 +124,21 @@ constexpr uint32_t kOrderMaxRows = 2048;   // tile rows the prep kernel ranks (1
 // variant: 1 = baseline (thread per pixel, exact test per sphere from global memory),
 //          2 = tiled broad phase with the scene resident in shared memory,
 //          3 = tiled broad phase streaming sphere chunks through shared memory.
-cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream, int* launches = nullptr);
+// Where a depth-1 frame's prep kernel may run ahead of the frame before it: on `stream`, once `buffers_free` (the frame
+// that last used this frame's record buffers) has passed; the primary pass waits for `prep_done`.  Null: on the frame's stream.
+struct PrepAsync {
+    cudaStream_t stream;
+    cudaEvent_t buffers_free, also_wait, prep_done;   // also_wait: null, or a second event the prep kernel must follow
+};
+cudaError_t launch_update(const UpdateParams& p, int variant, int sm_count, cudaStream_t stream, int* launches = nullptr,
+                          const PrepAsync* prep_async = nullptr, bool* prep_was_async = nullptr);
 bool primary_pass_applies(const UpdateParams& p);
 // max_depth == 1 behind a primary pass: primary_hits_kernel<true> finishes the texels (and honours p.rgba8_out)
 bool fused_shade_applies(const UpdateParams& p, int variant);
 // variant 4 = common-origin primary pass followed by the update kernel (chosen by variant 0 whenever the camera is
 // a pinhole, defocus_angle <= 0); p.prim / p.first_hit must be set.
 cudaError_t launch_prep_primary_tree(const UpdateParams& p, bool zero_wavefront, cudaStream_t stream);
+constexpr int kPrepThreads = 64;   // small blocks of few registers and no shared memory: they fit beside the primary pass's CTAs
 cudaError_t launch_prep_geometry(const GpuSphere* spheres, float4* geom, uint32_t n, cudaStream_t stream);
 cudaError_t launch_quantize(const float4* accum, uchar4* rgba8, uint64_t n_texels, cudaStream_t stream);
 cudaError_t launch_signal(void* flag, uint32_t value, cudaStream_t stream);
