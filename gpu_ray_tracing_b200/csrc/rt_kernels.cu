@@ -1033,12 +1033,29 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
     uint32_t exact_tests = 0, rays = 0;
 #if RT_PRIM_PROBE
     uint32_t probe_busy = 0;
+    // modes 2 / 3: when the warps end / start, in ns after the first warp's arrival (the frame's update-kernel ticket word
+    // is free during a primary pass and holds that reference): rt_exact_tests = the sum over warps, rt_rays_traced = the max
+    uint32_t probe_ref = 0, probe_start = 0;
+    if (RT_PRIM_PROBE >= 2) {
+        unsigned long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        if (lane == 0) {
+            const uint32_t mine = (uint32_t)g | 1u;
+            const uint32_t seen = atomicCAS(P.tile_counter, 0u, mine);
+            probe_ref = seen ? seen : mine;
+        }
+        probe_ref = __shfl_sync(kFull, probe_ref, 0);
+        probe_start = (uint32_t)g - probe_ref;
+        if ((int32_t)probe_start < 0) probe_start = 0;
+    }
 #endif
 
+    // A warp's first ticket is its number in the grid — thousands of warps drawing from one counter in the launch's first
+    // microsecond queue up behind each other — and the counter hands out the tickets behind those.
+    const uint32_t first_drawn = gridDim.x * (uint32_t)(kPrimThreads / 32);
+    uint32_t ticket = blockIdx.x * (uint32_t)(kPrimThreads / 32) + (threadIdx.x >> 5);
     for (;;) {
-        uint32_t tile = 0;
-        if (lane == 0) tile = atomicAdd(P.tile_counter + 1, 1u);
-        tile = __shfl_sync(kFull, tile, 0);
+        uint32_t tile = __shfl_sync(kFull, ticket, 0);
         if (tile >= n_tiles) break;
 #if RT_PRIM_TILE_ORDER == 1
         tile = n_tiles - 1u - tile;   // bottom-up: see RT_PRIM_TILE_ORDER
@@ -1069,9 +1086,20 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
 #if RT_PRIM_PROBE
         probe_busy += (uint32_t)(clock64() - t_begin);
 #endif
+        if (lane == 0) ticket = first_drawn + atomicAdd(P.tile_counter + 1, 1u);
     }
 #if RT_PRIM_PROBE
     exact_tests = lane == 0 ? probe_busy : 0u;   // developer probe: the counter reports the warps' busy cycles instead
+    if (RT_PRIM_PROBE >= 2) {
+        unsigned long long g;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+        const uint32_t when = RT_PRIM_PROBE == 2 ? (uint32_t)g - probe_ref : probe_start;
+        if (lane == 0) {
+            atomicAdd(&P.counters[1], (unsigned long long)when);
+            atomicMax(&P.counters[0], (unsigned long long)when);
+        }
+        return;
+    }
 #endif
     prim_flush(P, exact_tests, rays, lane);
 }
