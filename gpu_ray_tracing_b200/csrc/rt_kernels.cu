@@ -448,6 +448,13 @@ constexpr int kPrimSlots = 8;   // shared-memory floats per ray: d.xyz, o.xyz, n
 static_assert((kPrimList + 4) * 6 >= kPrimRays * 32, "prim_setup parks one float per ray and lane in the list area");
 static_assert(kPrimThreads % 32 == 0 && kPrimWork >= 160 + 64, "entry list (rtt::kMaxEntry) + growth");
 
+constexpr int kPrimSched = 4;   // per-warp words behind the work stack: the current tile's row and starting clock (+ padding)
+__device__ __forceinline__ uint32_t clock32() {
+    uint32_t c;
+    asm volatile("mov.u32 %0, %%clock;" : "=r"(c));
+    return c;
+}
+
 struct PrimLanes {
     float2 ux[kPrimRays / 2], uy[kPrimRays / 2], uz[kPrimRays / 2];   // .x = row 2q, .y = row 2q + 1
     uint32_t alive;   // bit p: ray p is traced here
@@ -1007,11 +1014,12 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
     // per warp: [kPrimList + 4] float4 records of the listed spheres, [kPrimList + 4] their indices, as many
     // nearest-distance bounds, [kPrimWork] nodes
     uint32_t* s_warp = reinterpret_cast<uint32_t*>(s_dyn) + kPrimRays * kPrimSlots * kPrimThreads +
-                       (threadIdx.x >> 5) * (6 * (kPrimList + 4) + kPrimWork);
+                       (threadIdx.x >> 5) * (6 * (kPrimList + 4) + kPrimWork + kPrimSched);
     float4* s_rec = reinterpret_cast<float4*>(s_warp);
     uint32_t* s_idx = s_warp + 4 * (kPrimList + 4);
     float* s_near = reinterpret_cast<float*>(s_idx + (kPrimList + 4));
     uint32_t* s_work = s_idx + 2 * (kPrimList + 4);
+    uint32_t* s_sched = s_work + kPrimWork;   // [0] the current tile's row, [1] the clock at its start
     const int lane = threadIdx.x & 31;
 
     const uint32_t seed_bits = rtc::f2u(P.cam.random_seed * 4294967296.0f);
@@ -1052,8 +1060,10 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
 
     // A warp's first ticket is its number in the grid — thousands of warps drawing from one counter in the launch's first
     // microsecond queue up behind each other — and the counter hands out the tickets behind those.
-    const uint32_t first_drawn = gridDim.x * (uint32_t)(kPrimThreads / 32);
     uint32_t ticket = blockIdx.x * (uint32_t)(kPrimThreads / 32) + (threadIdx.x >> 5);
+#if !RT_PRIM_STATIC_FIRST
+    if (lane == 0) ticket = atomicAdd(P.tile_counter + 1, 1u);   // (A/B arm: every ticket drawn)
+#endif
     for (;;) {
         uint32_t tile = __shfl_sync(kFull, ticket, 0);
         if (tile >= n_tiles) break;
@@ -1067,9 +1077,13 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
         }
 #endif
         // ticket -> tile: the ticket's tile row goes through the frame's row order (dearest rows of the last frame first)
+        // (the tile's row and starting time wait in the warp's shared memory, not in registers the tile's work is short of)
         uint32_t tile_row = tile / tiles_x;
         if (P.row_order != nullptr) tile_row = P.row_order[tile_row];
-        const long long t_begin = clock64();
+        if (lane == 0) {
+            s_sched[0] = tile_row;
+            s_sched[1] = clock32();
+        }
         const int x = (int)((tile % tiles_x) * kPrimTileW) + lane;
         const int row0 = (int)(tile_row * kPrimTileH);
         PrimLanes L;
@@ -1082,11 +1096,14 @@ __global__ void __launch_bounds__(kPrimThreads, kPrimCtas) primary_hits_kernel(c
             prim_tree_walk(T, s_work, s_rec, s_idx, s_near, m, chord, s_d, P, L, untraced, exact_tests, lane);
         }
         prim_finish<kMode, F>(P, x, row0, s_d, L, untraced, seed_bits, reset, rays);
-        if (lane == 0 && P.row_cost_cur != nullptr) atomicAdd(P.row_cost_cur + tile_row, (unsigned int)((clock64() - t_begin) >> 6));
+        if (lane == 0) {
+            const uint32_t spent = clock32() - s_sched[1];
+            if (P.row_cost_cur != nullptr) atomicAdd(P.row_cost_cur + s_sched[0], spent >> 6);
 #if RT_PRIM_PROBE
-        probe_busy += (uint32_t)(clock64() - t_begin);
+            probe_busy += spent;
 #endif
-        if (lane == 0) ticket = first_drawn + atomicAdd(P.tile_counter + 1, 1u);
+            ticket = (RT_PRIM_STATIC_FIRST ? gridDim.x * (uint32_t)(kPrimThreads / 32) : 0u) + atomicAdd(P.tile_counter + 1, 1u);
+        }
     }
 #if RT_PRIM_PROBE
     exact_tests = lane == 0 ? probe_busy : 0u;   // developer probe: the counter reports the warps' busy cycles instead
@@ -2279,7 +2296,7 @@ __global__ void __launch_bounds__(kBlockThreads, 2) update_streamed_kernel(const
 // ---------------------------------------------------------------------------------------------
 static size_t prim_smem_bytes() {
     return (size_t)kPrimRays * kPrimSlots * kPrimThreads * sizeof(float) +
-           (size_t)(kPrimThreads / 32) * (6 * (kPrimList + 4) + kPrimWork) * sizeof(uint32_t);
+           (size_t)(kPrimThreads / 32) * (6 * (kPrimList + 4) + kPrimWork + kPrimSched) * sizeof(uint32_t);
 }
 
 static size_t bounce_smem_bytes() {

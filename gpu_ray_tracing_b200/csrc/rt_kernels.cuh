@@ -55,6 +55,11 @@ constexpr int kPrimTileH = 8;
 #ifndef RT_PREP_ASYNC
 #define RT_PREP_ASYNC 1
 #endif
+// 1: a warp's first tile of a primary pass is its number in the grid, tickets are drawn from the second tile on; 0: every
+// tile is drawn (the A/B arm)
+#ifndef RT_PRIM_STATIC_FIRST
+#define RT_PRIM_STATIC_FIRST 1
+#endif
 #ifndef RT_PRIM_PROBE
 #define RT_PRIM_PROBE 0   // developer probe: rt_exact_tests reports the primary pass's busy cycles summed over its warps
 #endif
