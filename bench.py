@@ -81,9 +81,9 @@ def workload_config(n_gpus):
         "workload": f"{N_SPHERES} random spheres (seed 1234) at {W}x{H}, max_depth 1, 1 sample/pixel, one frame per GPU per step",
         "spheres": N_SPHERES, "width": W, "height": H, "max_depth": 1, "frames_per_step": n_gpus,
         "parallelism": f"frames sharded over {n_gpus} GPU(s), scene replicated" + (
-            ", every frame's RGBA8 image delivered into rank 0's device memory over NVLink (CUDA-IPC mapping): stored by the "
-            "shading pass itself with a release flag behind (N <= 4), or written locally and sent by a copy engine behind the "
-            "next frame (N >= 5, where rank 0's ingress runs near the link's bandwidth); weak_like_for_like.mode says which" if n_gpus > 1 else ""),
+            ", every frame's RGBA8 image delivered into rank 0's device memory over NVLink (CUDA-IPC mapping): written locally "
+            "by the shading pass and sent by a copy engine behind the next frame (`copy`; the other way, stores out of the "
+            "shading pass with a release flag behind, is timed beside it); weak_like_for_like.mode says which the value used" if n_gpus > 1 else ""),
         "l2": "accumulation image (132.7 MB float4, stored once per step) exceeds the 126 MB L2; the 32 KB sphere buffer is shared-memory resident by design",
     }
 
@@ -339,10 +339,11 @@ def run_ours(args):
     #          nothing runs after the kernel, but the stores cross NVLink while the SMs compute
     #   copy   the shading pass writes the frame into a local buffer (rt_set_rgba8_output) and a copy engine sends it on a copy
     #          stream while the next frame renders (rt_read_rgba8_async): decoupled from the SMs, one frame of latency
-    # auto = fused while rank 0's ingress demand (N - 1 frames per step) stays under half the measured link bandwidth, copy
-    # beyond (N >= 5 here): near the link's limit the fused stores back-pressure the SMs that issue them.
-    demand_gbs = (world - 1) * frame_bytes / 0.29e-3 / 1e9
-    mode = args.deliver if args.deliver != "auto" else ("fused" if demand_gbs < 0.5 * 770.0 else "copy")
+    # auto = copy: measured at every N (profiles/r2_bench_n*_final.json, both ways timed in each run) the copy engines
+    # deliver a frame at less cost to the step than the shading pass's own stores — N = 2 / 4: 0.277 against 0.287 ms per
+    # step, N = 8 (rank 0's ingress at the link's bandwidth, where the stores back-pressure the SMs that issue them): 0.296
+    # against 0.356.  Fused delivery remains what a caller picks for latency: its frame is whole when the kernel ends.
+    mode = args.deliver if args.deliver != "auto" else "copy"
 
     def weak_step(i, how):
         if how == "fused":
