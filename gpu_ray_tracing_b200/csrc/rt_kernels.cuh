@@ -60,6 +60,16 @@ constexpr int kPrimTileH = 8;
 #ifndef RT_PRIM_STATIC_FIRST
 #define RT_PRIM_STATIC_FIRST 1
 #endif
+// Bounces a warp of the tail launch keeps its 64 paths of a short queue before the survivors are dealt out again, evenly
+// (an ODD number: the hand-back must not go to the queue the pass loads from); 0: every path is finished where it was
+// first loaded (the A/B arm)
+#ifndef RT_WF_REDEAL_AFTER
+#define RT_WF_REDEAL_AFTER 1u
+#endif
+// ... and the bounces the evenly dealt survivors are kept before they are dealt out once more (odd; 0: to their end)
+#ifndef RT_WF_REDEAL_AGAIN
+#define RT_WF_REDEAL_AGAIN 0u
+#endif
 #ifndef RT_PRIM_PROBE
 #define RT_PRIM_PROBE 0   // developer probe: rt_exact_tests reports the primary pass's busy cycles summed over its warps
 #endif
