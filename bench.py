@@ -172,9 +172,18 @@ def ffma_peak_tflops(device):
 
 
 def git_head():
+    """The commit the library was built at: from git where the checkout has its history, else from the note
+    __graft_entry__.build() leaves beside the library (a gpurun snapshot travels without .git)."""
     try:
-        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip() or None
+        head = subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+        if head:
+            return head
     except Exception:
+        pass
+    try:
+        with open(os.path.join(ROOT, "gpu_ray_tracing_b200", "librt_b200.so.commit")) as f:
+            return f.read().strip() or None
+    except OSError:
         return None
 
 
