@@ -617,7 +617,7 @@ def run_ours(args):
         "cpu_baseline": cpu, "e2e": e2e, "deep": deep, "strong": strong, "weak_like_for_like": like,
         "sustained": sustained, "gather_check": gather_check, "gpu_launches": int(launches), "clocks": clocks,
         "parity": parity, "parity_libm": parity_libm,
-        "tree": {"build_ms_1024_spheres": r.tree_build_ms(), "info": r.tree_info()},
+        "tree": tree_block(rt, scenes, r, local_rank),
         "git_head": git_head(),
     }
     emit_json(line)
@@ -757,6 +757,20 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
                "link_floor_ms": inbound / 770e9 * 1e3,
                "identical_to_single_gpu_frame": same_p, "frames": K, "waits_timed_out": timed_out}
     barrier()
+    return out
+
+
+def tree_block(rt, scenes, r, local_rank):
+    """Host time of the tree build (rt_tree.h: built on one host thread at the first update after new sphere bytes) for the
+    benchmark scene and for the 65,536-sphere scene of config 5, next to rt_tree_info's (nodes, levels, bounce path)."""
+    out = {"build_ms_1024_spheres": r.tree_build_ms(), "info": r.tree_info()}
+    with rt.Renderer(64, 36, device=local_rank) as rb:
+        rb.set_scene(scenes.grid_scene(65536))
+        rb.init()
+        rb.update(rt.orbit_camera(3, 256, 64, 36))
+        rb.synchronize()
+        out["build_ms_65536_spheres"] = rb.tree_build_ms()
+        out["info_65536_spheres"] = rb.tree_info()
     return out
 
 

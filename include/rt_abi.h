@@ -246,6 +246,9 @@ RT_API int rt_quantize(RtRenderer* r);                       /* accum -> rgba8, 
 /* Same, written straight into a caller-owned DEVICE buffer of row_count*width uchar4 (e.g. the send
  * buffer of an NCCL gather).  Asynchronous on the renderer's stream. */
 RT_API int rt_quantize_into(RtRenderer* r, void* device_rgba8);
+/* The renderer's stream: every kernel of rt_update runs on it or is ordered into it by events (a depth-1 frame's
+ * per-frame record kernel runs on an internal stream beside the frame before it and the frame's main kernel waits for
+ * it), so work a caller enqueues on this stream after rt_update sees the finished frame. */
 RT_API int rt_stream(RtRenderer* r, void** cuda_stream);
 RT_API int rt_window(RtRenderer* r, uint32_t* width, uint32_t* height,
                      uint32_t* row_begin, uint32_t* row_count);
