@@ -381,3 +381,35 @@ def test_async_read_into_device_memory():
             assert np.array_equal(host.numpy().reshape(H, W, 4), want)
     finally:
         rt.device_free(0, dst)
+
+
+def test_back_to_back_frames_keep_their_own_records():
+    """Frames enqueued without a synchronisation between them: a depth-1 frame's per-frame records are prepared on a
+    stream of their own WHILE the frame before it renders (double-buffered by frame parity), deep frames prepare theirs
+    in line, and a scene upload sits in the middle.  Every frame ACCUMULATES (camera_has_moved = 0 after the first) from a
+    pose of its own, so one frame traced with another frame's records would show in the running mean: the result must be
+    the oracle's fed the same sequence, bit for bit."""
+    W, H = 640, 360
+    depths = [1, 1, 1, 5, 1, 1, 3, 1, 1, 1]
+    cams = []
+    for f, depth in enumerate(depths):
+        cam = rt.orbit_camera(3 * f + 1, 64, W, H, radius=14.0, cam_height=2.5 + 0.2 * f, fov_deg=30.0)
+        cam.max_depth = float(depth)
+        cam.samples_per_pixel = 500.0
+        cam.camera_has_moved = 1.0 if f == 0 else 0.0
+        cam.random_seed = 0.03125 * (f + 1)
+        cams.append(cam)
+    scene_a, scene_b = scenes.default_scene(), scenes.random_scene(300)
+    cpu = None
+    for f, cam in enumerate(cams):
+        cpu, _ = ol.oracle_update(cam, scene_a if f < 6 else scene_b, W, H, accum=cpu)
+    with rt.Renderer(W, H) as r:
+        r.set_scene(scene_a)
+        r.init()
+        for f, cam in enumerate(cams):
+            if f == 6:
+                r.set_scene(scene_b)
+            r.update(cam)
+        gpu = r.read_accum()
+    assert_parity(gpu, cpu, "ten frames back to back, mixed depths, scene change")
+    assert (gpu[..., 3] == float(len(cams))).all()
