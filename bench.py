@@ -647,9 +647,9 @@ def strong_leg(rt, dist, torch, np, scenes, scene, rank, world, local_rank, barr
     deliver -> release arrived[i] = f + 1; rank 0 waits for every arrived[*] >= f + 1 — the frame is whole in its memory —
     and releases consumed = f + 1.  Time = device time, max over ranks, for K whole frames.  Afterwards rank 0 renders the
     same frames alone (t1) and compares."""
-    # frames per timed leg: the pipelined gather ends on a drain of one frame's copies, which the leg's time includes —
-    # over 20 frames that is 5 % of the figure, over 100 it is 1 %
-    K = max(5, min(args.steps, 100))
+    # frames per timed leg, whatever --steps says (that is the headline's K): the pipelined gather ends on a drain of one
+    # frame's copies, which the leg's time includes — over 20 frames that is 5 % of the figure, over 100 it is 1 %
+    K = 100
     frame8 = W8K * H8K * 4
     band_rows = int(os.environ.get("RT_BENCH_BAND_ROWS", "16"))   # (a multiple of 8; A/B knob)
     g = Gather(rt, dist, torch, rank, world, local_rank, frame8)
