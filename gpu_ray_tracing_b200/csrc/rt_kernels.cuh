@@ -77,7 +77,8 @@ constexpr int kPrimTileH = 8;
 #define RT_PRIM_WORK 224
 #endif
 // CTA shape of the primary pass: no block barrier anywhere, so the CTA is only a container of warps; 2 x 11 warps
-// per SM is what 88 registers and 10.2 KB of shared memory per warp (8 KB ray slots + lists) allow
+// per SM is what 80 registers (ptxas' cap for 2 x 352 threads: the file is allotted per 4 warps) and 10.2 KB of shared
+// memory per warp (8 KB ray slots + lists) allow
 constexpr int kPrimThreads = RT_PRIM_THREADS;
 constexpr int kPrimCtas = RT_PRIM_CTAS;
 constexpr int kPrimWork = RT_PRIM_WORK;   // per-warp stack of tree nodes awaiting their tile test (entry list <= 160 + growth)
